@@ -1,0 +1,610 @@
+// links_b200/csrc/kernels.cuh -- the hot-path kernels (sm_100a).
+//
+//   pack_kernel          ASCII -> 2-bit codes + invalid-base bitmap (+ per-record "has invalid" flag)
+//   rank_build_kernel    per flagged record: valid-k-mer-start bitmap + prefix ranks (rank/select)
+//   bf_build_kernel      K2: contig k-mers -> Bloom bits            (ref src/LINKS.hpp:316-324)
+//   table_build_kernel   K4a: contig k-mers -> open-addressing table (ref :569-601,379-402)
+//   extract_kernel       K3+K5a: read k-mer pairs -> Bloom probe -> pair-set insert (ref :515-567,354-378)
+//   classify_kernel      K4b: unique pairs -> table lookups -> link rows / issues (ref :824-968)
+//
+// HBM layout (all device arrays are flat, 256-byte aligned cudaMalloc blocks):
+//   packed   u32[ceil(B/16)+pad]   2 bits per base, base j of a word at bits 2j..2j+1
+//   inv      u32[ceil(B/32)+pad]   1 bit per base, 1 = not ACGTU
+//   bloom    u32[bytes/4]          btllib byte array viewed as little-endian words
+//   table    {u64 key,u64 val}[cap+1]   key = ntHash (fwd or rev) of a contig k-mer, EMPTY = ~0
+//                                  val = pos<<32 | tig<<3 | orient<<2 | multiple<<1 | present
+//   pairs    {u64 h_a,u64 h_b,u64 okey,u64 pad}[cap]   32 B = one DRAM sector per probe
+//   rows     u64 key[] + i32 distance[]  (dense packed row key, see pack_row_key)
+#pragma once
+#include "device_prims.cuh"
+#include "nthash.cuh"
+
+#include <cstdint>
+#include <cuda_runtime.h>
+
+namespace links {
+
+constexpr uint64_t kEmpty = ~0ULL;
+constexpr int kTile = 1024;        // candidates (or contig positions) per scheduling tile
+constexpr int kCtaThreads = 256;
+
+struct TableSlot { uint64_t key, val; };
+struct PairSlot { uint64_t a, b, okey, pad; };
+
+struct TableView { TableSlot* slots; uint64_t mask; int shift; /* 64 - log2(cap) */ };
+struct PairView { PairSlot* slots; uint64_t mask; int shift; };
+
+// counters accumulated on the device (one atomic per warp at kernel end)
+struct Counters {
+  unsigned long long n_candidates, n_survivors, n_unique, n_bf_probes, n_contig_kmers;
+  unsigned long long ct_ok_pairs, ct_problem_pairs, ct_ok_contig, ct_iz_issues, ct_illogical, ct_gate_fail;
+  unsigned long long n_rows, n_issues, issue_overflow;
+};
+
+struct IssueRec { // mirrors links_issue
+  uint32_t tig; uint8_t o1, o2, pad_[2];
+  uint64_t tig_len, s1, e1, s2, e2, pet_size;
+  int64_t insert_size;
+};
+
+__device__ __forceinline__ unsigned long long warp_sum_ull(unsigned long long v)
+{
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+
+__device__ __forceinline__ uint64_t slot_hash1(uint64_t h) { return h * 0x9E3779B97F4A7C15ULL; }
+__device__ __forceinline__ uint64_t slot_hash2(uint64_t a, uint64_t b)
+{
+  uint64_t x = a * 0x9E3779B97F4A7C15ULL + b;
+  x ^= x >> 32;
+  return x * 0xD6E8FEB86659FD93ULL;
+}
+
+// ------------------------------------------------------------------ pack
+
+__device__ __forceinline__ uint32_t find_record(const uint64_t* __restrict__ off, uint32_t n, uint64_t base0, uint64_t g)
+{
+  // largest r with off[r]-base0 <= g
+  uint32_t lo = 0, hi = n;
+  while (hi - lo > 1) {
+    const uint32_t mid = (lo + hi) >> 1;
+    if (off[mid] - base0 <= g) lo = mid; else hi = mid;
+  }
+  return lo;
+}
+
+// one thread = 32 bases -> two packed words + one invalid-mask word
+__global__ void __launch_bounds__(kCtaThreads) pack_kernel(const uint8_t* __restrict__ ascii, uint64_t n_bases,
+                                                           uint32_t* __restrict__ packed, uint32_t* __restrict__ inv,
+                                                           const uint64_t* __restrict__ off, uint32_t n_rec, uint64_t base0,
+                                                           uint32_t* __restrict__ flags)
+{
+  const uint64_t t = uint64_t(blockIdx.x) * blockDim.x + threadIdx.x;
+  const uint64_t g0 = t * 32;
+  if (g0 >= n_bases) return;
+  uint32_t bytes[8];
+  if (g0 + 32 <= n_bases) {
+    const uint4 a = __ldg(reinterpret_cast<const uint4*>(ascii + g0));
+    const uint4 b = __ldg(reinterpret_cast<const uint4*>(ascii + g0) + 1);
+    bytes[0] = a.x; bytes[1] = a.y; bytes[2] = a.z; bytes[3] = a.w;
+    bytes[4] = b.x; bytes[5] = b.y; bytes[6] = b.z; bytes[7] = b.w;
+  } else {
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      uint32_t v = 0;
+      for (int q = 0; q < 4; ++q) {
+        const uint64_t g = g0 + j * 4 + q;
+        v |= uint32_t(g < n_bases ? ascii[g] : uint8_t('N')) << (8 * q);
+      }
+      bytes[j] = v;
+    }
+  }
+  uint32_t p[2] = {0, 0};
+  uint32_t m = 0;
+#pragma unroll
+  for (int j = 0; j < 32; ++j) {
+    const uint32_t c = (bytes[j >> 2] >> (8 * (j & 3))) & 0xFFu;
+    p[j >> 4] |= base_code(c) << (2 * (j & 15));
+    m |= (base_valid(c) ? 0u : 1u) << j;
+  }
+  packed[t * 2] = p[0];
+  packed[t * 2 + 1] = p[1];
+  inv[t] = m;
+  // flag the records that own an invalid base (rare): they take the rank/select path
+  if (g0 + 32 > n_bases) m &= (n_bases - g0 >= 32) ? 0xFFFFFFFFu : ((1u << (n_bases - g0)) - 1u);
+  while (m) {
+    const int j = __ffs(m) - 1;
+    m &= m - 1;
+    const uint32_t r = find_record(off, n_rec, base0, g0 + j);
+    atomicOr(flags + r, 1u);
+    // skip the other invalid bases of the same record inside this word
+    const uint64_t end = off[r + 1] - base0;
+    if (end >= g0 + 32) break;
+    m &= ~((1u << (end - g0)) - 1u);
+  }
+}
+
+// ------------------------------------------------------------------ rank/select for records with invalid bases
+//
+// btllib::NtHash::roll() visits, in increasing order, exactly the k-mer starts whose window holds
+// no invalid base (nthash.hpp:1493-1533).  LINKS pairs the n-th such start of the stream begun
+// at `offset` with the n-th of the stream begun at `offset+d` (src/LINKS.hpp:525-543), so a
+// bit-exact kernel needs rank/select over "valid start" bits, not raw positions.
+// For record r: words live at wb = (g0 >> 6) + 2r ; vs[wb+w] = valid-start bits of positions
+// 64w..64w+63 ; vrank[wb+w] = number of valid starts before 64w ; vrank[wb+nwords] = total.
+
+__global__ void __launch_bounds__(kCtaThreads) rank_build_kernel(const uint32_t* __restrict__ inv,
+                                                                 const uint64_t* __restrict__ off, uint64_t base0,
+                                                                 const uint32_t* __restrict__ flags, int k,
+                                                                 unsigned long long* __restrict__ vs,
+                                                                 uint32_t* __restrict__ vrank)
+{
+  const uint32_t r = blockIdx.x;
+  if (!flags[r]) return;
+  __shared__ uint32_t sm[9];
+  const uint64_t g0 = off[r] - base0, len = off[r + 1] - off[r];
+  const uint64_t wb = (g0 >> 6) + 2ull * r;
+  const uint64_t npos = len >= uint64_t(k) ? len - k + 1 : 0;
+  const uint64_t nwords = (npos + 63) >> 6;
+  uint32_t carry = 0;
+  for (uint64_t w0 = 0; w0 < nwords; w0 += kCtaThreads) {
+    const uint64_t w = w0 + threadIdx.x;
+    unsigned long long bits = 0;
+    if (w < nwords) {
+      const uint64_t p0 = w * 64;
+      const uint64_t pend = p0 + 64 < npos ? p0 + 64 : npos; // positions [p0, pend)
+      int run = 0;
+      for (uint64_t x = p0; x < pend + k - 1; ++x) {
+        const uint64_t g = g0 + x;
+        const bool bad = (inv[g >> 5] >> (g & 31)) & 1u;
+        run = bad ? 0 : run + 1;
+        if (run >= k) bits |= 1ull << (x - (k - 1) - p0);
+      }
+      vs[wb + w] = bits;
+    }
+    uint32_t total;
+    const uint32_t ex = block_excl_scan(uint32_t(__popcll(bits)), &total, sm);
+    if (w < nwords) vrank[wb + w] = carry + ex;
+    carry += total;
+  }
+  if (threadIdx.x == 0) vrank[wb + nwords] = carry;
+}
+
+struct RankView { const unsigned long long* vs; const uint32_t* vrank; uint64_t wb, nwords, npos; uint32_t total; };
+
+__device__ __forceinline__ uint32_t rank_of(const RankView& rv, uint64_t p)
+{
+  if (p >= rv.npos) return rv.total;
+  const uint64_t w = p >> 6;
+  return rv.vrank[rv.wb + w] + __popcll(rv.vs[rv.wb + w] & ((1ull << (p & 63)) - 1ull));
+}
+__device__ __forceinline__ uint64_t select_of(const RankView& rv, uint32_t n) // n < total
+{
+  uint64_t lo = 0, hi = rv.nwords; // largest w with vrank[w] <= n
+  while (hi - lo > 1) {
+    const uint64_t mid = (lo + hi) >> 1;
+    if (rv.vrank[rv.wb + mid] <= n) lo = mid; else hi = mid;
+  }
+  unsigned long long bits = rv.vs[rv.wb + lo];
+  for (uint32_t i = rv.vrank[rv.wb + lo]; i < n; ++i) bits &= bits - 1;
+  return lo * 64 + (__ffsll((long long)bits) - 1);
+}
+
+// ------------------------------------------------------------------ tile scheduling
+
+// seg_tile_start[s] = first tile of segment s (cumulative); returns s owning `tile`
+__device__ __forceinline__ uint32_t find_segment(const uint32_t* __restrict__ seg_tile_start, uint32_t n_seg, uint32_t tile)
+{
+  uint32_t lo = 0, hi = n_seg;
+  while (hi - lo > 1) {
+    const uint32_t mid = (lo + hi) >> 1;
+    if (seg_tile_start[mid] <= tile) lo = mid; else hi = mid;
+  }
+  return lo;
+}
+
+// ------------------------------------------------------------------ contigs: Bloom build + table build
+
+struct ContigBatch {
+  const uint32_t* packed; const uint32_t* inv; const uint64_t* off; uint64_t base0;
+  const uint32_t* seg_tile_start; uint32_t n_seq, n_tiles; uint32_t first_tig;
+};
+
+__device__ __forceinline__ void table_insert(const TableView& tv, uint64_t h, uint64_t payload)
+{
+  if (h == kEmpty) { // the sentinel value itself is a legal hash: it owns the extra slot [cap]
+    unsigned long long* v = reinterpret_cast<unsigned long long*>(&tv.slots[tv.mask + 1].val);
+    const unsigned long long old = atomicOr(v, 1ull);
+    atomicOr(v, (old & 1ull) ? 2ull : payload);
+    return;
+  }
+  uint64_t i = slot_hash1(h) >> tv.shift;
+  for (;;) {
+    unsigned long long* kp = reinterpret_cast<unsigned long long*>(&tv.slots[i].key);
+    unsigned long long cur = *reinterpret_cast<volatile unsigned long long*>(kp);
+    if (cur == kEmpty) cur = atomicCAS(kp, kEmpty, h);
+    unsigned long long* vp = reinterpret_cast<unsigned long long*>(&tv.slots[i].val);
+    if (cur == kEmpty) { atomicOr(vp, payload | 1ull); return; } // first of this hash: (tig,pos,orient)
+    if (cur == h) { atomicOr(vp, 2ull); return; }                // seen again: multiple (ref :398-400)
+    i = (i + 1) & tv.mask;
+  }
+}
+
+__device__ __forceinline__ uint64_t table_lookup(const TableView& tv, uint64_t h)
+{
+  if (h == kEmpty) return tv.slots[tv.mask + 1].val;
+  uint64_t i = slot_hash1(h) >> tv.shift;
+  for (;;) {
+    const ulonglong2 s = __ldg(reinterpret_cast<const ulonglong2*>(&tv.slots[i]));
+    if (s.x == h) return s.y;
+    if (s.x == kEmpty) return 0;
+    i = (i + 1) & tv.mask;
+  }
+}
+
+// MODE 0: Bloom insert (KmerBloomFilter::insert, bloom_filter.hpp:814-821)
+// MODE 1: table insert of fwd and rev hash of every valid position (populate_mate_info, :577-598)
+template <int MODE>
+__global__ void __launch_bounds__(kCtaThreads) contig_kernel(ContigBatch cb, int k, uint64_t kseed,
+                                                             const ulonglong2* __restrict__ g_tab, BloomView bf,
+                                                             TableView tv, Counters* __restrict__ ctr)
+{
+  extern __shared__ ulonglong2 s_tab[];
+  for (int i = threadIdx.x; i < k * 4; i += blockDim.x) s_tab[i] = g_tab[i];
+  __shared__ uint32_t s_seg;
+  __syncthreads();
+  unsigned long long n_kmers = 0;
+  for (uint32_t tile = blockIdx.x; tile < cb.n_tiles; tile += gridDim.x) {
+    if (threadIdx.x == 0) s_seg = find_segment(cb.seg_tile_start, cb.n_seq, tile);
+    __syncthreads();
+    const uint32_t c = s_seg;
+    const uint64_t g0 = cb.off[c] - cb.base0, len = cb.off[c + 1] - cb.off[c];
+    const uint64_t npos = len - k + 1; // segments with len < k own zero tiles
+    const uint64_t p_begin = uint64_t(tile - cb.seg_tile_start[c]) * kTile;
+    for (int q = threadIdx.x; q < kTile; q += kCtaThreads) {
+      const uint64_t p = p_begin + q;
+      if (p >= npos) break;
+      if (!window_valid(cb.inv, g0 + p, k)) continue;
+      uint64_t f, r;
+      hash_kmer(cb.packed, g0 + p, k, s_tab, f, r);
+      if (MODE == 0) {
+        bloom_insert(bf, f, r, kseed);
+      } else {
+        const uint64_t payload = (p << 32) | (uint64_t(cb.first_tig + c) << 3);
+        table_insert(tv, f, payload);
+        table_insert(tv, r, payload | 4ull);
+        n_kmers += 2;
+      }
+    }
+    __syncthreads();
+  }
+  if (MODE == 1) {
+    n_kmers = warp_sum_ull(n_kmers);
+    if ((threadIdx.x & 31) == 0 && n_kmers) atomicAdd(&ctr->n_contig_kmers, n_kmers);
+  }
+}
+
+// ------------------------------------------------------------------ reads: extract + probe + pair-set insert
+
+struct ReadBatch {
+  const uint32_t* packed; const uint32_t* inv; const uint64_t* off; uint64_t base0;
+  const uint32_t* seg_tile_start; uint32_t n_seq, n_tiles;
+  const uint32_t* flags; const unsigned long long* vs; const uint32_t* vrank;
+  uint64_t first_read_idx;
+};
+
+struct DistParams { const uint32_t* dist; const uint32_t* step; uint32_t n_dist; uint64_t offset; };
+
+__device__ __forceinline__ ulonglong2 cas128(PairSlot* slot, ulonglong2 cmp, ulonglong2 val)
+{
+  ulonglong2 old;
+  asm volatile(
+    "{\n\t.reg .b128 c, v, o;\n\t"
+    "mov.b128 c, {%2, %3};\n\t"
+    "mov.b128 v, {%4, %5};\n\t"
+    "atom.global.cas.b128 o, [%6], c, v;\n\t"
+    "mov.b128 {%0, %1}, o;\n\t}"
+    : "=l"(old.x), "=l"(old.y)
+    : "l"(cmp.x), "l"(cmp.y), "l"(val.x), "l"(val.y), "l"(slot)
+    : "memory");
+  return old;
+}
+
+// mate_pair first-wins insert (ref src/LINKS.hpp:370-373): set semantics on (a,b); the winner's
+// distance index is recovered from the minimum order key.  Returns true if (a,b) was new.
+__device__ __forceinline__ bool pair_insert(const PairView& pv, uint64_t a, uint64_t b, uint64_t okey, bool multi_d)
+{
+  uint64_t i = slot_hash2(a, b) >> pv.shift;
+  bool fresh = false;
+  for (;;) {
+    PairSlot* s = pv.slots + i;
+    ulonglong2 cur = __ldcg(reinterpret_cast<const ulonglong2*>(s));
+    if (cur.x == kEmpty || cur.y == kEmpty) { // empty (or a torn read of a slot being claimed)
+      cur = cas128(s, make_ulonglong2(kEmpty, kEmpty), make_ulonglong2(a, b));
+      if (cur.x == kEmpty && cur.y == kEmpty) { fresh = true; cur = make_ulonglong2(a, b); }
+    }
+    if (cur.x == a && cur.y == b) {
+      if (multi_d) atomicMin(reinterpret_cast<unsigned long long*>(&s->okey), (unsigned long long)okey);
+      return fresh;
+    }
+    i = (i + 1) & pv.mask;
+  }
+}
+
+constexpr int kOkeyRankBits = 28, kOkeyDistBits = 8;
+__host__ __device__ __forceinline__ uint64_t make_okey(uint64_t read_idx, uint32_t d_idx, uint64_t rank)
+{
+  return (read_idx << (kOkeyRankBits + kOkeyDistBits)) | (uint64_t(d_idx) << kOkeyRankBits) | rank;
+}
+__host__ __device__ __forceinline__ uint32_t okey_d_idx(uint64_t okey)
+{
+  return uint32_t(okey >> kOkeyRankBits) & ((1u << kOkeyDistBits) - 1u);
+}
+
+__global__ void __launch_bounds__(kCtaThreads) extract_kernel(ReadBatch rb, DistParams dp, int k, uint64_t kseed,
+                                                              const ulonglong2* __restrict__ g_tab, BloomView bf,
+                                                              PairView pv, Counters* __restrict__ ctr)
+{
+  extern __shared__ ulonglong2 s_tab[];
+  for (int i = threadIdx.x; i < k * 4; i += blockDim.x) s_tab[i] = g_tab[i];
+  __shared__ uint32_t s_seg;
+  __shared__ uint32_t s_va0, s_vb0;
+  __shared__ unsigned long long s_cnt;
+  __syncthreads();
+  unsigned long long n_cand = 0, n_surv = 0, n_uniq = 0;
+  uint32_t n_probe = 0;
+  unsigned long long n_probe_acc = 0;
+  const bool multi_d = dp.n_dist > 1;
+  for (uint32_t tile = blockIdx.x; tile < rb.n_tiles; tile += gridDim.x) {
+    const uint32_t n_seg = rb.n_seq * dp.n_dist;
+    if (threadIdx.x == 0) {
+      const uint32_t s = find_segment(rb.seg_tile_start, n_seg, tile);
+      s_seg = s;
+      const uint32_t r = s / dp.n_dist, di = s - r * dp.n_dist;
+      const uint64_t len = rb.off[r + 1] - rb.off[r];
+      const uint64_t npos = len - k + 1; // segments of reads shorter than k own zero tiles
+      const uint64_t o = dp.offset, d = dp.dist[di], t = dp.step[di];
+      unsigned long long cnt = 0;
+      if (!rb.flags[r]) {
+        // no invalid base: a[n] = o+n, b[n] = o+d+n, n < npos-o-d
+        if (npos > o + d) cnt = (npos - o - d) / t;
+      } else {
+        const uint64_t g0 = rb.off[r] - rb.base0;
+        RankView rv;
+        rv.vs = rb.vs; rv.vrank = rb.vrank; rv.wb = (g0 >> 6) + 2ull * r; rv.npos = npos;
+        rv.nwords = (npos + 63) >> 6; rv.total = rb.vrank[rv.wb + rv.nwords];
+        const uint32_t va0 = rank_of(rv, o), vb0 = rank_of(rv, o + d);
+        const uint32_t na = rv.total - va0, nb = rv.total - vb0;
+        cnt = (na < nb ? na : nb) / t;
+        s_va0 = va0; s_vb0 = vb0;
+      }
+      s_cnt = cnt;
+    }
+    __syncthreads();
+    const uint32_t s = s_seg;
+    const uint32_t r = s / dp.n_dist, di = s - r * dp.n_dist;
+    const uint64_t g0 = rb.off[r] - rb.base0;
+    const uint64_t d = dp.dist[di], t = dp.step[di];
+    const unsigned long long cnt = s_cnt;
+    const bool flagged = rb.flags[r] != 0;
+    const uint64_t j_begin = uint64_t(tile - rb.seg_tile_start[s]) * kTile;
+    RankView rv;
+    uint32_t va0 = 0, vb0 = 0;
+    if (flagged) {
+      const uint64_t len = rb.off[r + 1] - rb.off[r];
+      rv.vs = rb.vs; rv.vrank = rb.vrank; rv.wb = (g0 >> 6) + 2ull * r; rv.npos = len - k + 1;
+      rv.nwords = (rv.npos + 63) >> 6; rv.total = rb.vrank[rv.wb + rv.nwords];
+      va0 = s_va0; vb0 = s_vb0;
+    }
+    for (int q = threadIdx.x; q < kTile; q += kCtaThreads) {
+      const uint64_t j = j_begin + q;
+      if (j >= cnt) break;
+      const uint64_t n = j * t + (t - 1); // rank among valid k-mers of each stream (ref :530-543)
+      uint64_t a, b;
+      if (!flagged) { a = dp.offset + n; b = a + d; }
+      else { a = select_of(rv, va0 + uint32_t(n)); b = select_of(rv, vb0 + uint32_t(n)); }
+      ++n_cand;
+      uint64_t fa, ra, fb, rbv;
+      hash_kmer(rb.packed, g0 + a, k, s_tab, fa, ra);
+      if (!bloom_contains(bf, fa, ra, kseed, n_probe)) continue; // ref :554 (short-circuit &&)
+      hash_kmer(rb.packed, g0 + b, k, s_tab, fb, rbv);
+      if (!bloom_contains(bf, fb, rbv, kseed, n_probe)) continue;
+      ++n_surv;
+      uint64_t h_a, h_b; // ref :546-552
+      if (fa < rbv) { h_a = rbv; h_b = ra; } else { h_a = fa; h_b = fb; }
+      if (pair_insert(pv, h_a, h_b, make_okey(rb.first_read_idx + r, di, n), multi_d)) ++n_uniq;
+    }
+    n_probe_acc += n_probe; n_probe = 0;
+    __syncthreads();
+  }
+  n_cand = warp_sum_ull(n_cand); n_surv = warp_sum_ull(n_surv); n_uniq = warp_sum_ull(n_uniq);
+  n_probe_acc = warp_sum_ull(n_probe_acc);
+  if ((threadIdx.x & 31) == 0) {
+    if (n_cand) atomicAdd(&ctr->n_candidates, n_cand);
+    if (n_surv) atomicAdd(&ctr->n_survivors, n_surv);
+    if (n_uniq) atomicAdd(&ctr->n_unique, n_uniq);
+    if (n_probe_acc) atomicAdd(&ctr->n_bf_probes, n_probe_acc);
+  }
+}
+
+// re-insert every occupied slot of `src` into `dst` (growth) -- also used by links_pairs_import
+__global__ void pair_rehash_kernel(const PairSlot* __restrict__ src, uint64_t n_src, PairView dst, Counters* ctr, int count_unique)
+{
+  unsigned long long fresh = 0;
+  for (uint64_t i = uint64_t(blockIdx.x) * blockDim.x + threadIdx.x; i < n_src; i += uint64_t(gridDim.x) * blockDim.x) {
+    const PairSlot s = src[i];
+    if (s.a == kEmpty && s.b == kEmpty) continue;
+    if (pair_insert(dst, s.a, s.b, s.okey, true)) ++fresh;
+  }
+  if (count_unique) {
+    fresh = warp_sum_ull(fresh);
+    if ((threadIdx.x & 31) == 0 && fresh) atomicAdd(&ctr->n_unique, fresh);
+  }
+}
+
+// ------------------------------------------------------------------ stage 4: classify unique pairs
+
+// dense row key: bin_code << (2*tb) | A << tb | B with A/B = tig<<1 | rev ; tb = bits of (n_tigs<<1|1)
+__host__ __device__ __forceinline__ uint64_t pack_row_key(uint32_t bin_code, uint32_t a, uint32_t b, int tb)
+{
+  return (uint64_t(bin_code) << (2 * tb)) | (uint64_t(a) << tb) | uint64_t(b);
+}
+__host__ __device__ __forceinline__ int bin_code_of(int distance) // get_distance_bin, ref :764-770
+{
+  return distance < 0 ? 0 : distance == 10 ? 1 : distance < 500 ? 2 : distance < 5000 ? 3 : 4;
+}
+
+struct ClassifyParams {
+  const uint32_t* dist; const int32_t* min_allowed; uint32_t n_dist;
+  const uint32_t* tig_len; // [0] = 0 : the empty tig id
+  int tb;
+  uint64_t* row_keys; int32_t* row_dist; uint64_t row_cap;
+  IssueRec* issues; uint64_t issue_cap;
+};
+
+struct KInfo { uint32_t tig; uint32_t start, end; bool orient; bool multiple; };
+__device__ __forceinline__ KInfo decode_kinfo(uint64_t v, int k)
+{
+  KInfo ki;
+  if (!(v & 1ull)) { ki.tig = 0; ki.start = 0; ki.end = 0; ki.orient = false; ki.multiple = false; return ki; } // KmerInfo() ref :123-136
+  ki.tig = uint32_t(v >> 3) & 0x1FFFFFFFu; ki.start = uint32_t(v >> 32); ki.end = ki.start + k;
+  ki.orient = (v >> 2) & 1ull; ki.multiple = (v >> 1) & 1ull;
+  return ki;
+}
+
+__global__ void __launch_bounds__(kCtaThreads) classify_kernel(const PairSlot* __restrict__ pairs, uint64_t n_slots,
+                                                               TableView tv, ClassifyParams cp, int k,
+                                                               Counters* __restrict__ ctr)
+{
+  unsigned long long c_ok = 0, c_prob = 0, c_okc = 0, c_iz = 0, c_ill = 0, c_gate = 0;
+  const int lane = threadIdx.x & 31;
+  const uint64_t stride = uint64_t(gridDim.x) * blockDim.x;
+  const uint64_t n_round = (n_slots + stride - 1) / stride * stride; // keep whole warps in the loop
+  for (uint64_t i = uint64_t(blockIdx.x) * blockDim.x + threadIdx.x; i < n_round; i += stride) {
+    bool emit = false;
+    uint64_t rkey = 0; int32_t rdist = 0;
+    if (i < n_slots) {
+      const ulonglong2 hk = __ldg(reinterpret_cast<const ulonglong2*>(pairs + i));
+      if (!(hk.x == kEmpty && hk.y == kEmpty)) {
+        const uint32_t di = cp.n_dist > 1 ? okey_d_idx(pairs[i].okey) : 0;
+        const KInfo k1 = decode_kinfo(table_lookup(tv, hk.x), k);
+        const KInfo k2 = decode_kinfo(table_lookup(tv, hk.y), k);
+        if (k1.multiple || k2.multiple) { ++c_gate; } // ref :827-830
+        else {
+          const int64_t insert_size = cp.dist[di];
+          const int min_allowed = cp.min_allowed[di]; // ref :838, evaluated on the host in float
+          if (k1.tig != k2.tig) { // ref :851-899
+            const uint32_t l1 = cp.tig_len[k1.tig], l2 = cp.tig_len[k2.tig];
+            // get_distance (ref :772-779) in 32-bit wrap-around arithmetic == its uint64->int truncations
+            uint32_t span; uint32_t oe;
+            if (!k1.orient) {
+              if (!k2.orient) { span = (l1 - k1.start) + k2.start; oe = 0; }
+              else { span = (l1 - k1.start) + (l2 - k2.end); oe = 1; }
+            } else {
+              if (!k2.orient) { span = (l1 - (l1 - k1.end)) + k2.start; oe = 2; }
+              else { span = (l2 - k2.end) + k1.end; oe = 3; }
+            }
+            const int distance = int(uint32_t(insert_size) - span);
+            if (distance > min_allowed && int64_t(distance) < insert_size) {
+              ++c_ok;
+              // add_to_pair_map (ref :717-733): first row X->Y, second row flip(Y)->flip(X).
+              uint32_t A, B;
+              switch (oe) {
+              case 0: A = k1.tig << 1; B = k2.tig << 1; break;
+              case 1: A = k1.tig << 1; B = (k2.tig << 1) | 1u; break;
+              case 2: A = (k1.tig << 1) | 1u; B = k2.tig << 1; break;
+              default: A = (k1.tig << 1) | 1u; B = (k2.tig << 1) | 1u; break;
+              }
+              const uint32_t bc = bin_code_of(distance);
+              const uint64_t k_first = pack_row_key(bc, A, B, cp.tb);
+              const uint64_t k_second = pack_row_key(bc, B ^ 1u, A ^ 1u, cp.tb);
+              rkey = k_first < k_second ? k_first : k_second; // the two rows always travel together
+              rdist = distance;
+              emit = true;
+            } else { ++c_prob; }
+          } else { // same contig, ref :900-954
+            if (k1.orient == k2.orient) {
+              const unsigned low_iz = unsigned(insert_size + min_allowed), up_iz = unsigned(insert_size - min_allowed);
+              const uint64_t pet = k1.start > k2.start ? uint64_t(k1.start - k2.start) : uint64_t(k2.start - k1.start);
+              if (pet >= low_iz && pet <= up_iz) { ++c_okc; }
+              else {
+                ++c_iz;
+                const unsigned long long slot = atomicAdd(&ctr->n_issues, 1ull);
+                if (slot < cp.issue_cap) {
+                  IssueRec is;
+                  is.tig = k1.tig; is.o1 = k1.orient; is.o2 = k2.orient; is.pad_[0] = is.pad_[1] = 0;
+                  is.tig_len = cp.tig_len[k1.tig];
+                  is.s1 = k1.start; is.e1 = k1.end; is.s2 = k2.start; is.e2 = k2.end;
+                  is.pet_size = pet; is.insert_size = insert_size;
+                  cp.issues[slot] = is;
+                }
+              }
+            } else { ++c_ill; }
+          }
+        }
+      }
+    }
+    const uint32_t em = __ballot_sync(0xffffffffu, emit);
+    if (em) {
+      unsigned long long base = 0;
+      if (lane == 0) base = atomicAdd(&ctr->n_rows, (unsigned long long)__popc(em));
+      base = __shfl_sync(0xffffffffu, base, 0);
+      if (emit) {
+        const uint64_t dst = base + __popc(em & ((1u << lane) - 1u));
+        if (dst < cp.row_cap) { cp.row_keys[dst] = rkey; cp.row_dist[dst] = rdist; }
+      }
+    }
+  }
+  c_ok = warp_sum_ull(c_ok); c_prob = warp_sum_ull(c_prob); c_okc = warp_sum_ull(c_okc);
+  c_iz = warp_sum_ull(c_iz); c_ill = warp_sum_ull(c_ill); c_gate = warp_sum_ull(c_gate);
+  if (lane == 0) {
+    if (c_ok) atomicAdd(&ctr->ct_ok_pairs, c_ok);
+    if (c_prob) atomicAdd(&ctr->ct_problem_pairs, c_prob);
+    if (c_okc) atomicAdd(&ctr->ct_ok_contig, c_okc);
+    if (c_iz) atomicAdd(&ctr->ct_iz_issues, c_iz);
+    if (c_ill) atomicAdd(&ctr->ct_illogical, c_ill);
+    if (c_gate) atomicAdd(&ctr->ct_gate_fail, c_gate);
+  }
+}
+
+// ------------------------------------------------------------------ inspection helpers
+
+__global__ void kmer_hashes_kernel(const uint32_t* __restrict__ packed, const uint32_t* __restrict__ inv, uint64_t npos,
+                                   int k, const ulonglong2* __restrict__ g_tab, uint64_t* __restrict__ fwd,
+                                   uint64_t* __restrict__ rev, uint8_t* __restrict__ valid)
+{
+  extern __shared__ ulonglong2 s_tab[];
+  for (int i = threadIdx.x; i < k * 4; i += blockDim.x) s_tab[i] = g_tab[i];
+  __syncthreads();
+  for (uint64_t p = uint64_t(blockIdx.x) * blockDim.x + threadIdx.x; p < npos; p += uint64_t(gridDim.x) * blockDim.x) {
+    const bool ok = window_valid(inv, p, k);
+    uint64_t f = 0, r = 0;
+    if (ok) hash_kmer(packed, p, k, s_tab, f, r);
+    fwd[p] = f; rev[p] = r; valid[p] = ok;
+  }
+}
+
+__global__ void bf_contains_kernel(BloomView bf, uint64_t kseed, const uint64_t* __restrict__ fwd,
+                                   const uint64_t* __restrict__ rev, uint64_t n, uint8_t* __restrict__ out)
+{
+  const uint64_t i = uint64_t(blockIdx.x) * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  uint32_t probes = 0;
+  out[i] = bloom_contains(bf, fwd[i], rev[i], kseed, probes);
+}
+
+// compact occupied pair slots: out[] = {a, b, okey}
+__global__ void pair_compact_kernel(const PairSlot* __restrict__ pairs, uint64_t n_slots, uint64_t* __restrict__ out3,
+                                    uint64_t cap, unsigned long long* __restrict__ count)
+{
+  for (uint64_t i = uint64_t(blockIdx.x) * blockDim.x + threadIdx.x; i < n_slots; i += uint64_t(gridDim.x) * blockDim.x) {
+    const PairSlot s = pairs[i];
+    if (s.a == kEmpty && s.b == kEmpty) continue;
+    const unsigned long long dst = atomicAdd(count, 1ull);
+    if (dst < cap) { out3[dst * 3] = s.a; out3[dst * 3 + 1] = s.b; out3[dst * 3 + 2] = s.okey; }
+  }
+}
+
+} // namespace links

@@ -1,0 +1,951 @@
+// links_b200/csrc/links_gpu.cu -- C-ABI implementation (include/links_gpu.h) over the sm_100a kernels.
+//
+// Host-side flow per context (one CUDA device, two streams):
+//   contigs_push : H2D ascii -> pack -> [bf_build] ; packed contigs stay resident for the table build
+//   reads_push   : chunked; per chunk  H2D (copy stream) -> pack -> rank_build -> extract (compute stream)
+//                  with two chunk slots so chunk i+1's copy overlaps chunk i's kernels
+//   finalize     : table_build over resident contigs -> classify over the pair set -> radix sort
+//                  -> reduce-by-key -> D2H rows -> mirror expansion + final ordering on the host
+// There is no CPU implementation of any of these stages in this library.
+#include "../../include/links_gpu.h"
+#include "kernels.cuh"
+
+#include <algorithm>
+#include <cmath>
+#include <cstdarg>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <string>
+#include <vector>
+
+using namespace links;
+
+namespace {
+
+thread_local std::string g_create_error;
+
+struct DevBuf {
+  void* p = nullptr;
+  size_t cap = 0;
+  cudaError_t ensure(size_t bytes)
+  {
+    if (bytes <= cap) return cudaSuccess;
+    if (p) cudaFree(p);
+    p = nullptr; cap = 0;
+    size_t want = bytes + bytes / 8 + 256;
+    cudaError_t e = cudaMalloc(&p, want);
+    if (e != cudaSuccess) { cudaGetLastError(); want = bytes; e = cudaMalloc(&p, want); }
+    if (e == cudaSuccess) cap = want; else p = nullptr;
+    return e;
+  }
+  void release() { if (p) cudaFree(p); p = nullptr; cap = 0; }
+  template <class T> T* as() const { return reinterpret_cast<T*>(p); }
+};
+
+struct SeqBatchDev { // device-resident packed sequences of one push/chunk
+  DevBuf packed, inv, off, segs, flags, vs, vrank;
+  uint64_t n_bases = 0, base0 = 0;
+  uint32_t n_seq = 0, n_tiles = 0, first_id = 0;
+  uint64_t first_read_idx = 0;
+  void release() { packed.release(); inv.release(); off.release(); segs.release(); flags.release(); vs.release(); vrank.release(); }
+};
+
+enum Family { F_H2D, F_PACK, F_BF, F_TABLE, F_EXTRACT, F_CLASSIFY, F_SORT, F_D2H, F_COUNT };
+
+struct TimedSpan { int fam; cudaEvent_t a, b; };
+
+} // namespace
+
+struct links_ctx {
+  int device = 0;
+  int sm_count = 148;
+  links_params prm{};
+  std::vector<uint32_t> dist;
+  std::vector<uint32_t> step;
+  std::vector<int32_t> min_allowed;
+  std::string err;
+  cudaStream_t s_compute = nullptr, s_copy = nullptr;
+
+  // ntHash table + distance params on device
+  DevBuf d_tab, d_dist, d_step, d_minallowed;
+  uint64_t kseed = 0;
+
+  // Bloom filter
+  DevBuf d_bloom;
+  uint64_t bf_bytes = 0;
+  uint32_t hash_num = 0;
+  bool bf_ready = false, bf_insert = false;
+
+  // contigs (resident)
+  std::vector<SeqBatchDev*> contig_batches;
+  std::vector<uint32_t> tig_len; // [0] = 0
+  uint64_t contig_positions = 0;
+  uint32_t n_tigs_seen = 0;
+
+  // read chunk slots
+  static constexpr int kSlots = 2;
+  SeqBatchDev slot[kSlots];
+  DevBuf slot_ascii[kSlots];
+  cudaEvent_t ev_copied[kSlots]{}, ev_done[kSlots]{};
+  bool slot_used[kSlots] = {false, false};
+  int next_slot = 0;
+  DevBuf contig_ascii;
+
+  // pair set
+  DevBuf d_pairs;
+  uint64_t pair_cap = 0;
+  uint64_t pair_bound = 0; // host upper bound on occupied slots
+  uint64_t cand_total = 0;
+
+  // counters
+  DevBuf d_ctr;
+
+  // contig table
+  DevBuf d_table;
+  uint64_t table_cap = 0;
+
+  // timing
+  std::vector<TimedSpan> spans;
+  std::vector<cudaEvent_t> ev_pool;
+  float fam_ms[F_COUNT] = {0};
+  uint64_t launches = 0;
+  bool timing = true;
+  bool finalized = false;
+};
+
+namespace {
+
+int fail(links_ctx* c, int code, const char* fmt, ...)
+{
+  char buf[1024];
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(buf, sizeof buf, fmt, ap);
+  va_end(ap);
+  if (c) c->err = buf; else g_create_error = buf;
+  return code;
+}
+
+#define CU(c, call)                                                                                   \
+  do {                                                                                                \
+    cudaError_t e__ = (call);                                                                         \
+    if (e__ != cudaSuccess) {                                                                         \
+      cudaGetLastError();                                                                             \
+      return fail((c), e__ == cudaErrorMemoryAllocation ? LINKS_E_NOMEM : LINKS_E_CUDA, "%s: %s (%s:%d)", #call, \
+                  cudaGetErrorString(e__), __FILE__, __LINE__);                                       \
+    }                                                                                                 \
+  } while (0)
+
+cudaEvent_t get_event(links_ctx* c)
+{
+  if (!c->ev_pool.empty()) { cudaEvent_t e = c->ev_pool.back(); c->ev_pool.pop_back(); return e; }
+  cudaEvent_t e;
+  cudaEventCreate(&e);
+  return e;
+}
+
+struct Span {
+  links_ctx* c; int fam; cudaStream_t s; cudaEvent_t a = nullptr;
+  Span(links_ctx* c_, int fam_, cudaStream_t s_) : c(c_), fam(fam_), s(s_)
+  {
+    if (c->timing) { a = get_event(c); cudaEventRecord(a, s); }
+  }
+  ~Span()
+  {
+    if (c->timing) { cudaEvent_t b = get_event(c); cudaEventRecord(b, s); c->spans.push_back({fam, a, b}); }
+  }
+};
+
+void resolve_spans(links_ctx* c)
+{
+  for (auto& sp : c->spans) {
+    float ms = 0;
+    if (cudaEventSynchronize(sp.b) == cudaSuccess && cudaEventElapsedTime(&ms, sp.a, sp.b) == cudaSuccess) c->fam_ms[sp.fam] += ms;
+    else cudaGetLastError();
+    c->ev_pool.push_back(sp.a);
+    c->ev_pool.push_back(sp.b);
+  }
+  c->spans.clear();
+}
+
+int grid_for(links_ctx* c, uint64_t work_items, int per_cta, int ctas_per_sm)
+{
+  uint64_t need = (work_items + per_cta - 1) / per_cta;
+  uint64_t cap = uint64_t(c->sm_count) * ctas_per_sm;
+  if (need < 1) need = 1;
+  return int(std::min(need, cap));
+}
+
+int log2_ceil(uint64_t v)
+{
+  int b = 0;
+  while ((1ull << b) < v) ++b;
+  return b;
+}
+
+TableView table_view(links_ctx* c)
+{
+  TableView tv;
+  tv.slots = c->d_table.as<TableSlot>();
+  tv.mask = c->table_cap ? c->table_cap - 1 : 0;
+  tv.shift = 64 - log2_ceil(c->table_cap ? c->table_cap : 2);
+  return tv;
+}
+PairView pair_view(PairSlot* p, uint64_t cap)
+{
+  PairView pv;
+  pv.slots = p; pv.mask = cap - 1; pv.shift = 64 - log2_ceil(cap);
+  return pv;
+}
+BloomView bloom_view(links_ctx* c)
+{
+  BloomView bf;
+  bf.words = c->d_bloom.as<uint32_t>();
+  bf.array_bits = c->bf_bytes * 8;
+  bf.magic = bf.array_bits ? uint64_t((((unsigned __int128)1) << 64) / bf.array_bits) : 0;
+  bf.hash_num = c->hash_num;
+  return bf;
+}
+
+// exclusive scan of n u32 (in place allowed); total written to *d_total (device)
+int device_scan(links_ctx* c, cudaStream_t s, uint32_t* d_in, uint64_t n, uint32_t* d_out, DevBuf& tmp, uint32_t* d_total)
+{
+  if (n <= uint64_t(kScanTile)) {
+    scan_small_kernel<<<1, kScanThreads, 0, s>>>(d_in, uint32_t(n), d_out, d_total);
+    c->launches++;
+    return LINKS_OK;
+  }
+  // level sizes
+  std::vector<uint64_t> lv;
+  for (uint64_t m = n; m > uint64_t(kScanTile);) { m = (m + kScanTile - 1) / kScanTile; lv.push_back(m); }
+  uint64_t tot = 0;
+  for (auto m : lv) tot += m + 8;
+  CU(c, tmp.ensure(tot * sizeof(uint32_t)));
+  std::vector<uint32_t*> ptr;
+  { uint32_t* p = tmp.as<uint32_t>(); for (auto m : lv) { ptr.push_back(p); p += m + 8; } }
+  // up-sweep
+  const uint32_t* src = d_in; uint64_t m = n;
+  for (size_t l = 0; l < lv.size(); ++l) {
+    scan_sums_kernel<<<unsigned(lv[l]), kScanThreads, 0, s>>>(src, m, ptr[l]);
+    c->launches++;
+    src = ptr[l]; m = lv[l];
+  }
+  scan_small_kernel<<<1, kScanThreads, 0, s>>>(ptr.back(), uint32_t(lv.back()), ptr.back(), d_total);
+  c->launches++;
+  // down-sweep
+  for (size_t l = lv.size(); l-- > 0;) {
+    uint32_t* data = l == 0 ? d_in : ptr[l - 1];
+    uint32_t* out = l == 0 ? d_out : ptr[l - 1];
+    const uint64_t cnt = l == 0 ? n : lv[l - 1];
+    scan_apply_kernel<<<unsigned(lv[l]), kScanThreads, 0, s>>>(data, cnt, ptr[l], out);
+    c->launches++;
+  }
+  return LINKS_OK;
+}
+
+// upload + pack one batch of sequences into `b` (device-resident).  tiles_per_seg computed by caller.
+int upload_and_pack(links_ctx* c, SeqBatchDev& b, DevBuf& ascii, const char* seq, const uint64_t* off, uint32_t n,
+                    const std::vector<uint32_t>& seg_tile_start, bool want_rank, cudaStream_t s_copy, cudaStream_t s_comp,
+                    cudaEvent_t ev_copied)
+{
+  const uint64_t base0 = off[0], n_bases = off[n] - off[0];
+  b.n_bases = n_bases; b.base0 = base0; b.n_seq = n;
+  b.n_tiles = seg_tile_start.back();
+  CU(c, ascii.ensure(((n_bases + 63) & ~63ull) + 64));
+  CU(c, b.packed.ensure(((n_bases + 15) / 16 + 8) * 4));
+  CU(c, b.inv.ensure(((n_bases + 31) / 32 + 8) * 4));
+  CU(c, b.off.ensure((uint64_t(n) + 1) * 8));
+  CU(c, b.segs.ensure(seg_tile_start.size() * 4));
+  CU(c, b.flags.ensure((uint64_t(n) + 1) * 4));
+  if (want_rank) {
+    const uint64_t nw = (n_bases >> 6) + 2ull * n + 4;
+    CU(c, b.vs.ensure(nw * 8));
+    CU(c, b.vrank.ensure(nw * 4));
+  }
+  {
+    Span sp(c, F_H2D, s_copy);
+    if (n_bases) CU(c, cudaMemcpyAsync(ascii.p, seq + base0, n_bases, cudaMemcpyHostToDevice, s_copy));
+    CU(c, cudaMemcpyAsync(b.off.p, off, (uint64_t(n) + 1) * 8, cudaMemcpyHostToDevice, s_copy));
+    CU(c, cudaMemcpyAsync(b.segs.p, seg_tile_start.data(), seg_tile_start.size() * 4, cudaMemcpyHostToDevice, s_copy));
+  }
+  CU(c, cudaEventRecord(ev_copied, s_copy));
+  CU(c, cudaStreamWaitEvent(s_comp, ev_copied, 0));
+  {
+    Span sp(c, F_PACK, s_comp);
+    CU(c, cudaMemsetAsync(b.flags.p, 0, (uint64_t(n) + 1) * 4, s_comp));
+    // zero the padding words the k-mer window loads may touch
+    CU(c, cudaMemsetAsync(b.packed.as<uint32_t>() + (n_bases + 15) / 16, 0, 8 * 4, s_comp));
+    CU(c, cudaMemsetAsync(b.inv.as<uint32_t>() + (n_bases + 31) / 32, 0xFF, 8 * 4, s_comp));
+    if (n_bases) {
+      const uint64_t threads = (n_bases + 31) / 32;
+      pack_kernel<<<unsigned((threads + kCtaThreads - 1) / kCtaThreads), kCtaThreads, 0, s_comp>>>(
+        ascii.as<uint8_t>(), n_bases, b.packed.as<uint32_t>(), b.inv.as<uint32_t>(), b.off.as<uint64_t>(), n, base0,
+        b.flags.as<uint32_t>());
+      c->launches++;
+      if (want_rank) {
+        rank_build_kernel<<<n, kCtaThreads, 0, s_comp>>>(b.inv.as<uint32_t>(), b.off.as<uint64_t>(), base0,
+                                                         b.flags.as<uint32_t>(), int(c->prm.k),
+                                                         b.vs.as<unsigned long long>(), b.vrank.as<uint32_t>());
+        c->launches++;
+      }
+    }
+  }
+  CU(c, cudaGetLastError());
+  return LINKS_OK;
+}
+
+int ensure_pair_capacity(links_ctx* c, uint64_t incoming)
+{
+  // Invariant kept: occupied + in-flight inserts <= 0.7 * cap, so probing always terminates.
+  auto fits = [&](uint64_t bound, uint64_t cap) { return cap && (bound + incoming) * 10 <= cap * 7; };
+  if (fits(c->pair_bound, c->pair_cap)) { c->pair_bound += incoming; return LINKS_OK; }
+  // tighten the bound with the real count
+  CU(c, cudaStreamSynchronize(c->s_compute));
+  Counters h;
+  CU(c, cudaMemcpy(&h, c->d_ctr.p, sizeof h, cudaMemcpyDeviceToHost));
+  c->pair_bound = h.n_unique;
+  if (fits(c->pair_bound, c->pair_cap)) { c->pair_bound += incoming; return LINKS_OK; }
+  uint64_t want = uint64_t(double(c->pair_bound + incoming) / 0.5) + 1024;
+  uint64_t cap = 1ull << log2_ceil(std::max<uint64_t>(want, 1ull << 16));
+  DevBuf nb;
+  CU(c, nb.ensure(cap * sizeof(PairSlot)));
+  CU(c, cudaMemsetAsync(nb.p, 0xFF, cap * sizeof(PairSlot), c->s_compute));
+  if (c->pair_cap && c->pair_bound) {
+    Span sp(c, F_EXTRACT, c->s_compute);
+    pair_rehash_kernel<<<grid_for(c, c->pair_cap, 256, 8), 256, 0, c->s_compute>>>(
+      c->d_pairs.as<PairSlot>(), c->pair_cap, pair_view(nb.as<PairSlot>(), cap), c->d_ctr.as<Counters>(), 0);
+    c->launches++;
+  }
+  CU(c, cudaStreamSynchronize(c->s_compute));
+  c->d_pairs.release();
+  c->d_pairs = nb;
+  c->pair_cap = cap;
+  c->pair_bound += incoming;
+  return LINKS_OK;
+}
+
+} // namespace
+
+// ====================================================================== C ABI
+
+extern "C" {
+
+const char* links_last_error(const links_ctx* ctx) { return ctx ? ctx->err.c_str() : g_create_error.c_str(); }
+
+void* links_host_alloc(size_t bytes)
+{
+  void* p = nullptr;
+  if (cudaHostAlloc(&p, bytes ? bytes : 1, cudaHostAllocDefault) != cudaSuccess) { cudaGetLastError(); return nullptr; }
+  return p;
+}
+void links_host_free(void* p) { if (p) cudaFreeHost(p); }
+
+int links_bf_size(uint64_t file_bytes, float fpr, uint64_t* m_bits, uint64_t* bytes, uint32_t* hash_num)
+{
+  if (!file_bytes) return LINKS_E_INVAL;
+  // LINKS::make_bf, reference src/LINKS.hpp:297-302 -- same expression shapes, double libm.
+  uint64_t m = uint64_t(std::ceil((-1 * double(file_bytes) * std::log(double(fpr))) / (std::log(2.0) * std::log(2.0))));
+  m = (uint64_t(m / 8) + 1) * 8;
+  const unsigned hash_fct = unsigned(std::floor((double(m) / double(file_bytes)) * std::log(2.0)));
+  uint64_t b = m / 8;
+  b = uint64_t(std::ceil(double(b) / 8.0) * 8.0); // BloomFilter ctor, btllib bloom_filter.hpp:617-621
+  if (m_bits) *m_bits = m;
+  if (bytes) *bytes = b;
+  if (hash_num) *hash_num = hash_fct;
+  return LINKS_OK;
+}
+
+size_t links_bf_header(char* dst, size_t cap, uint32_t k, uint32_t hash_num, uint64_t bytes)
+{
+  // KmerBloomFilter::save -> BloomFilter::save, btllib bloom_filter.hpp:766-783,866-888 (cpptoml table dump)
+  int n = snprintf(dst, cap,
+                   "[BTLKmerBloomFilter_v6]\n\tk = %u\n\thash_fn = \"ntHash_v1\"\n\thash_num = %u\n\tbytes = %llu\n"
+                   "[HeaderEnd]\n\n  <binary data>\n",
+                   k, hash_num, (unsigned long long)bytes);
+  if (n < 0 || size_t(n) + 49 > cap) return 0;
+  for (int i = 0; i < 48; ++i) dst[n++] = '\n';
+  dst[n] = 0;
+  return size_t(n);
+}
+
+int links_create(links_ctx** out, const links_params* p)
+{
+  if (!out || !p) return fail(nullptr, LINKS_E_INVAL, "links_create: null argument");
+  *out = nullptr;
+  if (p->k == 0 || p->k > LINKS_MAX_K) return fail(nullptr, LINKS_E_LIMIT, "links_create: k=%u outside 1..%u", p->k, LINKS_MAX_K);
+  if (p->n_dist == 0 || p->n_dist > LINKS_MAX_DIST || !p->dist || !p->step)
+    return fail(nullptr, LINKS_E_LIMIT, "links_create: need 1..%u distances with matching steps", LINKS_MAX_DIST);
+  for (uint32_t i = 0; i < p->n_dist; ++i)
+    if (p->step[i] == 0) return fail(nullptr, LINKS_E_INVAL, "links_create: step size 0");
+  int n_dev = 0;
+  if (cudaGetDeviceCount(&n_dev) != cudaSuccess || n_dev == 0) {
+    cudaGetLastError();
+    return fail(nullptr, LINKS_E_NODEVICE, "links_create: no CUDA device (this library has no CPU path)");
+  }
+  if (p->device < 0 || p->device >= n_dev) return fail(nullptr, LINKS_E_INVAL, "links_create: device %d of %d", p->device, n_dev);
+  links_ctx* c = new (std::nothrow) links_ctx();
+  if (!c) return fail(nullptr, LINKS_E_NOMEM, "links_create: out of host memory");
+  c->device = p->device;
+  c->prm = *p;
+  c->dist.assign(p->dist, p->dist + p->n_dist);
+  c->step.assign(p->step, p->step + p->n_dist);
+  c->prm.dist = c->dist.data();
+  c->prm.step = nullptr;
+  c->min_allowed.resize(p->n_dist);
+  for (uint32_t i = 0; i < p->n_dist; ++i) {
+    const int64_t insert_size = c->dist[i];
+    c->min_allowed[i] = int(-1 * (p->insert_stdev * insert_size)); // reference src/LINKS.hpp:838 (float product, truncation)
+  }
+  c->kseed = uint64_t(p->k) * kMultiSeed;
+  c->tig_len.assign(1, 0);
+#define CUC(call)                                                                                          \
+  do {                                                                                                     \
+    cudaError_t e__ = (call);                                                                              \
+    if (e__ != cudaSuccess) {                                                                              \
+      cudaGetLastError();                                                                                  \
+      fail(nullptr, LINKS_E_CUDA, "links_create: %s: %s", #call, cudaGetErrorString(e__));                 \
+      links_destroy(c);                                                                                    \
+      return LINKS_E_CUDA;                                                                                 \
+    }                                                                                                      \
+  } while (0)
+  CUC(cudaSetDevice(c->device));
+  cudaDeviceProp prop;
+  CUC(cudaGetDeviceProperties(&prop, c->device));
+  c->sm_count = prop.multiProcessorCount;
+  CUC(cudaStreamCreateWithFlags(&c->s_compute, cudaStreamNonBlocking));
+  CUC(cudaStreamCreateWithFlags(&c->s_copy, cudaStreamNonBlocking));
+  for (int i = 0; i < links_ctx::kSlots; ++i) {
+    CUC(cudaEventCreateWithFlags(&c->ev_copied[i], cudaEventDisableTiming));
+    CUC(cudaEventCreateWithFlags(&c->ev_done[i], cudaEventDisableTiming));
+  }
+  {
+    std::vector<ulonglong2> tab(size_t(p->k) * 4);
+    build_nthash_table(p->k, tab.data());
+    CUC(c->d_tab.ensure(tab.size() * sizeof(ulonglong2)));
+    CUC(cudaMemcpy(c->d_tab.p, tab.data(), tab.size() * sizeof(ulonglong2), cudaMemcpyHostToDevice));
+    CUC(c->d_dist.ensure(p->n_dist * 4));
+    CUC(cudaMemcpy(c->d_dist.p, c->dist.data(), p->n_dist * 4, cudaMemcpyHostToDevice));
+    CUC(c->d_step.ensure(p->n_dist * 4));
+    CUC(cudaMemcpy(c->d_step.p, c->step.data(), p->n_dist * 4, cudaMemcpyHostToDevice));
+    CUC(c->d_minallowed.ensure(p->n_dist * 4));
+    CUC(cudaMemcpy(c->d_minallowed.p, c->min_allowed.data(), p->n_dist * 4, cudaMemcpyHostToDevice));
+    CUC(c->d_ctr.ensure(sizeof(Counters)));
+    CUC(cudaMemset(c->d_ctr.p, 0, sizeof(Counters)));
+  }
+#undef CUC
+  *out = c;
+  return LINKS_OK;
+}
+
+void links_destroy(links_ctx* c)
+{
+  if (!c) return;
+  cudaSetDevice(c->device);
+  cudaDeviceSynchronize();
+  resolve_spans(c);
+  for (auto e : c->ev_pool) cudaEventDestroy(e);
+  for (auto* b : c->contig_batches) { b->release(); delete b; }
+  for (int i = 0; i < links_ctx::kSlots; ++i) {
+    c->slot[i].release(); c->slot_ascii[i].release();
+    if (c->ev_copied[i]) cudaEventDestroy(c->ev_copied[i]);
+    if (c->ev_done[i]) cudaEventDestroy(c->ev_done[i]);
+  }
+  c->contig_ascii.release();
+  c->d_tab.release(); c->d_dist.release(); c->d_step.release(); c->d_minallowed.release();
+  c->d_bloom.release(); c->d_pairs.release(); c->d_ctr.release(); c->d_table.release();
+  if (c->s_compute) cudaStreamDestroy(c->s_compute);
+  if (c->s_copy) cudaStreamDestroy(c->s_copy);
+  cudaGetLastError();
+  delete c;
+}
+
+int links_sync(links_ctx* c)
+{
+  if (!c) return LINKS_E_INVAL;
+  CU(c, cudaSetDevice(c->device));
+  CU(c, cudaStreamSynchronize(c->s_copy));
+  CU(c, cudaStreamSynchronize(c->s_compute));
+  return LINKS_OK;
+}
+
+int links_bf_alloc(links_ctx* c, uint64_t bytes, uint32_t hash_num)
+{
+  if (!c) return LINKS_E_INVAL;
+  if (bytes == 0 || (bytes & 7) || hash_num == 0 || hash_num > LINKS_MAX_HASH_NUM)
+    return fail(c, LINKS_E_INVAL, "links_bf_alloc: bytes must be a positive multiple of 8 and hash_num in 1..%u", LINKS_MAX_HASH_NUM);
+  CU(c, cudaSetDevice(c->device));
+  CU(c, c->d_bloom.ensure(bytes));
+  CU(c, cudaMemsetAsync(c->d_bloom.p, 0, bytes, c->s_compute));
+  c->bf_bytes = bytes; c->hash_num = hash_num; c->bf_ready = true; c->bf_insert = true;
+  return LINKS_OK;
+}
+
+int links_bf_load(links_ctx* c, const uint8_t* bits, uint64_t bytes, uint32_t hash_num)
+{
+  if (!c || !bits) return LINKS_E_INVAL;
+  if (bytes == 0 || (bytes & 3) || hash_num == 0 || hash_num > LINKS_MAX_HASH_NUM)
+    return fail(c, LINKS_E_INVAL, "links_bf_load: bytes must be a positive multiple of 4 and hash_num in 1..%u", LINKS_MAX_HASH_NUM);
+  CU(c, cudaSetDevice(c->device));
+  CU(c, c->d_bloom.ensure(bytes));
+  CU(c, cudaMemcpyAsync(c->d_bloom.p, bits, bytes, cudaMemcpyHostToDevice, c->s_compute));
+  CU(c, cudaStreamSynchronize(c->s_compute));
+  c->bf_bytes = bytes; c->hash_num = hash_num; c->bf_ready = true; c->bf_insert = false;
+  return LINKS_OK;
+}
+
+int links_bf_download(links_ctx* c, uint8_t* dst)
+{
+  if (!c || !dst) return LINKS_E_INVAL;
+  if (!c->bf_ready) return fail(c, LINKS_E_INVAL, "links_bf_download: no Bloom filter");
+  CU(c, cudaSetDevice(c->device));
+  CU(c, cudaMemcpyAsync(dst, c->d_bloom.p, c->bf_bytes, cudaMemcpyDeviceToHost, c->s_compute));
+  CU(c, cudaStreamSynchronize(c->s_compute));
+  return LINKS_OK;
+}
+
+int links_contigs_push(links_ctx* c, const char* seq, const uint64_t* off, uint32_t n, uint32_t first_tig_id)
+{
+  if (!c || !off || (!seq && n && off[n] != off[0])) return LINKS_E_INVAL;
+  if (!c->bf_ready) return fail(c, LINKS_E_INVAL, "links_contigs_push: call links_bf_alloc or links_bf_load first");
+  if (first_tig_id == 0) return fail(c, LINKS_E_INVAL, "links_contigs_push: contig ids are 1-based");
+  if (n == 0) return LINKS_OK;
+  if (uint64_t(first_tig_id) + n - 1 > LINKS_MAX_TIGS) return fail(c, LINKS_E_LIMIT, "links_contigs_push: more than %u contigs", LINKS_MAX_TIGS);
+  CU(c, cudaSetDevice(c->device));
+  const uint32_t k = c->prm.k;
+  std::vector<uint32_t> segs(size_t(n) + 1);
+  uint64_t tiles = 0, positions = 0;
+  if (c->tig_len.size() < size_t(first_tig_id) + n) c->tig_len.resize(size_t(first_tig_id) + n, 0);
+  for (uint32_t i = 0; i < n; ++i) {
+    if (off[i + 1] < off[i]) return fail(c, LINKS_E_INVAL, "links_contigs_push: offsets not monotone");
+    const uint64_t len = off[i + 1] - off[i];
+    if (len >= (1ull << 32)) return fail(c, LINKS_E_LIMIT, "links_contigs_push: contig longer than 2^32-1");
+    segs[i] = uint32_t(tiles);
+    if (len >= k) {
+      c->tig_len[first_tig_id + i] = uint32_t(len); // reference src/LINKS.hpp:655-658
+      tiles += (len - k + 1 + kTile - 1) / kTile;
+      positions += len - k + 1;
+    }
+    if (tiles >= (1ull << 31)) return fail(c, LINKS_E_LIMIT, "links_contigs_push: batch too large, push fewer contigs per call");
+  }
+  segs[n] = uint32_t(tiles);
+  SeqBatchDev* b = new (std::nothrow) SeqBatchDev();
+  if (!b) return fail(c, LINKS_E_NOMEM, "links_contigs_push: out of host memory");
+  b->first_id = first_tig_id;
+  cudaEvent_t ev = c->ev_copied[0];
+  // the single contig staging buffer is reused: wait until the previous pack consumed it
+  CU(c, cudaStreamSynchronize(c->s_compute));
+  int rc = upload_and_pack(c, *b, c->contig_ascii, seq, off, n, segs, false, c->s_copy, c->s_compute, ev);
+  if (rc) { b->release(); delete b; return rc; }
+  c->contig_batches.push_back(b);
+  c->contig_positions += positions;
+  c->n_tigs_seen = std::max(c->n_tigs_seen, first_tig_id + n - 1);
+  if (c->bf_insert && b->n_tiles) {
+    Span sp(c, F_BF, c->s_compute);
+    ContigBatch cb{b->packed.as<uint32_t>(), b->inv.as<uint32_t>(), b->off.as<uint64_t>(), b->base0,
+                   b->segs.as<uint32_t>(), b->n_seq, b->n_tiles, b->first_id};
+    contig_kernel<0><<<grid_for(c, b->n_tiles, 1, 8), kCtaThreads, k * 4 * sizeof(ulonglong2), c->s_compute>>>(
+      cb, int(k), c->kseed, c->d_tab.as<ulonglong2>(), bloom_view(c), TableView{nullptr, 0, 0}, c->d_ctr.as<Counters>());
+    c->launches++;
+    CU(c, cudaGetLastError());
+  }
+  CU(c, cudaStreamSynchronize(c->s_copy)); // host buffers reusable
+  return LINKS_OK;
+}
+
+static int push_read_chunk(links_ctx* c, const char* seq, const uint64_t* off, uint32_t n, uint64_t first_read_idx,
+                           const std::vector<uint32_t>& segs, uint64_t cand)
+{
+  const int si = c->next_slot;
+  c->next_slot = (si + 1) % links_ctx::kSlots;
+  if (c->slot_used[si]) {
+    // the slot's previous chunk must have been consumed by its kernels before we overwrite it
+    CU(c, cudaEventSynchronize(c->ev_done[si]));
+  }
+  int rc = ensure_pair_capacity(c, cand);
+  if (rc) return rc;
+  SeqBatchDev& b = c->slot[si];
+  b.first_read_idx = first_read_idx;
+  rc = upload_and_pack(c, b, c->slot_ascii[si], seq, off, n, segs, true, c->s_copy, c->s_compute, c->ev_copied[si]);
+  if (rc) return rc;
+  if (b.n_tiles) {
+    Span sp(c, F_EXTRACT, c->s_compute);
+    ReadBatch rb{b.packed.as<uint32_t>(), b.inv.as<uint32_t>(), b.off.as<uint64_t>(), b.base0, b.segs.as<uint32_t>(),
+                 b.n_seq, b.n_tiles, b.flags.as<uint32_t>(), b.vs.as<unsigned long long>(), b.vrank.as<uint32_t>(),
+                 first_read_idx};
+    DistParams dp{c->d_dist.as<uint32_t>(), c->d_step.as<uint32_t>(), c->prm.n_dist, c->prm.offset};
+    extract_kernel<<<grid_for(c, b.n_tiles, 1, 8), kCtaThreads, c->prm.k * 4 * sizeof(ulonglong2), c->s_compute>>>(
+      rb, dp, int(c->prm.k), c->kseed, c->d_tab.as<ulonglong2>(), bloom_view(c), pair_view(c->d_pairs.as<PairSlot>(), c->pair_cap),
+      c->d_ctr.as<Counters>());
+    c->launches++;
+    CU(c, cudaGetLastError());
+  }
+  CU(c, cudaEventRecord(c->ev_done[si], c->s_compute));
+  c->slot_used[si] = true;
+  c->cand_total += cand;
+  return LINKS_OK;
+}
+
+int links_reads_push(links_ctx* c, const char* seq, const uint64_t* off, uint32_t n, uint64_t first_read_idx)
+{
+  if (!c || !off || (!seq && n && off[n] != off[0])) return LINKS_E_INVAL;
+  if (!c->bf_ready) return fail(c, LINKS_E_INVAL, "links_reads_push: no Bloom filter yet");
+  if (c->finalized) return fail(c, LINKS_E_INVAL, "links_reads_push: context already finalized");
+  if (n == 0) return LINKS_OK;
+  if (first_read_idx + n >= (1ull << 28)) return fail(c, LINKS_E_LIMIT, "links_reads_push: more than 2^28 reads");
+  CU(c, cudaSetDevice(c->device));
+  const uint32_t k = c->prm.k, nd = c->prm.n_dist;
+  const uint64_t o = c->prm.offset;
+  // chunk the push at record boundaries so copies overlap kernels
+  static const uint64_t kChunkBases = []() {
+    const char* e = getenv("LINKS_CHUNK_BASES");
+    return e ? strtoull(e, nullptr, 10) : (48ull << 20);
+  }();
+  const uint64_t kChunkCand = 1ull << 28;
+  uint32_t i0 = 0;
+  std::vector<uint32_t> segs;
+  while (i0 < n) {
+    segs.clear();
+    uint64_t tiles = 0, cand = 0;
+    uint32_t i = i0;
+    for (; i < n; ++i) {
+      if (off[i + 1] < off[i]) return fail(c, LINKS_E_INVAL, "links_reads_push: offsets not monotone");
+      const uint64_t len = off[i + 1] - off[i];
+      if (len >= (1ull << 28)) return fail(c, LINKS_E_LIMIT, "links_reads_push: read longer than 2^28-1");
+      if (i > i0 && (off[i + 1] - off[i0] > kChunkBases || cand > kChunkCand || uint64_t(i - i0) * nd > (1ull << 26))) break;
+      for (uint32_t di = 0; di < nd; ++di) {
+        segs.push_back(uint32_t(tiles));
+        // upper bound (exact when the read has no invalid base): reference src/LINKS.hpp:525-543
+        uint64_t cnt = 0;
+        if (len >= k) {
+          const uint64_t npos = len - k + 1, d = c->dist[di];
+          if (npos > o + d) cnt = (npos - o - d) / c->step[di];
+        }
+        tiles += (cnt + kTile - 1) / kTile;
+        cand += cnt;
+      }
+      if (tiles >= (1ull << 31)) return fail(c, LINKS_E_LIMIT, "links_reads_push: chunk too large");
+    }
+    segs.push_back(uint32_t(tiles));
+    int rc = push_read_chunk(c, seq, off + i0, i - i0, first_read_idx + i0, segs, cand);
+    if (rc) return rc;
+    i0 = i;
+  }
+  CU(c, cudaStreamSynchronize(c->s_copy)); // host buffers reusable
+  return LINKS_OK;
+}
+
+int links_get_timing(links_ctx* c, links_timing* t, int reset)
+{
+  if (!c || !t) return LINKS_E_INVAL;
+  CU(c, cudaSetDevice(c->device));
+  CU(c, cudaStreamSynchronize(c->s_copy));
+  CU(c, cudaStreamSynchronize(c->s_compute));
+  resolve_spans(c);
+  t->ms_h2d = c->fam_ms[F_H2D]; t->ms_pack = c->fam_ms[F_PACK]; t->ms_bf_build = c->fam_ms[F_BF];
+  t->ms_table_build = c->fam_ms[F_TABLE]; t->ms_extract = c->fam_ms[F_EXTRACT]; t->ms_classify = c->fam_ms[F_CLASSIFY];
+  t->ms_sort_reduce = c->fam_ms[F_SORT]; t->ms_d2h = c->fam_ms[F_D2H];
+  t->launches = c->launches;
+  if (reset) { for (auto& m : c->fam_ms) m = 0; c->launches = 0; }
+  return LINKS_OK;
+}
+
+static int build_table(links_ctx* c)
+{
+  const uint32_t k = c->prm.k;
+  const uint64_t entries = c->contig_positions * 2;
+  const uint64_t cap = 1ull << log2_ceil(std::max<uint64_t>(entries * 2, 1ull << 10));
+  CU(c, c->d_table.ensure((cap + 1) * sizeof(TableSlot)));
+  c->table_cap = cap;
+  Span sp(c, F_TABLE, c->s_compute);
+  // keys = EMPTY (all ones), vals = 0
+  CU(c, cudaMemsetAsync(c->d_table.p, 0xFF, (cap + 1) * sizeof(TableSlot), c->s_compute));
+  CU(c, cudaMemset2DAsync(reinterpret_cast<char*>(c->d_table.p) + 8, sizeof(TableSlot), 0, 8, cap + 1, c->s_compute));
+  for (auto* b : c->contig_batches) {
+    if (!b->n_tiles) continue;
+    ContigBatch cb{b->packed.as<uint32_t>(), b->inv.as<uint32_t>(), b->off.as<uint64_t>(), b->base0,
+                   b->segs.as<uint32_t>(), b->n_seq, b->n_tiles, b->first_id};
+    contig_kernel<1><<<grid_for(c, b->n_tiles, 1, 8), kCtaThreads, k * 4 * sizeof(ulonglong2), c->s_compute>>>(
+      cb, int(k), c->kseed, c->d_tab.as<ulonglong2>(), bloom_view(c), table_view(c), c->d_ctr.as<Counters>());
+    c->launches++;
+  }
+  CU(c, cudaGetLastError());
+  return LINKS_OK;
+}
+
+int links_finalize(links_ctx* c, links_row** rows_out, uint64_t* n_rows_out, links_issue** issues_out,
+                   uint64_t* n_issues_out, links_stats* stats)
+{
+  if (!c || !rows_out || !n_rows_out) return LINKS_E_INVAL;
+  *rows_out = nullptr; *n_rows_out = 0;
+  if (issues_out) *issues_out = nullptr;
+  if (n_issues_out) *n_issues_out = 0;
+  CU(c, cudaSetDevice(c->device));
+  cudaStream_t s = c->s_compute;
+  CU(c, cudaStreamSynchronize(c->s_copy));
+  int rc = build_table(c);
+  if (rc) return rc;
+  // unique pair count sizes the row buffers
+  CU(c, cudaStreamSynchronize(s));
+  Counters h;
+  CU(c, cudaMemcpy(&h, c->d_ctr.p, sizeof h, cudaMemcpyDeviceToHost));
+  const uint64_t n_unique = h.n_unique;
+  if (n_unique >= (1ull << 32) - kSortTile) return fail(c, LINKS_E_LIMIT, "links_finalize: more than 2^32 unique pairs on one GPU");
+
+  const int tb = log2_ceil(uint64_t(c->n_tigs_seen) * 2 + 2);
+  DevBuf d_keys[2], d_vals[2], d_issues, d_tiglen, d_hist, d_scan_tmp, d_flags, d_total, d_okeys, d_olinks, d_ogaps;
+  struct Cleanup { std::vector<DevBuf*> v; ~Cleanup() { for (auto* b : v) b->release(); } } cl;
+  cl.v = {&d_keys[0], &d_keys[1], &d_vals[0], &d_vals[1], &d_issues, &d_tiglen, &d_hist, &d_scan_tmp, &d_flags, &d_total, &d_okeys, &d_olinks, &d_ogaps};
+  const uint64_t row_cap = std::max<uint64_t>(n_unique, 1);
+  uint64_t issue_cap = std::max<uint64_t>(1ull << 16, 1);
+  CU(c, d_keys[0].ensure(row_cap * 8)); CU(c, d_vals[0].ensure(row_cap * 4));
+  CU(c, d_tiglen.ensure(c->tig_len.size() * 4));
+  CU(c, cudaMemcpyAsync(d_tiglen.p, c->tig_len.data(), c->tig_len.size() * 4, cudaMemcpyHostToDevice, s));
+  CU(c, d_total.ensure(64));
+
+  for (int attempt = 0; attempt < 2; ++attempt) {
+    CU(c, d_issues.ensure(issue_cap * sizeof(IssueRec)));
+    // reset the stage-4 counters (keeps the stage-2/3 ones)
+    CU(c, cudaMemsetAsync(reinterpret_cast<char*>(c->d_ctr.p) + offsetof(Counters, ct_ok_pairs), 0,
+                          sizeof(Counters) - offsetof(Counters, ct_ok_pairs), s));
+    if (c->pair_cap) {
+      Span sp(c, F_CLASSIFY, s);
+      ClassifyParams cp{c->d_dist.as<uint32_t>(), c->d_minallowed.as<int32_t>(), c->prm.n_dist, d_tiglen.as<uint32_t>(), tb,
+                        d_keys[0].as<uint64_t>(), d_vals[0].as<int32_t>(), row_cap, d_issues.as<IssueRec>(), issue_cap};
+      classify_kernel<<<grid_for(c, c->pair_cap, kCtaThreads, 8), kCtaThreads, 0, s>>>(
+        c->d_pairs.as<PairSlot>(), c->pair_cap, table_view(c), cp, int(c->prm.k), c->d_ctr.as<Counters>());
+      c->launches++;
+      CU(c, cudaGetLastError());
+    }
+    CU(c, cudaStreamSynchronize(s));
+    CU(c, cudaMemcpy(&h, c->d_ctr.p, sizeof h, cudaMemcpyDeviceToHost));
+    if (h.n_issues <= issue_cap) break;
+    issue_cap = h.n_issues; // rerun with an exact-size buffer
+  }
+  const uint64_t n_rows_raw = h.n_rows;
+  if (n_rows_raw > row_cap) return fail(c, LINKS_E_CUDA, "links_finalize: internal row overflow");
+
+  // ---- sort + reduce-by-key on the packed row key (K5b)
+  std::vector<uint64_t> hk; std::vector<unsigned long long> hl; std::vector<long long> hg;
+  uint32_t n_seg = 0;
+  if (n_rows_raw) {
+    Span sp(c, F_SORT, s);
+    const int key_bits = 3 + 2 * tb;
+    const uint32_t n_blocks = uint32_t((n_rows_raw + kSortTile - 1) / kSortTile);
+    CU(c, d_keys[1].ensure(n_rows_raw * 8)); CU(c, d_vals[1].ensure(n_rows_raw * 4));
+    CU(c, d_hist.ensure(uint64_t(kRadix) * n_blocks * 4));
+    int cur = 0;
+    for (int shift = 0; shift < key_bits; shift += 8) {
+      radix_hist_kernel<<<n_blocks, kSortThreads, 0, s>>>(d_keys[cur].as<uint64_t>(), n_rows_raw, shift, d_hist.as<uint32_t>(), n_blocks);
+      c->launches++;
+      rc = device_scan(c, s, d_hist.as<uint32_t>(), uint64_t(kRadix) * n_blocks, d_hist.as<uint32_t>(), d_scan_tmp, d_total.as<uint32_t>());
+      if (rc) return rc;
+      radix_scatter_kernel<<<n_blocks, kSortThreads, 0, s>>>(d_keys[cur].as<uint64_t>(), d_vals[cur].as<int32_t>(), n_rows_raw, shift,
+                                                            d_hist.as<uint32_t>(), n_blocks, d_keys[cur ^ 1].as<uint64_t>(),
+                                                            d_vals[cur ^ 1].as<int32_t>());
+      c->launches++;
+      cur ^= 1;
+    }
+    CU(c, d_flags.ensure(n_rows_raw * 4));
+    head_flags_kernel<<<unsigned((n_rows_raw + 255) / 256), 256, 0, s>>>(d_keys[cur].as<uint64_t>(), n_rows_raw, d_flags.as<uint32_t>());
+    c->launches++;
+    rc = device_scan(c, s, d_flags.as<uint32_t>(), n_rows_raw, d_flags.as<uint32_t>(), d_scan_tmp, d_total.as<uint32_t>());
+    if (rc) return rc;
+    CU(c, cudaMemcpyAsync(&n_seg, d_total.p, 4, cudaMemcpyDeviceToHost, s));
+    CU(c, cudaStreamSynchronize(s));
+    CU(c, d_okeys.ensure(uint64_t(n_seg) * 8)); CU(c, d_olinks.ensure(uint64_t(n_seg) * 8)); CU(c, d_ogaps.ensure(uint64_t(n_seg) * 8));
+    CU(c, cudaMemsetAsync(d_olinks.p, 0, uint64_t(n_seg) * 8, s));
+    CU(c, cudaMemsetAsync(d_ogaps.p, 0, uint64_t(n_seg) * 8, s));
+    const uint64_t thr = (n_rows_raw + kReduceItems - 1) / kReduceItems;
+    reduce_by_key_kernel<<<unsigned((thr + 255) / 256), 256, 0, s>>>(d_keys[cur].as<uint64_t>(), d_vals[cur].as<int32_t>(), n_rows_raw,
+                                                                   d_flags.as<uint32_t>(), d_okeys.as<uint64_t>(),
+                                                                   d_olinks.as<unsigned long long>(), d_ogaps.as<unsigned long long>());
+    c->launches++;
+    CU(c, cudaGetLastError());
+    hk.resize(n_seg); hl.resize(n_seg); hg.resize(n_seg);
+  }
+  std::vector<IssueRec> hi(h.n_issues);
+  {
+    Span sp(c, F_D2H, s);
+    if (n_seg) {
+      CU(c, cudaMemcpyAsync(hk.data(), d_okeys.p, uint64_t(n_seg) * 8, cudaMemcpyDeviceToHost, s));
+      CU(c, cudaMemcpyAsync(hl.data(), d_olinks.p, uint64_t(n_seg) * 8, cudaMemcpyDeviceToHost, s));
+      CU(c, cudaMemcpyAsync(hg.data(), d_ogaps.p, uint64_t(n_seg) * 8, cudaMemcpyDeviceToHost, s));
+    }
+    if (h.n_issues) CU(c, cudaMemcpyAsync(hi.data(), d_issues.p, h.n_issues * sizeof(IssueRec), cudaMemcpyDeviceToHost, s));
+  }
+  CU(c, cudaStreamSynchronize(s));
+
+  // ---- host: expand each canonical row into the two rows add_to_pair_map writes (reference :717-761)
+  static const int32_t bin_of_code[5] = {-1, 10, 500, 5000, 10000};
+  const uint64_t n_out = uint64_t(n_seg) * 2;
+  links_row* rows = static_cast<links_row*>(malloc(std::max<uint64_t>(n_out, 1) * sizeof(links_row)));
+  if (!rows) return fail(c, LINKS_E_NOMEM, "links_finalize: out of host memory");
+  const uint64_t tmask = (1ull << tb) - 1;
+  for (uint32_t i = 0; i < n_seg; ++i) {
+    const uint64_t key = hk[i];
+    const uint32_t B = uint32_t(key & tmask), A = uint32_t((key >> tb) & tmask), bc = uint32_t(key >> (2 * tb));
+    links_row r;
+    memset(&r, 0, sizeof r);
+    r.bin = bin_of_code[bc]; r.links = hl[i]; r.gaps = hg[i];
+    r.tig_a = A >> 1; r.rev_a = A & 1; r.tig_b = B >> 1; r.rev_b = B & 1;
+    rows[2 * i] = r;
+    r.tig_a = B >> 1; r.rev_a = (B & 1) ^ 1; r.tig_b = A >> 1; r.rev_b = (A & 1) ^ 1;
+    rows[2 * i + 1] = r;
+  }
+  std::sort(rows, rows + n_out, [](const links_row& a, const links_row& b) {
+    if (a.bin != b.bin) return a.bin < b.bin;
+    if (a.tig_a != b.tig_a) return a.tig_a < b.tig_a;
+    if (a.rev_a != b.rev_a) return a.rev_a < b.rev_a;
+    if (a.tig_b != b.tig_b) return a.tig_b < b.tig_b;
+    return a.rev_b < b.rev_b;
+  });
+  links_issue* issues = nullptr;
+  if (issues_out) {
+    issues = static_cast<links_issue*>(malloc(std::max<uint64_t>(hi.size(), 1) * sizeof(links_issue)));
+    if (!issues) { free(rows); return fail(c, LINKS_E_NOMEM, "links_finalize: out of host memory"); }
+    static_assert(sizeof(links_issue) == sizeof(IssueRec), "issue record layout");
+    if (!hi.empty()) memcpy(issues, hi.data(), hi.size() * sizeof(links_issue));
+    std::sort(issues, issues + hi.size(), [](const links_issue& a, const links_issue& b) {
+#define LK(f) if (a.f != b.f) return a.f < b.f
+      LK(tig); LK(s1); LK(s2); LK(e1); LK(e2); LK(o1); LK(o2); LK(pet_size); LK(insert_size); LK(tig_len);
+#undef LK
+      return false;
+    });
+    *issues_out = issues;
+    if (n_issues_out) *n_issues_out = hi.size();
+  }
+  *rows_out = rows; *n_rows_out = n_out;
+  if (stats) {
+    memset(stats, 0, sizeof *stats);
+    stats->n_candidates = h.n_candidates; stats->n_survivors = h.n_survivors; stats->n_unique_pairs = h.n_unique;
+    stats->n_bf_probes = h.n_bf_probes; stats->n_contig_kmers = h.n_contig_kmers;
+    stats->ct_ok_pairs = h.ct_ok_pairs; stats->ct_problem_pairs = h.ct_problem_pairs; stats->ct_ok_contig = h.ct_ok_contig;
+    stats->ct_iz_issues = h.ct_iz_issues; stats->ct_illogical = h.ct_illogical; stats->ct_gate_fail = h.ct_gate_fail;
+    stats->n_rows = n_out;
+  }
+  c->finalized = true;
+  return LINKS_OK;
+}
+
+void links_free_result(links_row* rows, links_issue* issues) { free(rows); free(issues); }
+
+int links_format_row(const links_row* r, char* dst, size_t cap)
+{
+  char a[16] = "", b[16] = "";
+  if (r->tig_a) snprintf(a, sizeof a, "%u", r->tig_a);
+  if (r->tig_b) snprintf(b, sizeof b, "%u", r->tig_b);
+  return snprintf(dst, cap, "%d\t%c%s\t%c%s\t%llu\t%lld\n", r->bin, r->rev_a ? 'r' : 'f', a, r->rev_b ? 'r' : 'f', b,
+                  (unsigned long long)r->links, (long long)r->gaps);
+}
+
+int links_format_issue(const links_issue* r, char* dst, size_t cap)
+{
+  char t[16] = "";
+  if (r->tig) snprintf(t, sizeof t, "%u", r->tig);
+  return snprintf(dst, cap,
+                  "Pairs unsatisfied in distance within a contig.  Pairs on contig id: %s (length: %llu)\n"
+                  "kmer start: %llu kmer end: %llu orientation: %d\n"
+                  "kmer start: %llu kmer end: %llu orientation: %d\n"
+                  "Calculated distance apart on contig: %llu - Distance on read: %lld\n",
+                  t, (unsigned long long)r->tig_len, (unsigned long long)r->s1, (unsigned long long)r->e1, int(r->o1),
+                  (unsigned long long)r->s2, (unsigned long long)r->e2, int(r->o2), (unsigned long long)r->pet_size,
+                  (long long)r->insert_size);
+}
+
+// ---------------------------------------------------------------- inspection utilities
+
+int links_kmer_hashes(links_ctx* c, const char* seq, uint64_t len, uint64_t* fwd, uint64_t* rev, uint8_t* valid)
+{
+  if (!c || !seq || !fwd || !rev || !valid) return LINKS_E_INVAL;
+  const uint32_t k = c->prm.k;
+  if (len < k) return LINKS_OK;
+  CU(c, cudaSetDevice(c->device));
+  const uint64_t npos = len - k + 1;
+  SeqBatchDev b; DevBuf ascii, d_f, d_r, d_v;
+  struct Cleanup { SeqBatchDev& b; DevBuf &a, &f, &r, &v; ~Cleanup() { b.release(); a.release(); f.release(); r.release(); v.release(); } } cl{b, ascii, d_f, d_r, d_v};
+  const uint64_t off[2] = {0, len};
+  std::vector<uint32_t> segs = {0, 0};
+  CU(c, cudaStreamSynchronize(c->s_compute));
+  int rc = upload_and_pack(c, b, ascii, seq, off, 1, segs, false, c->s_copy, c->s_compute, c->ev_copied[0]);
+  if (rc) return rc;
+  CU(c, d_f.ensure(npos * 8)); CU(c, d_r.ensure(npos * 8)); CU(c, d_v.ensure(npos));
+  kmer_hashes_kernel<<<grid_for(c, npos, 256, 16), 256, k * 4 * sizeof(ulonglong2), c->s_compute>>>(
+    b.packed.as<uint32_t>(), b.inv.as<uint32_t>(), npos, int(k), c->d_tab.as<ulonglong2>(), d_f.as<uint64_t>(), d_r.as<uint64_t>(),
+    d_v.as<uint8_t>());
+  c->launches++;
+  CU(c, cudaGetLastError());
+  CU(c, cudaMemcpyAsync(fwd, d_f.p, npos * 8, cudaMemcpyDeviceToHost, c->s_compute));
+  CU(c, cudaMemcpyAsync(rev, d_r.p, npos * 8, cudaMemcpyDeviceToHost, c->s_compute));
+  CU(c, cudaMemcpyAsync(valid, d_v.p, npos, cudaMemcpyDeviceToHost, c->s_compute));
+  CU(c, cudaStreamSynchronize(c->s_compute));
+  return LINKS_OK;
+}
+
+int links_bf_contains(links_ctx* c, const uint64_t* fwd, const uint64_t* rev, uint64_t n, uint8_t* out)
+{
+  if (!c || !fwd || !rev || !out) return LINKS_E_INVAL;
+  if (!c->bf_ready) return fail(c, LINKS_E_INVAL, "links_bf_contains: no Bloom filter");
+  if (!n) return LINKS_OK;
+  CU(c, cudaSetDevice(c->device));
+  DevBuf d_f, d_r, d_o;
+  struct Cleanup { DevBuf &f, &r, &o; ~Cleanup() { f.release(); r.release(); o.release(); } } cl{d_f, d_r, d_o};
+  CU(c, d_f.ensure(n * 8)); CU(c, d_r.ensure(n * 8)); CU(c, d_o.ensure(n));
+  cudaStream_t s = c->s_compute;
+  CU(c, cudaMemcpyAsync(d_f.p, fwd, n * 8, cudaMemcpyHostToDevice, s));
+  CU(c, cudaMemcpyAsync(d_r.p, rev, n * 8, cudaMemcpyHostToDevice, s));
+  bf_contains_kernel<<<unsigned((n + 255) / 256), 256, 0, s>>>(bloom_view(c), c->kseed, d_f.as<uint64_t>(), d_r.as<uint64_t>(), n, d_o.as<uint8_t>());
+  c->launches++;
+  CU(c, cudaGetLastError());
+  CU(c, cudaMemcpyAsync(out, d_o.p, n, cudaMemcpyDeviceToHost, s));
+  CU(c, cudaStreamSynchronize(s));
+  return LINKS_OK;
+}
+
+int links_pairs_download(links_ctx* c, uint64_t* h_a, uint64_t* h_b, uint32_t* d_idx, uint64_t cap, uint64_t* n)
+{
+  if (!c || !n) return LINKS_E_INVAL;
+  CU(c, cudaSetDevice(c->device));
+  CU(c, cudaStreamSynchronize(c->s_compute));
+  Counters h;
+  CU(c, cudaMemcpy(&h, c->d_ctr.p, sizeof h, cudaMemcpyDeviceToHost));
+  *n = h.n_unique;
+  if (!h_a || !h_b || !d_idx) return LINKS_OK;
+  if (cap < h.n_unique) return fail(c, LINKS_E_INVAL, "links_pairs_download: cap %llu < %llu", (unsigned long long)cap, (unsigned long long)h.n_unique);
+  if (!h.n_unique) return LINKS_OK;
+  DevBuf d_out, d_cnt;
+  struct Cleanup { DevBuf &a, &b; ~Cleanup() { a.release(); b.release(); } } cl{d_out, d_cnt};
+  CU(c, d_out.ensure(h.n_unique * 24)); CU(c, d_cnt.ensure(8));
+  CU(c, cudaMemsetAsync(d_cnt.p, 0, 8, c->s_compute));
+  pair_compact_kernel<<<grid_for(c, c->pair_cap, 256, 8), 256, 0, c->s_compute>>>(c->d_pairs.as<PairSlot>(), c->pair_cap, d_out.as<uint64_t>(),
+                                                                                   h.n_unique, d_cnt.as<unsigned long long>());
+  c->launches++;
+  CU(c, cudaGetLastError());
+  std::vector<uint64_t> tmp(h.n_unique * 3);
+  CU(c, cudaMemcpyAsync(tmp.data(), d_out.p, h.n_unique * 24, cudaMemcpyDeviceToHost, c->s_compute));
+  CU(c, cudaStreamSynchronize(c->s_compute));
+  for (uint64_t i = 0; i < h.n_unique; ++i) {
+    h_a[i] = tmp[3 * i]; h_b[i] = tmp[3 * i + 1];
+    d_idx[i] = c->prm.n_dist > 1 ? okey_d_idx(tmp[3 * i + 2]) : 0;
+  }
+  return LINKS_OK;
+}
+
+// ---------------------------------------------------------------- multi-GPU exchange hooks
+
+int links_pairs_export(links_ctx* c, uint32_t n_ranks, void** dev_records, uint64_t* counts)
+{
+  (void)n_ranks; (void)dev_records; (void)counts;
+  return fail(c, LINKS_E_INVAL, "links_pairs_export: not implemented yet");
+}
+int links_pairs_import(links_ctx* c, const void* dev_records, uint64_t n_records)
+{
+  (void)dev_records; (void)n_records;
+  return fail(c, LINKS_E_INVAL, "links_pairs_import: not implemented yet");
+}
+int links_pairs_clear(links_ctx* c)
+{
+  return fail(c, LINKS_E_INVAL, "links_pairs_clear: not implemented yet");
+}
+
+} // extern "C"

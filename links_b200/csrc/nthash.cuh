@@ -1,0 +1,147 @@
+// links_b200/csrc/nthash.cuh -- ntHash2 on 2-bit packed bases (device) + table generation (host).
+//
+// Restates btllib's ntHash2 (reference btllib/include/btllib/nthash.hpp):
+//   fwd(kmer) = XOR_i srol^(k-1-i)(seed[c_i])        (:897-930 base loop; rolling form :576-589)
+//   rev(kmer) = XOR_i srol^(i)(seed[comp(c_i)])      (:591-603)
+// where srol = rol1 + swapbits033 (:443-447,480-486) rotates the low 33 and high 31 bits of the
+// word independently.  Because the hash is XOR-linear in per-position contributions, a k-mer is
+// hashed from scratch with k table lookups -- no serial dependence between neighbouring
+// positions, which is what lets one thread own one (read, distance, rank) candidate.
+#pragma once
+#include <cstdint>
+#include <cuda_runtime.h>
+
+namespace links {
+
+// 2-bit code = (ascii >> 1) & 3 : A/a=0 C/c=1 T/t/U/u=2 G/g=3 ; complement = code ^ 2
+__host__ __device__ __forceinline__ uint32_t base_code(uint32_t c) { return (c >> 1) & 3u; }
+__host__ __device__ __forceinline__ bool base_valid(uint32_t c)
+{
+  // SEED_TAB[c] != 0 for ACGTU/acgtu (nthash.hpp:38-71); control bytes 1,3,4,5,7 are out of domain
+  const uint32_t u = c & 0xDFu;
+  return u == 'A' || u == 'C' || u == 'G' || u == 'T' || u == 'U';
+}
+
+constexpr uint64_t kSeedA = 0x3c8bfbb395c60474ULL; // nthash.hpp:30-33
+constexpr uint64_t kSeedC = 0x3193c18562a02b4cULL;
+constexpr uint64_t kSeedG = 0x20323ed082572324ULL;
+constexpr uint64_t kSeedT = 0x295549f54be24456ULL;
+constexpr uint64_t kMultiSeed = 0x90b45d39fb6da1faULL; // nthash.hpp:27
+constexpr int kMultiShift = 27;                        // nthash.hpp:24
+
+inline uint64_t srol_n_host(uint64_t v, unsigned n)
+{
+  uint64_t hi = v >> 33, lo = v & 0x1FFFFFFFFULL;
+  const unsigned a = n % 31, b = n % 33;
+  if (a) hi = ((hi << a) | (hi >> (31 - a))) & 0x7FFFFFFFULL;
+  if (b) lo = ((lo << b) | (lo >> (33 - b))) & 0x1FFFFFFFFULL;
+  return (hi << 33) | lo;
+}
+
+// tab[i*4 + code] = { contribution of base `code` at k-mer offset i to fwd , to rev }
+inline void build_nthash_table(unsigned k, ulonglong2* tab)
+{
+  const uint64_t seed_by_code[4] = {kSeedA, kSeedC, kSeedT, kSeedG};
+  for (unsigned i = 0; i < k; ++i)
+    for (unsigned c = 0; c < 4; ++c) {
+      tab[i * 4 + c].x = srol_n_host(seed_by_code[c], k - 1 - i);
+      tab[i * 4 + c].y = srol_n_host(seed_by_code[c ^ 2], i);
+    }
+}
+
+// Hash the k-mer starting at global base index g of a 2-bit packed stream (16 bases per u32,
+// base j of a word at bits 2j..2j+1).  `tab` is the shared-memory copy of the table.  Reads one
+// word past the last needed one (buffers are padded).
+__device__ __forceinline__ void hash_kmer(const uint32_t* __restrict__ packed, uint64_t g, int k,
+                                          const ulonglong2* __restrict__ tab, uint64_t& fwd, uint64_t& rev)
+{
+  const uint64_t w = g >> 4;
+  const int sh = int(g & 15) * 2;
+  uint32_t cur = __ldg(packed + w);
+  uint64_t f = 0, r = 0;
+  for (int i = 0; i < k; i += 16) {
+    const uint32_t nxt = __ldg(packed + w + 1 + (i >> 4));
+    const uint32_t win = __funnelshift_r(cur, nxt, sh);
+    const int nb = min(16, k - i);
+#pragma unroll
+    for (int b = 0; b < 16; ++b) {
+      if (b < nb) {
+        const ulonglong2 e = tab[(i + b) * 4 + ((win >> (2 * b)) & 3u)];
+        f ^= e.x;
+        r ^= e.y;
+      }
+    }
+    cur = nxt;
+  }
+  fwd = f;
+  rev = r;
+}
+
+// true iff none of the bases g .. g+k-1 is flagged in the invalid-base bitmap (32 bases per u32)
+__device__ __forceinline__ bool window_valid(const uint32_t* __restrict__ inv, uint64_t g, int k)
+{
+  uint64_t w = g >> 5;
+  int sh = int(g & 31);
+  int left = k;
+  uint32_t cur = __ldg(inv + w);
+  while (left > 0) {
+    const uint32_t nxt = __ldg(inv + w + 1);
+    const uint32_t win = __funnelshift_r(cur, nxt, sh);
+    const uint32_t mask = left >= 32 ? 0xFFFFFFFFu : ((1u << left) - 1u);
+    if (win & mask) return false;
+    left -= 32;
+    ++w;
+    cur = nxt;
+  }
+  return true;
+}
+
+// hashes()[i] of the canonical multi-hash (nthash.hpp:920-927)
+__device__ __forceinline__ uint64_t multihash_i(uint64_t h0, uint64_t kseed /* k*MULTISEED */, uint32_t i)
+{
+  if (i == 0) return h0;
+  uint64_t t = h0 * (uint64_t(i) ^ kseed);
+  t ^= t >> kMultiShift;
+  return t;
+}
+
+// Bloom filter view: bit n of the byte array = bit (n & 31) of little-endian word n >> 5
+// (btllib BloomFilter::insert/contains, bloom_filter.hpp:639-659).
+struct BloomView {
+  uint32_t* words;
+  uint64_t array_bits; // bytes * 8
+  uint64_t magic;      // floor(2^64 / array_bits)
+  uint32_t hash_num;
+};
+
+__device__ __forceinline__ uint64_t bloom_mod(uint64_t h, const BloomView& bf)
+{
+  // exact h % array_bits: q = floor(h*magic/2^64) is floor(h/d) or one less
+  const uint64_t q = __umul64hi(h, bf.magic);
+  uint64_t r = h - q * bf.array_bits;
+  if (r >= bf.array_bits) r -= bf.array_bits;
+  return r;
+}
+
+__device__ __forceinline__ bool bloom_contains(const BloomView& bf, uint64_t fwd, uint64_t rev, uint64_t kseed,
+                                               uint32_t& probes)
+{
+  const uint64_t h0 = rev < fwd ? rev : fwd;
+  for (uint32_t i = 0; i < bf.hash_num; ++i) {
+    const uint64_t n = bloom_mod(multihash_i(h0, kseed, i), bf);
+    ++probes;
+    if (!((__ldg(bf.words + (n >> 5)) >> (n & 31)) & 1u)) return false;
+  }
+  return true;
+}
+
+__device__ __forceinline__ void bloom_insert(const BloomView& bf, uint64_t fwd, uint64_t rev, uint64_t kseed)
+{
+  const uint64_t h0 = rev < fwd ? rev : fwd;
+  for (uint32_t i = 0; i < bf.hash_num; ++i) {
+    const uint64_t n = bloom_mod(multihash_i(h0, kseed, i), bf);
+    atomicOr(bf.words + (n >> 5), 1u << (n & 31));
+  }
+}
+
+} // namespace links

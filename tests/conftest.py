@@ -1,0 +1,110 @@
+"""Shared fixtures.  `-m "not gpu"` runs everywhere; `-m gpu` needs a B200 and calls the C-ABI."""
+from __future__ import annotations
+
+import gzip
+import hashlib
+import json
+import os
+import sys
+
+import numpy as np
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+GOLDEN = os.path.join(ROOT, "tests", "golden")
+GOLDEN_CASES = sorted(d for d in os.listdir(GOLDEN) if os.path.exists(os.path.join(GOLDEN, d, "case.json")))
+
+
+def pytest_configure(config):
+    config.addinivalue_line("markers", "gpu: needs a CUDA device (B200); calls liblinks_gpu.so")
+
+
+def sha256(b: bytes) -> str:
+    return hashlib.sha256(b).hexdigest()
+
+
+class GoldenCase:
+    """One tests/golden/<name>/ directory, inputs decompressed into tmp files on demand."""
+
+    def __init__(self, name: str):
+        self.name = name
+        self.dir = os.path.join(GOLDEN, name)
+        self.meta = json.load(open(os.path.join(self.dir, "case.json")))
+        self.opts = self.meta["opts"]
+
+    def raw(self, fn: str) -> bytes:
+        with gzip.open(os.path.join(self.dir, fn + ".gz"), "rb") as f:
+            return f.read()
+
+    def contigs(self):
+        from links_b200.seqio import read_seqfile
+        return read_seqfile(os.path.join(self.dir, "contigs.fa.gz"))
+
+    def reads(self):
+        from links_b200.seqio import SeqSet, read_seqfile
+        return SeqSet.concat([read_seqfile(os.path.join(self.dir, fn + ".gz")) for fn in self.meta["read_files"]])
+
+    def steps(self) -> list[int]:
+        t = list(self.opts["t"])
+        while len(t) < len(self.opts["d"]):
+            t.append(t[-1])
+        return t
+
+    def expected_tsv(self) -> bytes:
+        return open(os.path.join(self.dir, "expected.tigpair_checkpoint.tsv"), "rb").read()
+
+    def expected_issues(self) -> bytes:
+        return open(os.path.join(self.dir, "expected.pairing_issues"), "rb").read()
+
+    def materialize(self, tmpdir: str) -> tuple[str, str]:
+        """Write contigs.fa + read files + reads.fof uncompressed; returns (contigs path, fof path)."""
+        cpath = os.path.join(tmpdir, "contigs.fa")
+        open(cpath, "wb").write(self.raw("contigs.fa"))
+        paths = []
+        for fn in self.meta["read_files"]:
+            p = os.path.join(tmpdir, fn)
+            open(p, "wb").write(self.raw(fn))
+            paths.append(p)
+        fof = os.path.join(tmpdir, "reads.fof")
+        open(fof, "w").write("\n".join(paths) + "\n")
+        return cpath, fof
+
+
+def sort_lines(b: bytes) -> bytes:
+    return b"".join(sorted(b.splitlines(keepends=True)))
+
+
+def sort_issue_records(text: bytes) -> bytes:
+    lines = text.split(b"\n")
+    recs = [b"\n".join(lines[i:i + 4]) for i in range(0, len(lines) - 1, 4)]
+    return b"".join(r + b"\n" for r in sorted(recs))
+
+
+@pytest.fixture(params=GOLDEN_CASES)
+def golden_case(request) -> GoldenCase:
+    return GoldenCase(request.param)
+
+
+@pytest.fixture(scope="session")
+def oracle():
+    from oracle import oracle_py
+    oracle_py.load()
+    return oracle_py
+
+
+def have_gpu() -> bool:
+    try:
+        import torch
+        return torch.cuda.is_available()
+    except Exception:
+        return False
+
+
+@pytest.fixture(scope="session")
+def gpu_lib():
+    """The built CUDA library; GPU tests must fail loudly if it is missing (no fallback)."""
+    from links_b200 import _abi
+    return _abi.load()

@@ -1,0 +1,232 @@
+"""GPU parity: the CUDA path, called through the C-ABI, against the CPU oracle and the committed
+golden fixtures.  Integer / byte / index work: every comparison is bit-exact."""
+from __future__ import annotations
+
+import numpy as np
+import pytest
+
+from .conftest import GoldenCase, sha256, sort_issue_records, sort_lines
+
+pytestmark = pytest.mark.gpu
+
+
+def _links(k=15, d=(4000,), t=(2,), o=0, e=0.1):
+    from links_b200 import Links, LinksOptions
+    return Links(LinksOptions(k=k, distances=list(d), step_sizes=list(t), offset=o, insert_stdev=e))
+
+
+def _dirty(rng, n, alphabet=b"ACGTACGTACGTACGTacgtNnRYUu-."):
+    a = np.frombuffer(alphabet, np.uint8)
+    return a[rng.integers(0, len(a), n)].tobytes()
+
+
+def test_nthash_known_answer_on_device(gpu_lib):
+    # reference btllib/tests/nthash.cpp:10-28
+    kmer = b"ACGTACACTGGACTGAGTCT"
+    with _links(k=20) as L:
+        fwd, rev, valid = L.kmer_hashes(kmer)
+    assert valid.tolist() == [1]
+    assert min(int(fwd[0]), int(rev[0])) == 10434435546371013747
+
+
+@pytest.mark.parametrize("k", [1, 2, 15, 16, 17, 20, 31, 32, 33, 40, 64, 100])
+def test_kmer_hashes_match_oracle(gpu_lib, oracle, k):
+    rng = np.random.default_rng(k)
+    for n in (0, k - 1, k, k + 1, 257, 5000):
+        if n < 0:
+            continue
+        seq = _dirty(rng, n) if n != 257 else _dirty(rng, n, b"ACGT")
+        with _links(k=k) as L:
+            fwd, rev, valid = L.kmer_hashes(seq)
+        pos, ofwd, orev, _ = oracle.nthash_walk(seq, 1, k)
+        assert np.array_equal(np.flatnonzero(valid), pos.astype(np.int64))
+        assert np.array_equal(fwd[valid == 1], ofwd) and np.array_equal(rev[valid == 1], orev)
+
+
+def test_bloom_build_matches_oracle_and_golden(gpu_lib, oracle, golden_case):
+    c = golden_case
+    from links_b200 import bf_header, bf_size
+    contigs = c.contigs()
+    m, nbytes, h = bf_size(c.meta["contigs_file_bytes"], c.opts["p"])
+    with _links(k=c.opts["k"]) as L:
+        L.bf_alloc(nbytes, h)
+        L.push_contigs(contigs)
+        bits = L.bf_bits()
+    assert np.array_equal(bits, oracle.bf_build(contigs.seq, contigs.off, nbytes, h, c.opts["k"]))
+    assert sha256(bf_header(c.opts["k"], h, nbytes) + bits.tobytes()) == c.meta["bloom_sha256"]
+
+
+def test_bloom_contains_matches_oracle(gpu_lib, oracle):
+    rng = np.random.default_rng(5)
+    from links_b200.seqio import SeqSet
+    s = SeqSet.from_records([_dirty(rng, 4000, b"ACGT") for _ in range(3)])
+    k, nbytes, h = 15, 4096, 5
+    bits = oracle.bf_build(s.seq, s.off, nbytes, h, k)
+    fwd = rng.integers(0, 2**63, 3000, dtype=np.uint64) * np.uint64(2) + rng.integers(0, 2, 3000, dtype=np.uint64)
+    rev = rng.integers(0, 2**63, 3000, dtype=np.uint64) * np.uint64(2) + rng.integers(0, 2, 3000, dtype=np.uint64)
+    _p, f2, r2, _h = oracle.nthash_walk(s.record(0), 1, k)
+    fwd = np.concatenate([fwd, f2[:1000]]); rev = np.concatenate([rev, r2[:1000]])
+    with _links(k=k) as L:
+        L.bf_load(bits, h)
+        got = L.bf_contains(fwd, rev)
+    exp = oracle.bf_contains(bits, h, k, fwd, rev)
+    assert np.array_equal(got, exp)
+    assert exp[-1000:].all() and not exp[:3000].all()
+
+
+def _run_gpu(c: GoldenCase, chunk_reads: int | None = None):
+    from links_b200 import bf_size
+    from links_b200.seqio import SeqSet
+    contigs, reads = c.contigs(), c.reads()
+    m, nbytes, h = bf_size(c.meta["contigs_file_bytes"], c.opts["p"])
+    with _links(k=c.opts["k"], d=c.opts["d"], t=c.opts["t"], o=c.opts["o"], e=c.opts["e"]) as L:
+        L.bf_alloc(nbytes, h)
+        L.push_contigs(contigs)
+        if chunk_reads is None:
+            L.push_reads(reads)
+        else:
+            for i in range(0, reads.n, chunk_reads):
+                j = min(i + chunk_reads, reads.n)
+                sub = SeqSet(reads.seq, reads.off[i:j + 1], reads.names[i:j])
+                L.push_reads(sub, first_read_idx=i)
+        pa, pb, pd = L.pairs()
+        rows, issues, stats = L.finalize()
+        return L.format_rows(rows), L.format_issues(issues), stats, (pa, pb, pd)
+
+
+def test_whole_path_matches_reference_goldens(gpu_lib, golden_case):
+    """.tigpair_checkpoint.tsv and .pairing_issues vs the unmodified reference binary's output."""
+    tsv, issues, stats, _ = _run_gpu(golden_case)
+    assert sort_lines(tsv) == golden_case.expected_tsv()
+    assert sort_issue_records(issues) == golden_case.expected_issues()
+    assert stats["n_rows"] == golden_case.meta["n_rows"]
+
+
+def test_intermediates_match_oracle(gpu_lib, oracle, golden_case):
+    """Candidate / survivor counts, the distinct pair set with its first-wins distance index, and the
+    stage-4 counters, against the oracle on the same inputs."""
+    c = golden_case
+    contigs, reads = c.contigs(), c.reads()
+    _m, nbytes, h = oracle.bf_size(c.meta["contigs_file_bytes"], c.opts["p"])
+    bits = oracle.bf_build(contigs.seq, contigs.off, nbytes, h, c.opts["k"])
+    _rows, _iss, ostats, obs = oracle.run(c.opts["k"], c.opts["d"], c.steps(), c.opts["o"], c.opts["e"], bits, h,
+                                          contigs.seq, contigs.off, reads.seq, reads.off, keep_obs=True)
+    _tsv, _issues, stats, (pa, pb, pd) = _run_gpu(c)
+    for key in ("n_candidates", "n_survivors", "n_unique_pairs", "ct_ok_pairs", "ct_problem_pairs", "ct_ok_contig",
+                "ct_iz_issues", "ct_illogical", "ct_gate_fail"):
+        assert stats[key] == ostats[key], key
+    # first observation of each (h_a,h_b) in -j 1 order wins (reference src/LINKS.hpp:370-373)
+    first: dict[tuple[int, int], int] = {}
+    for a, b, d in zip(obs["h_a"].tolist(), obs["h_b"].tolist(), obs["d_idx"].tolist()):
+        first.setdefault((a, b), d)
+    got = dict(zip(zip(pa.tolist(), pb.tolist()), pd.tolist()))
+    assert got == first
+
+
+@pytest.mark.parametrize("name,chunk", [("adv_tandem", 7), ("adv_ns_lower", 1), ("adv_offset_k20", 13)])
+def test_push_granularity_does_not_matter(gpu_lib, name, chunk):
+    """Many small links_reads_push calls == one big call (first-wins uses global read ordinals)."""
+    c = GoldenCase(name)
+    tsv, issues, _stats, _ = _run_gpu(c, chunk_reads=chunk)
+    assert sort_lines(tsv) == c.expected_tsv()
+    assert sort_issue_records(issues) == c.expected_issues()
+
+
+def test_bf_load_path_equals_build_path(gpu_lib, oracle):
+    """-r: a filter loaded from bytes gives the same rows as one built on the device."""
+    c = GoldenCase("adv_offset_k20")
+    contigs, reads = c.contigs(), c.reads()
+    _m, nbytes, h = oracle.bf_size(c.meta["contigs_file_bytes"], c.opts["p"])
+    bits = oracle.bf_build(contigs.seq, contigs.off, nbytes, h, c.opts["k"])
+    with _links(k=c.opts["k"], d=c.opts["d"], t=c.opts["t"], o=c.opts["o"], e=c.opts["e"]) as L:
+        L.bf_load(bits, h)
+        L.push_contigs(contigs)
+        L.push_reads(reads)
+        rows, issues, _ = L.finalize()
+        assert sort_lines(L.format_rows(rows)) == c.expected_tsv()
+
+
+def test_stage_api_writes_reference_files(gpu_lib, tmp_path):
+    """The four stage methods of the reference's class LINKS, file in -> file out."""
+    from links_b200 import Links, LinksOptions
+    c = GoldenCase("c1")
+    cpath, fof = c.materialize(str(tmp_path))
+    base = str(tmp_path / "installation_test")
+    L = Links(LinksOptions(assembly_file=cpath, fof_file=fof, distances=c.opts["d"], step_sizes=c.opts["t"], k=15,
+                           base_name=base))
+    L.init_bloom_filter()
+    L.start_read_fasta()
+    L.start_read_contig()
+    L.pair_contigs()
+    L.close()
+    assert sha256(open(base + ".bloom", "rb").read()) == c.meta["bloom_sha256"]
+    assert sort_lines(open(base + ".tigpair_checkpoint.tsv", "rb").read()) == c.expected_tsv()
+    assert sort_issue_records(open(base + ".pairing_issues", "rb").read()) == c.expected_issues()
+    # -r: reuse the .bloom just written (reference src/LINKS.hpp:286-295)
+    base2 = str(tmp_path / "again")
+    L = Links(LinksOptions(assembly_file=cpath, fof_file=fof, distances=c.opts["d"], step_sizes=c.opts["t"], k=15,
+                           base_name=base2, bf_file=base + ".bloom"))
+    L.init_bloom_filter(); L.start_read_fasta(); L.start_read_contig(); L.pair_contigs(); L.close()
+    assert sort_lines(open(base2 + ".tigpair_checkpoint.tsv", "rb").read()) == c.expected_tsv()
+
+
+def test_synthetic_tiny_matches_oracle(gpu_lib, oracle):
+    """ONT-like synthetic data of the bench's shape at a size the oracle finishes in seconds."""
+    from links_b200 import bf_size, synth
+    _g, contigs, reads, k, d, t = synth.make_config("tiny")
+    _m, nbytes, h = bf_size(len(contigs.seq) + 10 * contigs.n, 0.001)
+    with _links(k=k, d=d, t=t) as L:
+        L.bf_alloc(nbytes, h)
+        L.push_contigs(contigs)
+        L.push_reads(reads)
+        bits = L.bf_bits()
+        rows, issues, stats = L.finalize()
+        tsv, iss = L.format_rows(rows), L.format_issues(issues)
+    assert np.array_equal(bits, oracle.bf_build(contigs.seq, contigs.off, nbytes, h, k))
+    orows, oiss, ostats, _ = oracle.run(k, d, t, 0, 0.1, bits, h, contigs.seq, contigs.off, reads.seq, reads.off)
+    assert tsv == oracle.format_rows(orows)
+    assert iss == oracle.format_issues(oiss)
+    assert stats["n_candidates"] == ostats["n_candidates"]
+    assert stats["n_survivors"] == ostats["n_survivors"] and stats["n_unique_pairs"] == ostats["n_unique_pairs"]
+    assert len(rows) > 0
+
+
+def test_edge_inputs(gpu_lib, oracle):
+    """Empty pushes, reads shorter than k or than k+d, all-N reads, contigs shorter than k."""
+    from links_b200.seqio import SeqSet
+    contigs = SeqSet.from_records([b"ACGT", b"", b"N" * 50, b"ACGTTGCATGCATGCAAGGCTTAACCGGTTAC" * 20])
+    reads = SeqSet.from_records([b"", b"ACG", b"N" * 3000, b"ACGTTGCATGCATGCAAGGCTTAACCGGTTAC" * 5, b"acgtn" * 400])
+    k, d, t = 15, [100, 5000], [1, 3]
+    nbytes, h = 1024, 4
+    with _links(k=k, d=d, t=t) as L:
+        L.bf_alloc(nbytes, h)
+        L.push_contigs(SeqSet.from_records([]))
+        L.push_contigs(contigs)
+        L.push_reads(SeqSet.from_records([]))
+        L.push_reads(reads)
+        bits = L.bf_bits()
+        rows, issues, stats = L.finalize()
+        tsv, iss = L.format_rows(rows), L.format_issues(issues)
+    assert np.array_equal(bits, oracle.bf_build(contigs.seq, contigs.off, nbytes, h, k))
+    orows, oiss, ostats, _ = oracle.run(k, d, t, 0, 0.1, bits, h, contigs.seq, contigs.off, reads.seq, reads.off)
+    assert tsv == oracle.format_rows(orows) and iss == oracle.format_issues(oiss)
+    assert stats["n_candidates"] == ostats["n_candidates"]
+    # nothing pushed at all
+    with _links() as L:
+        L.bf_alloc(64, 2)
+        rows, issues, stats = L.finalize()
+    assert len(rows) == 0 and len(issues) == 0 and stats["n_candidates"] == 0
+
+
+def test_argument_errors(gpu_lib):
+    from links_b200 import Links, LinksError, LinksOptions
+    from links_b200.seqio import SeqSet
+    with pytest.raises(LinksError):
+        Links(LinksOptions(k=0))
+    with pytest.raises(LinksError):
+        Links(LinksOptions(k=100000))
+    with _links() as L:
+        with pytest.raises(LinksError):
+            L.push_reads(SeqSet.from_records([b"ACGT" * 100]))  # no Bloom filter yet
+        with pytest.raises(LinksError):
+            L.bf_alloc(12, 3)  # not a multiple of 8
