@@ -1,0 +1,388 @@
+#!/usr/bin/env python
+"""bench.py -- the LINKS hot path (k-mer-pair extract -> Bloom probe -> contig k-mer map -> link
+aggregation) on B200, on the configuration BASELINE.json's metric is quoted on.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--workload NAME] [--scale S]
+
+One step = one complete job on one synthetic batch: Bloom filter build from the contigs, every read
+through extract + probe + pair-set insert, contig k-mer table build, classify, sort + reduce-by-key,
+rows back on the host.  Nothing is cached between steps (links_reset keeps allocations only).
+
+  value : candidate k-mer pairs/s with the ASCII inputs already resident in HBM
+  e2e   : same job through the C-ABI with pinned HOST buffers (H2D of contigs+reads and D2H of rows
+          inside the timed region)
+N > 1 (torchrun): weak scaling -- every rank gets its own 50x read set over the same contigs, the
+ranks' pair sets are exchanged with one NCCL all-to-all keyed on a hash of (h_a,h_b), each rank
+finishes its share and rank 0 sums the partial link tables.
+"""
+from __future__ import annotations
+
+import argparse
+import ctypes as C
+import json
+import os
+import shutil
+import statistics
+import subprocess
+import sys
+import tempfile
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+METRIC = "kmer_pairs_per_sec_extracted_probed_mapped"
+UNIT = "pairs/s"
+WORKLOADS = {
+    # BASELINE.json configs[1]: synthetic 5 Mbp bacterial genome, 500 contigs, 50x ONT-like 10 kb reads, -k 15 -d 4000 -t 2
+    "c2_bacterial_5mbp": "c2_bacterial_5mbp",
+    "tiny": "tiny",
+}
+
+
+def env_int(name: str, default: int) -> int:
+    try:
+        return int(os.environ.get(name, default))
+    except ValueError:
+        return default
+
+
+def load_workload(name: str, scale: float, seed_shift: int = 0):
+    """Synthetic inputs (cached as .npz under /tmp so back-to-back runs do not regenerate)."""
+    from links_b200 import synth
+    from links_b200.seqio import SeqSet
+    g, nc, cov, rl, k, d, t = synth.CONFIGS[name]
+    cache = os.path.join(tempfile.gettempdir(), f"links_b200_{name}_{scale}_{seed_shift}.npz")
+    if os.path.exists(cache):
+        z = np.load(cache)
+        contigs = SeqSet(z["cs"], z["co"], [])
+        reads = SeqSet(z["rs"], z["ro"], [])
+    else:
+        genome = synth.make_genome(int(g * scale), seed=1)
+        contigs = synth.make_contigs(genome, max(int(nc * scale), 2), seed=3)
+        reads = synth.make_reads(genome, cov, rl, seed=2 + 1000 * seed_shift)
+        tmp = cache + f".{os.getpid()}.tmp.npz"
+        np.savez(tmp, cs=contigs.seq, co=contigs.off, rs=reads.seq, ro=reads.off)
+        os.replace(tmp, cache)
+    return contigs, reads, k, d, t
+
+
+class ClockSampler:
+    """nvidia-smi clocks + throttle reasons during the timed region (B200_PROFILING.md recipe)."""
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, device: int):
+        self.device = device
+        self.proc = None
+        self.lines: list[str] = []
+
+    def start(self):
+        if not shutil.which("nvidia-smi"):
+            return
+        self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.device), f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                                      "-lms", "100"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+        self.thread = threading.Thread(target=self._pump, daemon=True)
+        self.thread.start()
+
+    def _pump(self):
+        for ln in self.proc.stdout:
+            self.lines.append(ln.strip())
+
+    def stop(self) -> dict:
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except Exception:
+            self.proc.kill()
+        sm, mx = [], []
+        reasons = set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for ln in self.lines:
+            f = [x.strip() for x in ln.split(",")]
+            if len(f) < 9:
+                continue
+            try:
+                sm.append(float(f[1])); mx.append(float(f[2]))
+            except ValueError:
+                continue
+            for nm, v in zip(names, f[5:9]):
+                if v.lower().startswith("active"):
+                    reasons.add(nm)
+        return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def pinned_copy(lib, arr: np.ndarray):
+    """Copy a numpy array into pinned host memory from links_host_alloc; returns (ptr, nbytes)."""
+    n = arr.nbytes
+    p = lib.links_host_alloc(max(n, 1))
+    if not p:
+        raise MemoryError("links_host_alloc failed")
+    C.memmove(p, arr.ctypes.data, n)
+    return p, n
+
+
+def rows_digest(rows: np.ndarray) -> str:
+    import hashlib
+    keep = np.empty(len(rows), dtype=[("bin", "<i4"), ("a", "<u4"), ("b", "<u4"), ("ra", "u1"), ("rb", "u1"), ("l", "<u8"), ("g", "<i8")])
+    keep["bin"], keep["a"], keep["b"], keep["ra"], keep["rb"], keep["l"], keep["g"] = (
+        rows["bin"], rows["tig_a"], rows["tig_b"], rows["rev_a"], rows["rev_b"], rows["links"], rows["gaps"])
+    return hashlib.sha256(keep.tobytes()).hexdigest()[:16]
+
+
+# ---------------------------------------------------------------------------------------------- reference arm
+
+def reference_sample(contigs, reads, k, d, t, target_cand: int):
+    """First reads of the workload up to ~target_cand candidate pairs."""
+    from links_b200 import synth
+    from links_b200.seqio import SeqSet
+    lens = np.diff(reads.off.astype(np.int64))
+    per_read = np.zeros(len(lens), dtype=np.int64)
+    for dd, tt in zip(d, t):
+        per_read += np.maximum(lens - k + 1 - dd, 0) // tt
+    cum = np.cumsum(per_read)
+    n = int(min(np.searchsorted(cum, target_cand) + 1, len(lens)))
+    sub = SeqSet(reads.seq[:int(reads.off[n])], reads.off[:n + 1], [f"r{i}" for i in range(n)])
+    return sub, int(cum[n - 1])
+
+
+def run_reference_once(workdir: str, k, d, t, threads: int) -> float:
+    """One run of the UNMODIFIED reference binary (oracle/_ref/LINKS_CPP) on files in workdir; returns seconds."""
+    from oracle import oracle_py
+    cmd = [oracle_py.REF_BIN, "-f", "contigs.fa", "-s", "reads.fof", "-b", "ref_out", "-j", str(threads), "-k", str(k),
+           "-d", ",".join(map(str, d)), "-t", ",".join(map(str, t))]
+    for suffix in (".bloom", ".tigpair_checkpoint.tsv", ".pairing_issues"):
+        try:
+            os.remove(os.path.join(workdir, "ref_out" + suffix))
+        except FileNotFoundError:
+            pass
+    t0 = time.perf_counter()
+    subprocess.run(cmd, cwd=workdir, check=True, stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL)
+    return time.perf_counter() - t0
+
+
+def prepare_reference_dir(contigs, sample) -> str:
+    from links_b200.seqio import write_fasta
+    wd = tempfile.mkdtemp(prefix="links_ref_")
+    contigs.names = [str(i + 1) for i in range(contigs.n)]
+    write_fasta(os.path.join(wd, "contigs.fa"), contigs)
+    write_fasta(os.path.join(wd, "reads.fa"), sample)
+    open(os.path.join(wd, "reads.fof"), "w").write("reads.fa\n")
+    return wd
+
+
+def cpu_reference(contigs, reads, k, d, t, target_cand: int, runs: int, warm: int):
+    from oracle import oracle_py
+    if not oracle_py.have_ref_bin():
+        return None
+    sample, cand = reference_sample(contigs, reads, k, d, t, target_cand)
+    wd = prepare_reference_dir(contigs, sample)
+    threads = min(4, os.cpu_count() or 1)  # the reference errors above -j 4 (README.md:45)
+    try:
+        for _ in range(warm):
+            run_reference_once(wd, k, d, t, threads)
+        secs = [run_reference_once(wd, k, d, t, threads) for _ in range(runs)]
+    finally:
+        shutil.rmtree(wd, ignore_errors=True)
+    return {"cand": cand, "secs": secs, "threads": threads, "n_reads": sample.n, "bases": int(sample.off[-1])}
+
+
+def main_reference(args, rank: int, world: int):
+    if rank != 0:
+        return
+    contigs, reads, k, d, t = load_workload(args.workload, args.scale)
+    r = cpu_reference(contigs, reads, k, d, t, args.ref_candidates, runs=args.steps, warm=min(args.warmup, 1))
+    if r is None:
+        print(json.dumps({"impl": "reference", "unavailable": "oracle/_ref/LINKS_CPP not built (needs /root/reference at build time)"}))
+        return
+    ms = 1000.0 * sum(r["secs"]) / len(r["secs"])
+    value = r["cand"] / (ms / 1000.0)
+    sample = (f"first {r['n_reads']} reads ({r['bases']} bases, {r['cand']} candidate pairs) of {args.workload} + all contigs; "
+              f"unmodified reference LINKS_CPP -j {r['threads']} from FASTA files, process wall time")
+    out = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
+           "ms_per_step": ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u64",
+           "data": "synthetic", "impl": "reference",
+           "config": {"workload": args.workload, "scale": args.scale, "k": k, "d": d, "t": t, "sample": sample},
+           "cpu_baseline": {"value": value, "unit": UNIT, "cores": r["threads"], "kind": "reference", "sample": sample},
+           "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+           "host_cores": os.cpu_count()}
+    print(json.dumps(out))
+
+
+# ---------------------------------------------------------------------------------------------- our arm
+
+def main_ours(args, rank: int, world: int, local_rank: int):
+    import torch
+    import torch.distributed as dist
+
+    from links_b200 import Links, LinksOptions, _abi, bf_size
+
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device; the hot path has no CPU fallback (use --impl reference for the CPU arm)")
+    torch.cuda.set_device(local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+    lib = _abi.load()
+
+    contigs, reads, k, d, t = load_workload(args.workload, args.scale, seed_shift=rank)
+    file_bytes = int(contigs.off[-1]) + contigs.n * (2 + len(str(contigs.n)))  # what the FASTA would weigh on disk
+    _m, bf_bytes, hash_num = bf_size(file_bytes, 0.001)
+
+    L = Links(LinksOptions(k=k, distances=d, step_sizes=t, device=local_rank))
+    stream = torch.cuda.current_stream()
+    L.set_stream(stream.cuda_stream)
+
+    # inputs: pinned host copies (e2e leg) and device-resident copies (value leg)
+    pc_seq, nb_c = pinned_copy(lib, contigs.seq)
+    pc_off, _ = pinned_copy(lib, contigs.off)
+    pr_seq, nb_r = pinned_copy(lib, reads.seq)
+    pr_off, _ = pinned_copy(lib, reads.off)
+    d_contigs = torch.from_numpy(contigs.seq).cuda()
+    d_reads = torch.from_numpy(reads.seq).cuda()
+    h2d_bytes = nb_c + nb_r + contigs.off.nbytes + reads.off.nbytes
+
+    state = {}
+
+    def step(resident: bool):
+        L.reset()
+        L.bf_alloc(bf_bytes, hash_num)
+        if resident:
+            L.push_contigs_dev(d_contigs.data_ptr(), contigs.off, 1)
+            L.push_reads_dev(d_reads.data_ptr(), reads.off, 0)
+        else:
+            L.push_contigs_raw(pc_seq, pc_off, contigs.n, 1)
+            L.push_reads_raw(pr_seq, pr_off, reads.n, 0)
+        if world > 1:
+            exchange_pairs(L, rank, world, torch, dist)
+        rows, issues, stats = L.finalize()
+        if world > 1:
+            rows = merge_rows(rows, rank, world, torch, dist)
+        state["rows"], state["issues"], state["stats"] = rows, issues, stats
+
+    def timed(resident: bool, steps: int, warmup: int):
+        for _ in range(warmup):
+            step(resident)
+        L.timing(reset=True)
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(stream)
+        for _ in range(steps):
+            step(resident)
+        e1.record(stream)
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        ms = e0.elapsed_time(e1)
+        if world > 1:
+            tms = torch.tensor([ms], device="cuda", dtype=torch.float64)
+            dist.all_reduce(tms, op=dist.ReduceOp.MAX)
+            ms = float(tms.item())
+        return ms / steps, L.timing(reset=True)
+
+    clocks = ClockSampler(local_rank)
+    clocks.start()
+    ms_res, tm_res = timed(True, args.steps, args.warmup)
+    digest_res = rows_digest(state["rows"]) if rank == 0 else ""
+    stats = dict(state["stats"])
+    ms_e2e, tm_e2e = timed(False, args.steps, max(args.warmup, 1))
+    clk = clocks.stop()
+    digest_e2e = rows_digest(state["rows"]) if rank == 0 else ""
+
+    cand = stats["n_candidates"]
+    cand_total = cand
+    if world > 1:
+        tc = torch.tensor([cand], device="cuda", dtype=torch.int64)
+        dist.all_reduce(tc)
+        cand_total = int(tc.item())
+    if rank == 0:
+        assert digest_res == digest_e2e, "device-resident and host-buffer legs disagree"
+        n_rows = len(state["rows"])
+        d2h_bytes = n_rows // 2 * 24 + len(state["issues"]) * 72 + 3 * 112
+        # roofline of the dominant kernel (extract_kernel): algorithmic bytes per launch / mean launch duration
+        n_launch = max(int(tm_res["extract_launches"]), 1)
+        steps_l = args.steps
+        alg_bytes_step = cand * (t[0] / 4.0) + stats["n_bf_probes"] * 32.0 + stats["n_survivors"] * 64.0
+        alg_bytes_launch = alg_bytes_step * steps_l / n_launch
+        ms_launch = tm_res["ms_extract"] / n_launch
+        achieved = alg_bytes_launch / (ms_launch * 1e-3) / 1e9 if ms_launch > 0 else 0.0
+        peak, peak_src = 6650.0, "fallback 6.65 TB/s (B200_PROFILING.md)"
+        try:
+            mp = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+            peak, peak_src = float(mp["hbm_gbs"]), "MEASURED_PEAKS.json hbm_gbs (burst copy)"
+        except Exception:
+            pass
+        out = {
+            "metric": METRIC, "value": cand_total / (ms_res * 1e-3), "unit": UNIT, "n_gpus": world, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": ms_res, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "u64", "data": "synthetic",
+            "config": {"workload": args.workload, "scale": args.scale, "k": k, "d": d, "t": t, "genome_bp": int(5_000_000 * args.scale),
+                       "contigs": contigs.n, "reads_per_gpu": reads.n, "read_bases_per_gpu": int(reads.off[-1]),
+                       "candidate_pairs_per_gpu": cand, "survivors": stats["n_survivors"], "unique_pairs": stats["n_unique_pairs"],
+                       "bf_probes": stats["n_bf_probes"], "rows": n_rows, "rows_digest": digest_res,
+                       "l2": "inputs (250 MB reads, GB-scale pair set and contig table) exceed the 126 MB L2; no flush",
+                       "sharding": "reads by rank, contigs replicated" if world > 1 else "single GPU"},
+            "e2e": {"value": cand_total / (ms_e2e * 1e-3), "unit": UNIT, "ms_per_step": ms_e2e, "h2d_bytes_per_step": int(h2d_bytes),
+                    "d2h_bytes_per_step": int(d2h_bytes)},
+            "gpu_launches": int(tm_res["launches"]),
+            "clocks": clk,
+            "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": None,
+                         "kernel": "extract_kernel", "launches": n_launch, "ms_per_launch": ms_launch,
+                         "algorithmic_bytes_per_launch": alg_bytes_launch,
+                         "bytes_per_pair": alg_bytes_step / max(cand, 1), "peak_source": peak_src},
+            "kernel_ms_per_step": {kk: vv / args.steps for kk, vv in tm_res.items() if kk.startswith("ms_")},
+            "kernel_ms_per_step_e2e": {kk: vv / args.steps for kk, vv in tm_e2e.items() if kk.startswith("ms_")},
+        }
+        if world == 1 and not args.no_cpu_baseline:
+            r = cpu_reference(contigs, reads, k, d, t, args.ref_candidates, runs=1, warm=0)
+            if r is not None:
+                v = r["cand"] / r["secs"][0]
+                out["cpu_baseline"] = {"value": v, "unit": UNIT, "cores": r["threads"], "kind": "reference",
+                                       "sample": f"first {r['n_reads']} reads ({r['cand']} candidate pairs) + all contigs, unmodified "
+                                                 f"reference LINKS_CPP -j {r['threads']} from FASTA, {r['secs'][0]:.1f} s wall; host has {os.cpu_count()} cores"}
+            else:
+                out["cpu_baseline"] = {"value": None, "unit": UNIT, "cores": 0, "kind": "reference", "sample": "oracle/_ref/LINKS_CPP missing"}
+        print(json.dumps(out))
+    L.close()
+    for p in (pc_seq, pc_off, pr_seq, pr_off):
+        lib.links_host_free(p)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def exchange_pairs(L, rank, world, torch, dist):
+    raise SystemExit("multi-GPU exchange is not wired yet in this revision")
+
+
+def merge_rows(rows, rank, world, torch, dist):
+    raise SystemExit("multi-GPU exchange is not wired yet in this revision")
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--workload", default="c2_bacterial_5mbp", choices=sorted(WORKLOADS))
+    ap.add_argument("--scale", type=float, default=1.0)
+    ap.add_argument("--ref-candidates", type=int, default=4_000_000, help="size of the bounded CPU sample (candidate pairs)")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    rank, world, local_rank = env_int("RANK", 0), env_int("WORLD_SIZE", 1), env_int("LOCAL_RANK", 0)
+    if args.impl == "reference":
+        main_reference(args, rank, world)
+    else:
+        main_ours(args, rank, world, local_rank)
+
+
+if __name__ == "__main__":
+    main()

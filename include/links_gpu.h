@@ -97,6 +97,12 @@ int links_create(links_ctx** out, const links_params* p);
 void links_destroy(links_ctx* ctx);
 const char* links_last_error(const links_ctx* ctx); /* ctx may be NULL: last create error */
 int links_sync(links_ctx* ctx);                      /* wait for all queued device work */
+/* Run the compute work on a caller-owned cudaStream_t (e.g. torch's current stream) so the caller's
+ * own CUDA events bracket it.  Call before any push. */
+int links_set_stream(links_ctx* ctx, void* cuda_stream);
+/* Forget the current job (filter, contigs, pair set, counters) but keep all device allocations, so
+ * a long-lived process can run job after job without re-allocating. */
+int links_reset(links_ctx* ctx);
 
 /* Pinned host buffers for callers that want full-speed H2D (optional). */
 void* links_host_alloc(size_t bytes);
@@ -121,11 +127,14 @@ size_t links_bf_header(char* dst, size_t cap, uint32_t k, uint32_t hash_num, uin
  * start_read_contig / populate_mate_info / write_from_block_to_set (src/LINKS.hpp:379-402,487-513,569-601,640-680).
  * Record i of this call is contig id first_tig_id + i (1-based ordinal over ALL records, :657-659). */
 int links_contigs_push(links_ctx* ctx, const char* seq, const uint64_t* off, uint32_t n, uint32_t first_tig_id);
+/* Same, with the concatenated ASCII already resident in device memory (offsets stay on the host). */
+int links_contigs_push_dev(links_ctx* ctx, const void* dev_seq, const uint64_t* off, uint32_t n, uint32_t first_tig_id);
 
 /* ---- stage 2: reads.  Replaces start_read_fasta / extract_mate_pair / write_from_block_to_map
  * (src/LINKS.hpp:354-378,470-486,515-567,602-638).  first_read_idx = ordinal of record 0 over
  * all files of the .fof (defines first-wins order when n_dist > 1). */
 int links_reads_push(links_ctx* ctx, const char* seq, const uint64_t* off, uint32_t n, uint64_t first_read_idx);
+int links_reads_push_dev(links_ctx* ctx, const void* dev_seq, const uint64_t* off, uint32_t n, uint64_t first_read_idx);
 
 /* ---- stage 4.  Replaces LINKS::pair_contigs (src/LINKS.hpp:780-1041).
  * rows: sorted by (bin, tig_a, rev_a, tig_b, rev_b), each key once.  issues: sorted.
@@ -157,8 +166,10 @@ int links_bf_contains(links_ctx* ctx, const uint64_t* fwd, const uint64_t* rev, 
 int links_pairs_download(links_ctx* ctx, uint64_t* h_a, uint64_t* h_b, uint32_t* d_idx, uint64_t cap, uint64_t* n);
 /* Device time (ms) and launch counts accumulated per kernel family since create / last reset. */
 typedef struct links_timing {
-  float ms_h2d, ms_pack, ms_bf_build, ms_table_build, ms_extract, ms_classify, ms_sort_reduce, ms_d2h;
-  uint64_t launches;
+  float ms_h2d, ms_pack, ms_bf_build, ms_table_build, ms_extract, ms_classify, ms_sort_reduce, ms_d2h, ms_grow;
+  uint32_t pad_;
+  uint64_t launches;         /* all kernels launched by this library */
+  uint64_t extract_launches; /* launches of the dominant kernel (extract_kernel) */
 } links_timing;
 int links_get_timing(links_ctx* ctx, links_timing* t, int reset);
 

@@ -62,7 +62,7 @@ class LinksStats(C.Structure):
 class LinksTiming(C.Structure):
     _fields_ = [(n, C.c_float) for n in (
         "ms_h2d", "ms_pack", "ms_bf_build", "ms_table_build", "ms_extract", "ms_classify", "ms_sort_reduce",
-        "ms_d2h")] + [("launches", C.c_uint64)]
+        "ms_d2h", "ms_grow")] + [("pad_", C.c_uint32), ("launches", C.c_uint64), ("extract_launches", C.c_uint64)]
 
 
 # name -> (restype, argtypes); this table is also what tests check against the header
@@ -71,6 +71,10 @@ SIGNATURES = {
     "links_destroy": (None, [C.c_void_p]),
     "links_last_error": (C.c_char_p, [C.c_void_p]),
     "links_sync": (C.c_int, [C.c_void_p]),
+    "links_set_stream": (C.c_int, [C.c_void_p, C.c_void_p]),
+    "links_reset": (C.c_int, [C.c_void_p]),
+    "links_contigs_push_dev": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint32, C.c_uint32]),
+    "links_reads_push_dev": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint32, C.c_uint64]),
     "links_host_alloc": (C.c_void_p, [C.c_size_t]),
     "links_host_free": (None, [C.c_void_p]),
     "links_bf_size": (C.c_int, [C.c_uint64, C.c_float, C.POINTER(C.c_uint64), C.POINTER(C.c_uint64), C.POINTER(C.c_uint32)]),

@@ -85,7 +85,7 @@ __global__ void __launch_bounds__(kCtaThreads) pack_kernel(const uint8_t* __rest
   const uint64_t g0 = t * 32;
   if (g0 >= n_bases) return;
   uint32_t bytes[8];
-  if (g0 + 32 <= n_bases) {
+  if (g0 + 32 <= n_bases && (reinterpret_cast<uintptr_t>(ascii) & 15) == 0) {
     const uint4 a = __ldg(reinterpret_cast<const uint4*>(ascii + g0));
     const uint4 b = __ldg(reinterpret_cast<const uint4*>(ascii + g0) + 1);
     bytes[0] = a.x; bytes[1] = a.y; bytes[2] = a.z; bytes[3] = a.w;
@@ -211,6 +211,13 @@ struct ContigBatch {
   const uint32_t* packed; const uint32_t* inv; const uint64_t* off; uint64_t base0;
   const uint32_t* seg_tile_start; uint32_t n_seq, n_tiles; uint32_t first_tig;
 };
+
+__global__ void table_init_kernel(TableSlot* __restrict__ slots, uint64_t n)
+{
+  const ulonglong2 e = make_ulonglong2(kEmpty, 0ull);
+  for (uint64_t i = uint64_t(blockIdx.x) * blockDim.x + threadIdx.x; i < n; i += uint64_t(gridDim.x) * blockDim.x)
+    reinterpret_cast<ulonglong2*>(slots)[i] = e;
+}
 
 __device__ __forceinline__ void table_insert(const TableView& tv, uint64_t h, uint64_t payload)
 {

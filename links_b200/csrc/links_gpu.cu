@@ -51,7 +51,7 @@ struct SeqBatchDev { // device-resident packed sequences of one push/chunk
   void release() { packed.release(); inv.release(); off.release(); segs.release(); flags.release(); vs.release(); vrank.release(); }
 };
 
-enum Family { F_H2D, F_PACK, F_BF, F_TABLE, F_EXTRACT, F_CLASSIFY, F_SORT, F_D2H, F_COUNT };
+enum Family { F_H2D, F_PACK, F_BF, F_TABLE, F_EXTRACT, F_CLASSIFY, F_SORT, F_D2H, F_GROW, F_COUNT };
 
 struct TimedSpan { int fam; cudaEvent_t a, b; };
 
@@ -66,6 +66,7 @@ struct links_ctx {
   std::vector<int32_t> min_allowed;
   std::string err;
   cudaStream_t s_compute = nullptr, s_copy = nullptr;
+  bool own_compute_stream = true;
 
   // ntHash table + distance params on device
   DevBuf d_tab, d_dist, d_step, d_minallowed;
@@ -79,6 +80,8 @@ struct links_ctx {
 
   // contigs (resident)
   std::vector<SeqBatchDev*> contig_batches;
+  std::vector<SeqBatchDev*> contig_pool; // released by links_reset, buffers kept
+  cudaEvent_t ev_contig = nullptr;
   std::vector<uint32_t> tig_len; // [0] = 0
   uint64_t contig_positions = 0;
   uint32_t n_tigs_seen = 0;
@@ -95,8 +98,15 @@ struct links_ctx {
   // pair set
   DevBuf d_pairs;
   uint64_t pair_cap = 0;
-  uint64_t pair_bound = 0; // host upper bound on occupied slots
-  uint64_t cand_total = 0;
+  uint64_t cand_total = 0;   // candidates enqueued so far (upper bound on inserts)
+  // asynchronous occupancy snapshots: {n_unique read back after a chunk, cand_total at that point}
+  static constexpr int kSnaps = 8;
+  Counters* h_snap = nullptr; // pinned, kSnaps entries
+  cudaEvent_t ev_snap[kSnaps]{};
+  uint64_t snap_cand[kSnaps] = {0};
+  bool snap_live[kSnaps] = {false};
+  int snap_next = 0;
+  uint64_t known_unique = 0, known_cand = 0; // latest completed snapshot
 
   // counters
   DevBuf d_ctr;
@@ -105,11 +115,15 @@ struct links_ctx {
   DevBuf d_table;
   uint64_t table_cap = 0;
 
+  // stage-4 scratch (kept across links_reset so repeated jobs do not re-allocate)
+  DevBuf f_keys[2], f_vals[2], f_issues, f_tiglen, f_hist, f_scan_tmp, f_flags, f_total, f_okeys, f_olinks, f_ogaps;
+  uint64_t issue_cap_hint = 1ull << 16;
+
   // timing
   std::vector<TimedSpan> spans;
   std::vector<cudaEvent_t> ev_pool;
   float fam_ms[F_COUNT] = {0};
-  uint64_t launches = 0;
+  uint64_t launches = 0, extract_launches = 0;
   bool timing = true;
   bool finalized = false;
 };
@@ -244,15 +258,17 @@ int device_scan(links_ctx* c, cudaStream_t s, uint32_t* d_in, uint64_t n, uint32
   return LINKS_OK;
 }
 
-// upload + pack one batch of sequences into `b` (device-resident).  tiles_per_seg computed by caller.
-int upload_and_pack(links_ctx* c, SeqBatchDev& b, DevBuf& ascii, const char* seq, const uint64_t* off, uint32_t n,
-                    const std::vector<uint32_t>& seg_tile_start, bool want_rank, cudaStream_t s_copy, cudaStream_t s_comp,
-                    cudaEvent_t ev_copied)
+// upload (unless the ASCII is already device-resident) + pack one batch of sequences into `b`.
+// seg_tile_start is computed by the caller.  `dev_seq` != nullptr: device pointer to the same
+// concatenated ASCII the host pointer would address (offsets are still absolute into it).
+int upload_and_pack(links_ctx* c, SeqBatchDev& b, DevBuf& ascii, const char* seq, const uint8_t* dev_seq, const uint64_t* off,
+                    uint32_t n, const std::vector<uint32_t>& seg_tile_start, bool want_rank, cudaStream_t s_copy,
+                    cudaStream_t s_comp, cudaEvent_t ev_copied)
 {
   const uint64_t base0 = off[0], n_bases = off[n] - off[0];
   b.n_bases = n_bases; b.base0 = base0; b.n_seq = n;
   b.n_tiles = seg_tile_start.back();
-  CU(c, ascii.ensure(((n_bases + 63) & ~63ull) + 64));
+  if (!dev_seq) CU(c, ascii.ensure(((n_bases + 63) & ~63ull) + 64));
   CU(c, b.packed.ensure(((n_bases + 15) / 16 + 8) * 4));
   CU(c, b.inv.ensure(((n_bases + 31) / 32 + 8) * 4));
   CU(c, b.off.ensure((uint64_t(n) + 1) * 8));
@@ -265,7 +281,7 @@ int upload_and_pack(links_ctx* c, SeqBatchDev& b, DevBuf& ascii, const char* seq
   }
   {
     Span sp(c, F_H2D, s_copy);
-    if (n_bases) CU(c, cudaMemcpyAsync(ascii.p, seq + base0, n_bases, cudaMemcpyHostToDevice, s_copy));
+    if (n_bases && !dev_seq) CU(c, cudaMemcpyAsync(ascii.p, seq + base0, n_bases, cudaMemcpyHostToDevice, s_copy));
     CU(c, cudaMemcpyAsync(b.off.p, off, (uint64_t(n) + 1) * 8, cudaMemcpyHostToDevice, s_copy));
     CU(c, cudaMemcpyAsync(b.segs.p, seg_tile_start.data(), seg_tile_start.size() * 4, cudaMemcpyHostToDevice, s_copy));
   }
@@ -274,14 +290,14 @@ int upload_and_pack(links_ctx* c, SeqBatchDev& b, DevBuf& ascii, const char* seq
   {
     Span sp(c, F_PACK, s_comp);
     CU(c, cudaMemsetAsync(b.flags.p, 0, (uint64_t(n) + 1) * 4, s_comp));
-    // zero the padding words the k-mer window loads may touch
+    // padding words the k-mer window loads may touch
     CU(c, cudaMemsetAsync(b.packed.as<uint32_t>() + (n_bases + 15) / 16, 0, 8 * 4, s_comp));
     CU(c, cudaMemsetAsync(b.inv.as<uint32_t>() + (n_bases + 31) / 32, 0xFF, 8 * 4, s_comp));
     if (n_bases) {
       const uint64_t threads = (n_bases + 31) / 32;
+      const uint8_t* src = dev_seq ? dev_seq + base0 : ascii.as<uint8_t>();
       pack_kernel<<<unsigned((threads + kCtaThreads - 1) / kCtaThreads), kCtaThreads, 0, s_comp>>>(
-        ascii.as<uint8_t>(), n_bases, b.packed.as<uint32_t>(), b.inv.as<uint32_t>(), b.off.as<uint64_t>(), n, base0,
-        b.flags.as<uint32_t>());
+        src, n_bases, b.packed.as<uint32_t>(), b.inv.as<uint32_t>(), b.off.as<uint64_t>(), n, base0, b.flags.as<uint32_t>());
       c->launches++;
       if (want_rank) {
         rank_build_kernel<<<n, kCtaThreads, 0, s_comp>>>(b.inv.as<uint32_t>(), b.off.as<uint64_t>(), base0,
@@ -295,33 +311,70 @@ int upload_and_pack(links_ctx* c, SeqBatchDev& b, DevBuf& ascii, const char* seq
   return LINKS_OK;
 }
 
-int ensure_pair_capacity(links_ctx* c, uint64_t incoming)
+// Latest completed occupancy snapshot -> (known_unique, known_cand).
+void poll_snapshots(links_ctx* c)
 {
-  // Invariant kept: occupied + in-flight inserts <= 0.7 * cap, so probing always terminates.
-  auto fits = [&](uint64_t bound, uint64_t cap) { return cap && (bound + incoming) * 10 <= cap * 7; };
-  if (fits(c->pair_bound, c->pair_cap)) { c->pair_bound += incoming; return LINKS_OK; }
-  // tighten the bound with the real count
+  for (int i = 0; i < links_ctx::kSnaps; ++i) {
+    if (!c->snap_live[i]) continue;
+    if (cudaEventQuery(c->ev_snap[i]) != cudaSuccess) { cudaGetLastError(); continue; }
+    c->snap_live[i] = false;
+    if (c->snap_cand[i] >= c->known_cand) { c->known_cand = c->snap_cand[i]; c->known_unique = c->h_snap[i].n_unique; }
+  }
+}
+
+int enqueue_snapshot(links_ctx* c)
+{
+  int i = c->snap_next;
+  c->snap_next = (i + 1) % links_ctx::kSnaps;
+  if (c->snap_live[i]) { // ring wrapped: wait for the old one
+    CU(c, cudaEventSynchronize(c->ev_snap[i]));
+    poll_snapshots(c);
+  }
+  CU(c, cudaMemcpyAsync(&c->h_snap[i], c->d_ctr.p, sizeof(Counters), cudaMemcpyDeviceToHost, c->s_compute));
+  CU(c, cudaEventRecord(c->ev_snap[i], c->s_compute));
+  c->snap_cand[i] = c->cand_total;
+  c->snap_live[i] = true;
+  return LINKS_OK;
+}
+
+// Pair-set capacity.  Invariant: occupied + in-flight inserts <= 0.7 * cap, so probing terminates.
+// The occupied count is only known with a lag (async snapshots), so the host bound is
+//   known_unique + (candidates enqueued after that snapshot) + incoming.
+// `later` = candidates of the rest of this push after `incoming` (used to size a growth once).
+int ensure_pair_capacity(links_ctx* c, uint64_t incoming, uint64_t later)
+{
+  auto bound = [&]() { return c->known_unique + (c->cand_total - c->known_cand) + incoming; };
+  auto fits = [&](uint64_t cap) { return cap && bound() * 10 <= cap * 7; };
+  poll_snapshots(c);
+  if (fits(c->pair_cap)) return LINKS_OK;
+  // tighten with the exact count
   CU(c, cudaStreamSynchronize(c->s_compute));
+  poll_snapshots(c);
   Counters h;
   CU(c, cudaMemcpy(&h, c->d_ctr.p, sizeof h, cudaMemcpyDeviceToHost));
-  c->pair_bound = h.n_unique;
-  if (fits(c->pair_bound, c->pair_cap)) { c->pair_bound += incoming; return LINKS_OK; }
-  uint64_t want = uint64_t(double(c->pair_bound + incoming) / 0.5) + 1024;
-  uint64_t cap = 1ull << log2_ceil(std::max<uint64_t>(want, 1ull << 16));
+  c->known_unique = h.n_unique; c->known_cand = c->cand_total;
+  if (fits(c->pair_cap)) return LINKS_OK;
+  // grow once to the projected final size: observed unique/candidate rate (x1.25) applied to the rest of the push,
+  // plus two chunks of in-flight slack
+  double rate = c->cand_total ? std::min(1.0, 1.25 * double(c->known_unique) / double(c->cand_total)) : 0.5;
+  const double projected = double(c->known_unique) + rate * double(later) + 2.0 * double(incoming);
+  const uint64_t want = uint64_t(std::max(projected, double(bound())) / 0.7) + 1024;
+  const uint64_t cap = 1ull << log2_ceil(std::max<uint64_t>(want, 1ull << 16));
   DevBuf nb;
   CU(c, nb.ensure(cap * sizeof(PairSlot)));
-  CU(c, cudaMemsetAsync(nb.p, 0xFF, cap * sizeof(PairSlot), c->s_compute));
-  if (c->pair_cap && c->pair_bound) {
-    Span sp(c, F_EXTRACT, c->s_compute);
-    pair_rehash_kernel<<<grid_for(c, c->pair_cap, 256, 8), 256, 0, c->s_compute>>>(
-      c->d_pairs.as<PairSlot>(), c->pair_cap, pair_view(nb.as<PairSlot>(), cap), c->d_ctr.as<Counters>(), 0);
-    c->launches++;
+  {
+    Span sp(c, F_GROW, c->s_compute);
+    CU(c, cudaMemsetAsync(nb.p, 0xFF, cap * sizeof(PairSlot), c->s_compute));
+    if (c->pair_cap && c->known_unique) {
+      pair_rehash_kernel<<<grid_for(c, c->pair_cap, 256, 8), 256, 0, c->s_compute>>>(
+        c->d_pairs.as<PairSlot>(), c->pair_cap, pair_view(nb.as<PairSlot>(), cap), c->d_ctr.as<Counters>(), 0);
+      c->launches++;
+    }
   }
   CU(c, cudaStreamSynchronize(c->s_compute));
   c->d_pairs.release();
   c->d_pairs = nb;
   c->pair_cap = cap;
-  c->pair_bound += incoming;
   return LINKS_OK;
 }
 
@@ -415,6 +468,7 @@ int links_create(links_ctx** out, const links_params* p)
   c->sm_count = prop.multiProcessorCount;
   CUC(cudaStreamCreateWithFlags(&c->s_compute, cudaStreamNonBlocking));
   CUC(cudaStreamCreateWithFlags(&c->s_copy, cudaStreamNonBlocking));
+  CUC(cudaEventCreateWithFlags(&c->ev_contig, cudaEventDisableTiming));
   for (int i = 0; i < links_ctx::kSlots; ++i) {
     CUC(cudaEventCreateWithFlags(&c->ev_copied[i], cudaEventDisableTiming));
     CUC(cudaEventCreateWithFlags(&c->ev_done[i], cudaEventDisableTiming));
@@ -432,6 +486,8 @@ int links_create(links_ctx** out, const links_params* p)
     CUC(cudaMemcpy(c->d_minallowed.p, c->min_allowed.data(), p->n_dist * 4, cudaMemcpyHostToDevice));
     CUC(c->d_ctr.ensure(sizeof(Counters)));
     CUC(cudaMemset(c->d_ctr.p, 0, sizeof(Counters)));
+    CUC(cudaHostAlloc(reinterpret_cast<void**>(&c->h_snap), sizeof(Counters) * links_ctx::kSnaps, cudaHostAllocDefault));
+    for (int i = 0; i < links_ctx::kSnaps; ++i) CUC(cudaEventCreateWithFlags(&c->ev_snap[i], cudaEventDisableTiming));
   }
 #undef CUC
   *out = c;
@@ -446,15 +502,21 @@ void links_destroy(links_ctx* c)
   resolve_spans(c);
   for (auto e : c->ev_pool) cudaEventDestroy(e);
   for (auto* b : c->contig_batches) { b->release(); delete b; }
+  for (auto* b : c->contig_pool) { b->release(); delete b; }
+  if (c->ev_contig) cudaEventDestroy(c->ev_contig);
   for (int i = 0; i < links_ctx::kSlots; ++i) {
     c->slot[i].release(); c->slot_ascii[i].release();
     if (c->ev_copied[i]) cudaEventDestroy(c->ev_copied[i]);
     if (c->ev_done[i]) cudaEventDestroy(c->ev_done[i]);
   }
   c->contig_ascii.release();
+  for (int i = 0; i < links_ctx::kSnaps; ++i) if (c->ev_snap[i]) cudaEventDestroy(c->ev_snap[i]);
+  if (c->h_snap) cudaFreeHost(c->h_snap);
+  for (DevBuf* b : {&c->f_keys[0], &c->f_keys[1], &c->f_vals[0], &c->f_vals[1], &c->f_issues, &c->f_tiglen, &c->f_hist,
+                    &c->f_scan_tmp, &c->f_flags, &c->f_total, &c->f_okeys, &c->f_olinks, &c->f_ogaps}) b->release();
   c->d_tab.release(); c->d_dist.release(); c->d_step.release(); c->d_minallowed.release();
   c->d_bloom.release(); c->d_pairs.release(); c->d_ctr.release(); c->d_table.release();
-  if (c->s_compute) cudaStreamDestroy(c->s_compute);
+  if (c->s_compute && c->own_compute_stream) cudaStreamDestroy(c->s_compute);
   if (c->s_copy) cudaStreamDestroy(c->s_copy);
   cudaGetLastError();
   delete c;
@@ -504,9 +566,10 @@ int links_bf_download(links_ctx* c, uint8_t* dst)
   return LINKS_OK;
 }
 
-int links_contigs_push(links_ctx* c, const char* seq, const uint64_t* off, uint32_t n, uint32_t first_tig_id)
+static int contigs_push_impl(links_ctx* c, const char* seq, const uint8_t* dev_seq, const uint64_t* off, uint32_t n,
+                             uint32_t first_tig_id)
 {
-  if (!c || !off || (!seq && n && off[n] != off[0])) return LINKS_E_INVAL;
+  if (!c || !off || (!seq && !dev_seq && n && off[n] != off[0])) return LINKS_E_INVAL;
   if (!c->bf_ready) return fail(c, LINKS_E_INVAL, "links_contigs_push: call links_bf_alloc or links_bf_load first");
   if (first_tig_id == 0) return fail(c, LINKS_E_INVAL, "links_contigs_push: contig ids are 1-based");
   if (n == 0) return LINKS_OK;
@@ -529,13 +592,16 @@ int links_contigs_push(links_ctx* c, const char* seq, const uint64_t* off, uint3
     if (tiles >= (1ull << 31)) return fail(c, LINKS_E_LIMIT, "links_contigs_push: batch too large, push fewer contigs per call");
   }
   segs[n] = uint32_t(tiles);
-  SeqBatchDev* b = new (std::nothrow) SeqBatchDev();
+  // reuse a released batch object (links_reset keeps their device buffers)
+  SeqBatchDev* b = nullptr;
+  if (!c->contig_pool.empty()) { b = c->contig_pool.back(); c->contig_pool.pop_back(); }
+  else b = new (std::nothrow) SeqBatchDev();
   if (!b) return fail(c, LINKS_E_NOMEM, "links_contigs_push: out of host memory");
   b->first_id = first_tig_id;
-  cudaEvent_t ev = c->ev_copied[0];
+  cudaEvent_t ev = c->ev_contig;
   // the single contig staging buffer is reused: wait until the previous pack consumed it
-  CU(c, cudaStreamSynchronize(c->s_compute));
-  int rc = upload_and_pack(c, *b, c->contig_ascii, seq, off, n, segs, false, c->s_copy, c->s_compute, ev);
+  if (!dev_seq) CU(c, cudaStreamSynchronize(c->s_compute));
+  int rc = upload_and_pack(c, *b, c->contig_ascii, seq, dev_seq, off, n, segs, false, c->s_copy, c->s_compute, ev);
   if (rc) { b->release(); delete b; return rc; }
   c->contig_batches.push_back(b);
   c->contig_positions += positions;
@@ -553,8 +619,18 @@ int links_contigs_push(links_ctx* c, const char* seq, const uint64_t* off, uint3
   return LINKS_OK;
 }
 
-static int push_read_chunk(links_ctx* c, const char* seq, const uint64_t* off, uint32_t n, uint64_t first_read_idx,
-                           const std::vector<uint32_t>& segs, uint64_t cand)
+int links_contigs_push(links_ctx* c, const char* seq, const uint64_t* off, uint32_t n, uint32_t first_tig_id)
+{
+  return contigs_push_impl(c, seq, nullptr, off, n, first_tig_id);
+}
+int links_contigs_push_dev(links_ctx* c, const void* dev_seq, const uint64_t* off, uint32_t n, uint32_t first_tig_id)
+{
+  if (!dev_seq) return LINKS_E_INVAL;
+  return contigs_push_impl(c, nullptr, static_cast<const uint8_t*>(dev_seq), off, n, first_tig_id);
+}
+
+static int push_read_chunk(links_ctx* c, const char* seq, const uint8_t* dev_seq, const uint64_t* off, uint32_t n,
+                           uint64_t first_read_idx, const std::vector<uint32_t>& segs, uint64_t cand, uint64_t later)
 {
   const int si = c->next_slot;
   c->next_slot = (si + 1) % links_ctx::kSlots;
@@ -562,35 +638,41 @@ static int push_read_chunk(links_ctx* c, const char* seq, const uint64_t* off, u
     // the slot's previous chunk must have been consumed by its kernels before we overwrite it
     CU(c, cudaEventSynchronize(c->ev_done[si]));
   }
-  int rc = ensure_pair_capacity(c, cand);
+  int rc = ensure_pair_capacity(c, cand, later);
   if (rc) return rc;
   SeqBatchDev& b = c->slot[si];
   b.first_read_idx = first_read_idx;
-  rc = upload_and_pack(c, b, c->slot_ascii[si], seq, off, n, segs, true, c->s_copy, c->s_compute, c->ev_copied[si]);
+  rc = upload_and_pack(c, b, c->slot_ascii[si], seq, dev_seq, off, n, segs, true, c->s_copy, c->s_compute, c->ev_copied[si]);
   if (rc) return rc;
+  c->cand_total += cand;
   if (b.n_tiles) {
-    Span sp(c, F_EXTRACT, c->s_compute);
-    ReadBatch rb{b.packed.as<uint32_t>(), b.inv.as<uint32_t>(), b.off.as<uint64_t>(), b.base0, b.segs.as<uint32_t>(),
-                 b.n_seq, b.n_tiles, b.flags.as<uint32_t>(), b.vs.as<unsigned long long>(), b.vrank.as<uint32_t>(),
-                 first_read_idx};
-    DistParams dp{c->d_dist.as<uint32_t>(), c->d_step.as<uint32_t>(), c->prm.n_dist, c->prm.offset};
-    extract_kernel<<<grid_for(c, b.n_tiles, 1, 8), kCtaThreads, c->prm.k * 4 * sizeof(ulonglong2), c->s_compute>>>(
-      rb, dp, int(c->prm.k), c->kseed, c->d_tab.as<ulonglong2>(), bloom_view(c), pair_view(c->d_pairs.as<PairSlot>(), c->pair_cap),
-      c->d_ctr.as<Counters>());
-    c->launches++;
-    CU(c, cudaGetLastError());
+    {
+      Span sp(c, F_EXTRACT, c->s_compute);
+      ReadBatch rb{b.packed.as<uint32_t>(), b.inv.as<uint32_t>(), b.off.as<uint64_t>(), b.base0, b.segs.as<uint32_t>(),
+                   b.n_seq, b.n_tiles, b.flags.as<uint32_t>(), b.vs.as<unsigned long long>(), b.vrank.as<uint32_t>(),
+                   first_read_idx};
+      DistParams dp{c->d_dist.as<uint32_t>(), c->d_step.as<uint32_t>(), c->prm.n_dist, c->prm.offset};
+      extract_kernel<<<grid_for(c, b.n_tiles, 1, 8), kCtaThreads, c->prm.k * 4 * sizeof(ulonglong2), c->s_compute>>>(
+        rb, dp, int(c->prm.k), c->kseed, c->d_tab.as<ulonglong2>(), bloom_view(c),
+        pair_view(c->d_pairs.as<PairSlot>(), c->pair_cap), c->d_ctr.as<Counters>());
+      c->launches++;
+      c->extract_launches++;
+      CU(c, cudaGetLastError());
+    }
+    rc = enqueue_snapshot(c);
+    if (rc) return rc;
   }
   CU(c, cudaEventRecord(c->ev_done[si], c->s_compute));
   c->slot_used[si] = true;
-  c->cand_total += cand;
   return LINKS_OK;
 }
 
-int links_reads_push(links_ctx* c, const char* seq, const uint64_t* off, uint32_t n, uint64_t first_read_idx)
+static int reads_push_impl(links_ctx* c, const char* seq, const uint8_t* dev_seq, const uint64_t* off, uint32_t n,
+                           uint64_t first_read_idx)
 {
-  if (!c || !off || (!seq && n && off[n] != off[0])) return LINKS_E_INVAL;
+  if (!c || !off || (!seq && !dev_seq && n && off[n] != off[0])) return LINKS_E_INVAL;
   if (!c->bf_ready) return fail(c, LINKS_E_INVAL, "links_reads_push: no Bloom filter yet");
-  if (c->finalized) return fail(c, LINKS_E_INVAL, "links_reads_push: context already finalized");
+  if (c->finalized) return fail(c, LINKS_E_INVAL, "links_reads_push: context already finalized (links_reset first)");
   if (n == 0) return LINKS_OK;
   if (first_read_idx + n >= (1ull << 28)) return fail(c, LINKS_E_LIMIT, "links_reads_push: more than 2^28 reads");
   CU(c, cudaSetDevice(c->device));
@@ -599,39 +681,93 @@ int links_reads_push(links_ctx* c, const char* seq, const uint64_t* off, uint32_
   // chunk the push at record boundaries so copies overlap kernels
   static const uint64_t kChunkBases = []() {
     const char* e = getenv("LINKS_CHUNK_BASES");
-    return e ? strtoull(e, nullptr, 10) : (48ull << 20);
+    return e ? strtoull(e, nullptr, 10) : (16ull << 20);
   }();
-  const uint64_t kChunkCand = 1ull << 28;
+  const uint64_t kChunkCand = 1ull << 27;
+  // upper bound on candidates per (read, distance): exact when the read has no invalid base (reference src/LINKS.hpp:525-543)
+  auto seg_count = [&](uint64_t len, uint32_t di) -> uint64_t {
+    if (len < k) return 0;
+    const uint64_t npos = len - k + 1, d = c->dist[di];
+    return npos > o + d ? (npos - o - d) / c->step[di] : 0;
+  };
+  uint64_t total_cand = 0;
+  for (uint32_t i = 0; i < n; ++i) {
+    if (off[i + 1] < off[i]) return fail(c, LINKS_E_INVAL, "links_reads_push: offsets not monotone");
+    const uint64_t len = off[i + 1] - off[i];
+    if (len >= (1ull << 28)) return fail(c, LINKS_E_LIMIT, "links_reads_push: read longer than 2^28-1");
+    for (uint32_t di = 0; di < nd; ++di) total_cand += seg_count(len, di);
+  }
   uint32_t i0 = 0;
+  uint64_t done_cand = 0;
   std::vector<uint32_t> segs;
   while (i0 < n) {
     segs.clear();
     uint64_t tiles = 0, cand = 0;
     uint32_t i = i0;
     for (; i < n; ++i) {
-      if (off[i + 1] < off[i]) return fail(c, LINKS_E_INVAL, "links_reads_push: offsets not monotone");
       const uint64_t len = off[i + 1] - off[i];
-      if (len >= (1ull << 28)) return fail(c, LINKS_E_LIMIT, "links_reads_push: read longer than 2^28-1");
       if (i > i0 && (off[i + 1] - off[i0] > kChunkBases || cand > kChunkCand || uint64_t(i - i0) * nd > (1ull << 26))) break;
       for (uint32_t di = 0; di < nd; ++di) {
         segs.push_back(uint32_t(tiles));
-        // upper bound (exact when the read has no invalid base): reference src/LINKS.hpp:525-543
-        uint64_t cnt = 0;
-        if (len >= k) {
-          const uint64_t npos = len - k + 1, d = c->dist[di];
-          if (npos > o + d) cnt = (npos - o - d) / c->step[di];
-        }
+        const uint64_t cnt = seg_count(len, di);
         tiles += (cnt + kTile - 1) / kTile;
         cand += cnt;
       }
       if (tiles >= (1ull << 31)) return fail(c, LINKS_E_LIMIT, "links_reads_push: chunk too large");
     }
     segs.push_back(uint32_t(tiles));
-    int rc = push_read_chunk(c, seq, off + i0, i - i0, first_read_idx + i0, segs, cand);
+    done_cand += cand;
+    int rc = push_read_chunk(c, seq, dev_seq, off + i0, i - i0, first_read_idx + i0, segs, cand, total_cand - done_cand);
     if (rc) return rc;
     i0 = i;
   }
   CU(c, cudaStreamSynchronize(c->s_copy)); // host buffers reusable
+  return LINKS_OK;
+}
+
+int links_reads_push(links_ctx* c, const char* seq, const uint64_t* off, uint32_t n, uint64_t first_read_idx)
+{
+  return reads_push_impl(c, seq, nullptr, off, n, first_read_idx);
+}
+int links_reads_push_dev(links_ctx* c, const void* dev_seq, const uint64_t* off, uint32_t n, uint64_t first_read_idx)
+{
+  if (!dev_seq) return LINKS_E_INVAL;
+  return reads_push_impl(c, nullptr, static_cast<const uint8_t*>(dev_seq), off, n, first_read_idx);
+}
+
+int links_set_stream(links_ctx* c, void* cuda_stream)
+{
+  if (!c) return LINKS_E_INVAL;
+  CU(c, cudaSetDevice(c->device));
+  CU(c, cudaStreamSynchronize(c->s_compute));
+  if (c->own_compute_stream && c->s_compute) cudaStreamDestroy(c->s_compute);
+  c->s_compute = static_cast<cudaStream_t>(cuda_stream);
+  c->own_compute_stream = false;
+  return LINKS_OK;
+}
+
+// Forget the job (Bloom bits, contigs, pair set, counters) but keep every device allocation.
+int links_reset(links_ctx* c)
+{
+  if (!c) return LINKS_E_INVAL;
+  CU(c, cudaSetDevice(c->device));
+  CU(c, cudaStreamSynchronize(c->s_copy));
+  CU(c, cudaStreamSynchronize(c->s_compute));
+  poll_snapshots(c);
+  for (auto* b : c->contig_batches) c->contig_pool.push_back(b);
+  c->contig_batches.clear();
+  c->tig_len.assign(1, 0);
+  c->contig_positions = 0; c->n_tigs_seen = 0;
+  c->bf_ready = false; c->bf_insert = false;
+  c->cand_total = 0; c->known_unique = 0; c->known_cand = 0;
+  for (int i = 0; i < links_ctx::kSnaps; ++i) c->snap_live[i] = false;
+  for (int i = 0; i < links_ctx::kSlots; ++i) c->slot_used[i] = false;
+  CU(c, cudaMemsetAsync(c->d_ctr.p, 0, sizeof(Counters), c->s_compute));
+  if (c->pair_cap) {
+    Span sp(c, F_GROW, c->s_compute);
+    CU(c, cudaMemsetAsync(c->d_pairs.p, 0xFF, c->pair_cap * sizeof(PairSlot), c->s_compute));
+  }
+  c->finalized = false;
   return LINKS_OK;
 }
 
@@ -644,9 +780,9 @@ int links_get_timing(links_ctx* c, links_timing* t, int reset)
   resolve_spans(c);
   t->ms_h2d = c->fam_ms[F_H2D]; t->ms_pack = c->fam_ms[F_PACK]; t->ms_bf_build = c->fam_ms[F_BF];
   t->ms_table_build = c->fam_ms[F_TABLE]; t->ms_extract = c->fam_ms[F_EXTRACT]; t->ms_classify = c->fam_ms[F_CLASSIFY];
-  t->ms_sort_reduce = c->fam_ms[F_SORT]; t->ms_d2h = c->fam_ms[F_D2H];
-  t->launches = c->launches;
-  if (reset) { for (auto& m : c->fam_ms) m = 0; c->launches = 0; }
+  t->ms_sort_reduce = c->fam_ms[F_SORT]; t->ms_d2h = c->fam_ms[F_D2H]; t->ms_grow = c->fam_ms[F_GROW];
+  t->launches = c->launches; t->extract_launches = c->extract_launches;
+  if (reset) { for (auto& m : c->fam_ms) m = 0; c->launches = 0; c->extract_launches = 0; }
   return LINKS_OK;
 }
 
@@ -659,8 +795,8 @@ static int build_table(links_ctx* c)
   c->table_cap = cap;
   Span sp(c, F_TABLE, c->s_compute);
   // keys = EMPTY (all ones), vals = 0
-  CU(c, cudaMemsetAsync(c->d_table.p, 0xFF, (cap + 1) * sizeof(TableSlot), c->s_compute));
-  CU(c, cudaMemset2DAsync(reinterpret_cast<char*>(c->d_table.p) + 8, sizeof(TableSlot), 0, 8, cap + 1, c->s_compute));
+  table_init_kernel<<<grid_for(c, cap + 1, 256 * 4, 16), 256, 0, c->s_compute>>>(c->d_table.as<TableSlot>(), cap + 1);
+  c->launches++;
   for (auto* b : c->contig_batches) {
     if (!b->n_tiles) continue;
     ContigBatch cb{b->packed.as<uint32_t>(), b->inv.as<uint32_t>(), b->off.as<uint64_t>(), b->base0,
@@ -693,11 +829,11 @@ int links_finalize(links_ctx* c, links_row** rows_out, uint64_t* n_rows_out, lin
   if (n_unique >= (1ull << 32) - kSortTile) return fail(c, LINKS_E_LIMIT, "links_finalize: more than 2^32 unique pairs on one GPU");
 
   const int tb = log2_ceil(uint64_t(c->n_tigs_seen) * 2 + 2);
-  DevBuf d_keys[2], d_vals[2], d_issues, d_tiglen, d_hist, d_scan_tmp, d_flags, d_total, d_okeys, d_olinks, d_ogaps;
-  struct Cleanup { std::vector<DevBuf*> v; ~Cleanup() { for (auto* b : v) b->release(); } } cl;
-  cl.v = {&d_keys[0], &d_keys[1], &d_vals[0], &d_vals[1], &d_issues, &d_tiglen, &d_hist, &d_scan_tmp, &d_flags, &d_total, &d_okeys, &d_olinks, &d_ogaps};
+  DevBuf (&d_keys)[2] = c->f_keys; DevBuf (&d_vals)[2] = c->f_vals;
+  DevBuf &d_issues = c->f_issues, &d_tiglen = c->f_tiglen, &d_hist = c->f_hist, &d_scan_tmp = c->f_scan_tmp, &d_flags = c->f_flags,
+         &d_total = c->f_total, &d_okeys = c->f_okeys, &d_olinks = c->f_olinks, &d_ogaps = c->f_ogaps;
   const uint64_t row_cap = std::max<uint64_t>(n_unique, 1);
-  uint64_t issue_cap = std::max<uint64_t>(1ull << 16, 1);
+  uint64_t issue_cap = c->issue_cap_hint;
   CU(c, d_keys[0].ensure(row_cap * 8)); CU(c, d_vals[0].ensure(row_cap * 4));
   CU(c, d_tiglen.ensure(c->tig_len.size() * 4));
   CU(c, cudaMemcpyAsync(d_tiglen.p, c->tig_len.data(), c->tig_len.size() * 4, cudaMemcpyHostToDevice, s));
@@ -721,6 +857,7 @@ int links_finalize(links_ctx* c, links_row** rows_out, uint64_t* n_rows_out, lin
     CU(c, cudaMemcpy(&h, c->d_ctr.p, sizeof h, cudaMemcpyDeviceToHost));
     if (h.n_issues <= issue_cap) break;
     issue_cap = h.n_issues; // rerun with an exact-size buffer
+    c->issue_cap_hint = issue_cap;
   }
   const uint64_t n_rows_raw = h.n_rows;
   if (n_rows_raw > row_cap) return fail(c, LINKS_E_CUDA, "links_finalize: internal row overflow");
@@ -867,7 +1004,7 @@ int links_kmer_hashes(links_ctx* c, const char* seq, uint64_t len, uint64_t* fwd
   const uint64_t off[2] = {0, len};
   std::vector<uint32_t> segs = {0, 0};
   CU(c, cudaStreamSynchronize(c->s_compute));
-  int rc = upload_and_pack(c, b, ascii, seq, off, 1, segs, false, c->s_copy, c->s_compute, c->ev_copied[0]);
+  int rc = upload_and_pack(c, b, ascii, seq, nullptr, off, 1, segs, false, c->s_copy, c->s_compute, c->ev_contig);
   if (rc) return rc;
   CU(c, d_f.ensure(npos * 8)); CU(c, d_r.ensure(npos * 8)); CU(c, d_v.ensure(npos));
   kmer_hashes_kernel<<<grid_for(c, npos, 256, 16), 256, k * 4 * sizeof(ulonglong2), c->s_compute>>>(

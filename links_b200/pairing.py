@@ -185,6 +185,25 @@ class Links:
         self._check(self._lib.links_contigs_push(self._h, seq_ptr, off_ptr, n, first_tig_id))
         self._n_contigs = max(self._n_contigs, first_tig_id + n - 1)
 
+    def push_reads_dev(self, dev_ptr: int, off: np.ndarray, first_read_idx: int = 0) -> None:
+        """Reads whose concatenated ASCII already sits in device memory (bench.py's HBM-resident leg)."""
+        off = np.ascontiguousarray(off, dtype=np.uint64)
+        self._check(self._lib.links_reads_push_dev(self._h, dev_ptr, off.ctypes.data, len(off) - 1, first_read_idx))
+
+    def push_contigs_dev(self, dev_ptr: int, off: np.ndarray, first_tig_id: int = 1) -> None:
+        off = np.ascontiguousarray(off, dtype=np.uint64)
+        self._check(self._lib.links_contigs_push_dev(self._h, dev_ptr, off.ctypes.data, len(off) - 1, first_tig_id))
+        self._n_contigs = max(self._n_contigs, first_tig_id + len(off) - 2)
+
+    def set_stream(self, cuda_stream: int) -> None:
+        self._check(self._lib.links_set_stream(self._h, cuda_stream))
+
+    def reset(self) -> None:
+        self._check(self._lib.links_reset(self._h))
+        self._n_contigs = 0
+        self._n_reads = 0
+        self._contigs_pushed = False
+
     def sync(self) -> None:
         self._check(self._lib.links_sync(self._h))
 
@@ -239,7 +258,7 @@ class Links:
     def timing(self, reset: bool = False) -> dict[str, float]:
         t = _abi.LinksTiming()
         self._check(self._lib.links_get_timing(self._h, C.byref(t), int(reset)))
-        return {n: float(getattr(t, n)) for n, _ in _abi.LinksTiming._fields_}
+        return {n: float(getattr(t, n)) for n, _ in _abi.LinksTiming._fields_ if n != "pad_"}
 
     def format_rows(self, rows: np.ndarray) -> bytes:
         buf = C.create_string_buffer(256)
