@@ -32,7 +32,7 @@ struct TableSlot { uint64_t key, val; };
 struct PairSlot { uint64_t a, b, okey, pad; };
 
 struct TableView { TableSlot* slots; uint64_t mask; int shift; /* 64 - log2(cap) */ };
-struct PairView { PairSlot* slots; uint64_t mask; int shift; };
+struct PairView { PairSlot* slots; uint64_t mask; int shift; ulonglong2* list; /* dense (h_a,h_b) of every distinct pair, in insertion order */ };
 
 // counters accumulated on the device (one atomic per warp at kernel end)
 struct Counters {
@@ -340,6 +340,19 @@ __device__ __forceinline__ bool pair_insert(const PairView& pv, uint64_t a, uint
   }
 }
 
+// order key of a pair known to be present
+__device__ __forceinline__ uint64_t pair_okey(const PairView& pv, uint64_t a, uint64_t b)
+{
+  uint64_t i = slot_hash2(a, b) >> pv.shift;
+  for (;;) {
+    const PairSlot* s = pv.slots + i;
+    const ulonglong2 cur = __ldg(reinterpret_cast<const ulonglong2*>(s));
+    if (cur.x == a && cur.y == b) return s->okey;
+    if (cur.x == kEmpty && cur.y == kEmpty) return kEmpty; // not present (cannot happen for listed pairs)
+    i = (i + 1) & pv.mask;
+  }
+}
+
 constexpr int kOkeyRankBits = 28, kOkeyDistBits = 8;
 __host__ __device__ __forceinline__ uint64_t make_okey(uint64_t read_idx, uint32_t d_idx, uint64_t rank)
 {
@@ -350,20 +363,43 @@ __host__ __device__ __forceinline__ uint32_t okey_d_idx(uint64_t okey)
   return uint32_t(okey >> kOkeyRankBits) & ((1u << kOkeyDistBits) - 1u);
 }
 
-__global__ void __launch_bounds__(kCtaThreads) extract_kernel(ReadBatch rb, DistParams dp, int k, uint64_t kseed,
-                                                              const ulonglong2* __restrict__ g_tab, BloomView bf,
-                                                              PairView pv, Counters* __restrict__ ctr)
+// Shared-memory work queue push: every thread of the block calls it (uniform trip counts), `pass`
+// lanes append their candidate id.  One shared atomic per warp.
+__device__ __forceinline__ void queue_push(bool pass, uint16_t q, uint16_t* queue, uint32_t* counter)
 {
-  extern __shared__ ulonglong2 s_tab[];
+  const uint32_t m = __ballot_sync(0xffffffffu, pass);
+  if (!m) return;
+  const int lane = threadIdx.x & 31;
+  uint32_t base = 0;
+  if (lane == (__ffs(m) - 1)) base = atomicAdd(counter, uint32_t(__popc(m)));
+  base = __shfl_sync(0xffffffffu, base, __ffs(m) - 1);
+  if (pass) queue[base + __popc(m & ((1u << lane) - 1u))] = q;
+}
+
+// K3 (+K5a): one tile = up to kTile candidates (rank n = j*t + t-1) of one (read, distance).
+// The reference's per-candidate sequence  hash A -> probe A -> hash B -> probe B -> insert
+// (src/LINKS.hpp:530-564) is run as five block-wide stages with a shared-memory compaction
+// between them, so that after every filter step the surviving candidates are re-packed onto
+// consecutive lanes (ONT-like reads: ~46 % of k-mers survive the filter; un-compacted, the
+// warps ran at 17 of 32 lanes).  Within a stage the Bloom probes of one k-mer are issued
+// together (2 first, the rest after) instead of one dependent load at a time.
+__global__ void __launch_bounds__(kCtaThreads, 4) extract_kernel(ReadBatch rb, DistParams dp, int k, uint64_t kseed,
+                                                                 const ulonglong2* __restrict__ g_tab, BloomView bf,
+                                                                 PairView pv, Counters* __restrict__ ctr)
+{
+  extern __shared__ ulonglong2 s_dyn[];
+  ulonglong2* s_tab = s_dyn;          // [k*4]
+  ulonglong2* sA = s_dyn + k * 4;     // [kTile] fwd/rev hash of k-mer A
+  ulonglong2* sB = sA + kTile;        // [kTile] fwd/rev hash of k-mer B, later (h_a,h_b) of fresh pairs
+  __shared__ uint16_t s_q[2][kTile];
+  __shared__ uint32_t s_n[5];
+  __shared__ uint32_t s_seg, s_va0, s_vb0;
+  __shared__ unsigned long long s_cnt, s_list_base;
   for (int i = threadIdx.x; i < k * 4; i += blockDim.x) s_tab[i] = g_tab[i];
-  __shared__ uint32_t s_seg;
-  __shared__ uint32_t s_va0, s_vb0;
-  __shared__ unsigned long long s_cnt;
   __syncthreads();
-  unsigned long long n_cand = 0, n_surv = 0, n_uniq = 0;
-  uint32_t n_probe = 0;
-  unsigned long long n_probe_acc = 0;
+  unsigned long long n_cand = 0, n_surv = 0, n_probe_acc = 0;
   const bool multi_d = dp.n_dist > 1;
+  const uint32_t h_first = min(bf.hash_num, 2u);
   for (uint32_t tile = blockIdx.x; tile < rb.n_tiles; tile += gridDim.x) {
     const uint32_t n_seg = rb.n_seq * dp.n_dist;
     if (threadIdx.x == 0) {
@@ -388,6 +424,7 @@ __global__ void __launch_bounds__(kCtaThreads) extract_kernel(ReadBatch rb, Dist
         s_va0 = va0; s_vb0 = vb0;
       }
       s_cnt = cnt;
+      s_n[0] = s_n[1] = s_n[2] = s_n[3] = s_n[4] = 0;
     }
     __syncthreads();
     const uint32_t s = s_seg;
@@ -397,6 +434,7 @@ __global__ void __launch_bounds__(kCtaThreads) extract_kernel(ReadBatch rb, Dist
     const unsigned long long cnt = s_cnt;
     const bool flagged = rb.flags[r] != 0;
     const uint64_t j_begin = uint64_t(tile - rb.seg_tile_start[s]) * kTile;
+    const uint32_t n_tile = j_begin < cnt ? uint32_t(min((unsigned long long)kTile, cnt - j_begin)) : 0u;
     RankView rv;
     uint32_t va0 = 0, vb0 = 0;
     if (flagged) {
@@ -405,33 +443,115 @@ __global__ void __launch_bounds__(kCtaThreads) extract_kernel(ReadBatch rb, Dist
       rv.nwords = (rv.npos + 63) >> 6; rv.total = rb.vrank[rv.wb + rv.nwords];
       va0 = s_va0; vb0 = s_vb0;
     }
-    for (int q = threadIdx.x; q < kTile; q += kCtaThreads) {
-      const uint64_t j = j_begin + q;
-      if (j >= cnt) break;
-      const uint64_t n = j * t + (t - 1); // rank among valid k-mers of each stream (ref :530-543)
-      uint64_t a, b;
-      if (!flagged) { a = dp.offset + n; b = a + d; }
-      else { a = select_of(rv, va0 + uint32_t(n)); b = select_of(rv, vb0 + uint32_t(n)); }
-      ++n_cand;
-      uint64_t fa, ra, fb, rbv;
-      hash_kmer(rb.packed, g0 + a, k, s_tab, fa, ra);
-      if (!bloom_contains(bf, fa, ra, kseed, n_probe)) continue; // ref :554 (short-circuit &&)
-      hash_kmer(rb.packed, g0 + b, k, s_tab, fb, rbv);
-      if (!bloom_contains(bf, fb, rbv, kseed, n_probe)) continue;
-      ++n_surv;
-      uint64_t h_a, h_b; // ref :546-552
-      if (fa < rbv) { h_a = rbv; h_b = ra; } else { h_a = fa; h_b = fb; }
-      if (pair_insert(pv, h_a, h_b, make_okey(rb.first_read_idx + r, di, n), multi_d)) ++n_uniq;
+    uint32_t n_probe = 0;
+
+    // ---- stage 1: hash k-mer A, first two probes
+    for (uint32_t base = 0; base < n_tile; base += kCtaThreads) {
+      const uint32_t q = base + threadIdx.x;
+      bool pass = false;
+      if (q < n_tile) {
+        const uint64_t n = (j_begin + q) * t + (t - 1); // rank among valid k-mers of each stream (ref :530-543)
+        const uint64_t a = flagged ? select_of(rv, va0 + uint32_t(n)) : dp.offset + n;
+        uint64_t f, rr;
+        hash_kmer(rb.packed, g0 + a, k, s_tab, f, rr);
+        sA[q] = make_ulonglong2(f, rr);
+        pass = bloom_probe_range(bf, rr < f ? rr : f, kseed, 0, h_first, n_probe);
+      }
+      queue_push(pass, uint16_t(q), s_q[0], &s_n[0]);
     }
-    n_probe_acc += n_probe; n_probe = 0;
+    n_cand += (threadIdx.x < n_tile) ? ((n_tile - threadIdx.x + kCtaThreads - 1) / kCtaThreads) : 0;
+    __syncthreads();
+    // ---- stage 2: remaining probes of A
+    {
+      const uint32_t n1 = s_n[0];
+      for (uint32_t base = 0; base < n1; base += kCtaThreads) {
+        const uint32_t i = base + threadIdx.x;
+        bool pass = false;
+        uint16_t q = 0;
+        if (i < n1) {
+          q = s_q[0][i];
+          const ulonglong2 h = sA[q];
+          pass = bloom_probe_range(bf, h.y < h.x ? h.y : h.x, kseed, h_first, bf.hash_num, n_probe);
+        }
+        queue_push(pass, q, s_q[1], &s_n[1]);
+      }
+    }
+    __syncthreads();
+    // ---- stage 3: hash k-mer B, first two probes (ref :554 evaluates B only if A is in the filter)
+    {
+      const uint32_t n2 = s_n[1];
+      for (uint32_t base = 0; base < n2; base += kCtaThreads) {
+        const uint32_t i = base + threadIdx.x;
+        bool pass = false;
+        uint16_t q = 0;
+        if (i < n2) {
+          q = s_q[1][i];
+          const uint64_t n = (j_begin + q) * t + (t - 1);
+          const uint64_t b = flagged ? select_of(rv, vb0 + uint32_t(n)) : dp.offset + n + d;
+          uint64_t f, rr;
+          hash_kmer(rb.packed, g0 + b, k, s_tab, f, rr);
+          sB[q] = make_ulonglong2(f, rr);
+          pass = bloom_probe_range(bf, rr < f ? rr : f, kseed, 0, h_first, n_probe);
+        }
+        queue_push(pass, q, s_q[0], &s_n[2]);
+      }
+    }
+    __syncthreads();
+    // ---- stage 4: remaining probes of B
+    {
+      const uint32_t n3 = s_n[2];
+      for (uint32_t base = 0; base < n3; base += kCtaThreads) {
+        const uint32_t i = base + threadIdx.x;
+        bool pass = false;
+        uint16_t q = 0;
+        if (i < n3) {
+          q = s_q[0][i];
+          const ulonglong2 h = sB[q];
+          pass = bloom_probe_range(bf, h.y < h.x ? h.y : h.x, kseed, h_first, bf.hash_num, n_probe);
+        }
+        queue_push(pass, q, s_q[1], &s_n[3]);
+      }
+    }
+    __syncthreads();
+    // ---- stage 5: pair key + first-wins insert; fresh pairs are staged for the dense list
+    {
+      const uint32_t n4 = s_n[3];
+      for (uint32_t base = 0; base < n4; base += kCtaThreads) {
+        const uint32_t i = base + threadIdx.x;
+        bool fresh = false;
+        uint16_t q = 0;
+        if (i < n4) {
+          q = s_q[1][i];
+          const ulonglong2 ha = sA[q], hb = sB[q];
+          uint64_t h_a, h_b; // ref :546-552
+          if (ha.x < hb.y) { h_a = hb.y; h_b = ha.y; } else { h_a = ha.x; h_b = hb.x; }
+          const uint64_t n = (j_begin + q) * t + (t - 1);
+          fresh = pair_insert(pv, h_a, h_b, make_okey(rb.first_read_idx + r, di, n), multi_d);
+          if (fresh) sB[q] = make_ulonglong2(h_a, h_b);
+        }
+        queue_push(fresh, q, s_q[0], &s_n[4]);
+      }
+      if (threadIdx.x == 0) n_surv += n4;
+    }
+    __syncthreads();
+    // ---- append the tile's fresh pairs to the dense unique-pair list (one global atomic per tile)
+    {
+      const uint32_t n5 = s_n[4];
+      if (n5) {
+        if (threadIdx.x == 0) s_list_base = atomicAdd(&ctr->n_unique, (unsigned long long)n5);
+        __syncthreads();
+        const unsigned long long lb = s_list_base;
+        for (uint32_t i = threadIdx.x; i < n5; i += kCtaThreads) pv.list[lb + i] = sB[s_q[0][i]];
+      }
+    }
+    n_probe_acc += n_probe;
     __syncthreads();
   }
-  n_cand = warp_sum_ull(n_cand); n_surv = warp_sum_ull(n_surv); n_uniq = warp_sum_ull(n_uniq);
+  n_cand = warp_sum_ull(n_cand); n_surv = warp_sum_ull(n_surv);
   n_probe_acc = warp_sum_ull(n_probe_acc);
   if ((threadIdx.x & 31) == 0) {
     if (n_cand) atomicAdd(&ctr->n_candidates, n_cand);
     if (n_surv) atomicAdd(&ctr->n_survivors, n_surv);
-    if (n_uniq) atomicAdd(&ctr->n_unique, n_uniq);
     if (n_probe_acc) atomicAdd(&ctr->n_bf_probes, n_probe_acc);
   }
 }
@@ -481,21 +601,22 @@ __device__ __forceinline__ KInfo decode_kinfo(uint64_t v, int k)
   return ki;
 }
 
-__global__ void __launch_bounds__(kCtaThreads) classify_kernel(const PairSlot* __restrict__ pairs, uint64_t n_slots,
-                                                               TableView tv, ClassifyParams cp, int k,
-                                                               Counters* __restrict__ ctr)
+__global__ void __launch_bounds__(kCtaThreads) classify_kernel(PairView pv, uint64_t n_pairs, TableView tv, ClassifyParams cp,
+                                                               int k, Counters* __restrict__ ctr)
 {
+  __shared__ uint32_t sm_scan[9];
+  __shared__ unsigned long long s_base;
   unsigned long long c_ok = 0, c_prob = 0, c_okc = 0, c_iz = 0, c_ill = 0, c_gate = 0;
   const int lane = threadIdx.x & 31;
   const uint64_t stride = uint64_t(gridDim.x) * blockDim.x;
-  const uint64_t n_round = (n_slots + stride - 1) / stride * stride; // keep whole warps in the loop
+  const uint64_t n_round = (n_pairs + stride - 1) / stride * stride; // whole blocks stay in the loop
   for (uint64_t i = uint64_t(blockIdx.x) * blockDim.x + threadIdx.x; i < n_round; i += stride) {
     bool emit = false;
     uint64_t rkey = 0; int32_t rdist = 0;
-    if (i < n_slots) {
-      const ulonglong2 hk = __ldg(reinterpret_cast<const ulonglong2*>(pairs + i));
-      if (!(hk.x == kEmpty && hk.y == kEmpty)) {
-        const uint32_t di = cp.n_dist > 1 ? okey_d_idx(pairs[i].okey) : 0;
+    if (i < n_pairs) {
+      const ulonglong2 hk = __ldg(pv.list + i);
+      {
+        const uint32_t di = cp.n_dist > 1 ? okey_d_idx(pair_okey(pv, hk.x, hk.y)) : 0;
         const KInfo k1 = decode_kinfo(table_lookup(tv, hk.x), k);
         const KInfo k2 = decode_kinfo(table_lookup(tv, hk.y), k);
         if (k1.multiple || k2.multiple) { ++c_gate; } // ref :827-830
@@ -553,15 +674,17 @@ __global__ void __launch_bounds__(kCtaThreads) classify_kernel(const PairSlot* _
         }
       }
     }
-    const uint32_t em = __ballot_sync(0xffffffffu, emit);
-    if (em) {
-      unsigned long long base = 0;
-      if (lane == 0) base = atomicAdd(&ctr->n_rows, (unsigned long long)__popc(em));
-      base = __shfl_sync(0xffffffffu, base, 0);
+    // block-level compaction of the emitted rows: one global atomic per block iteration
+    uint32_t total;
+    const uint32_t ex = block_excl_scan(emit ? 1u : 0u, &total, sm_scan);
+    if (total) {
+      if (threadIdx.x == 0) s_base = atomicAdd(&ctr->n_rows, (unsigned long long)total);
+      __syncthreads();
       if (emit) {
-        const uint64_t dst = base + __popc(em & ((1u << lane) - 1u));
+        const uint64_t dst = s_base + ex;
         if (dst < cp.row_cap) { cp.row_keys[dst] = rkey; cp.row_dist[dst] = rdist; }
       }
+      __syncthreads();
     }
   }
   c_ok = warp_sum_ull(c_ok); c_prob = warp_sum_ull(c_prob); c_okc = warp_sum_ull(c_okc);
@@ -574,6 +697,35 @@ __global__ void __launch_bounds__(kCtaThreads) classify_kernel(const PairSlot* _
     if (c_ill) atomicAdd(&ctr->ct_illogical, c_ill);
     if (c_gate) atomicAdd(&ctr->ct_gate_fail, c_gate);
   }
+}
+
+// After reduce-by-key: every canonical row i stands for two rows of the tsv (add_to_pair_map,
+// ref :717-761).  Emit both keys with payload = i (second row: i | 0x40000000 is not needed, the
+// payload only indexes links/gaps) so a final small sort puts all rows in output order.
+__global__ void mirror_expand_kernel(const uint64_t* __restrict__ keys, uint32_t n, int tb, uint64_t* __restrict__ out_keys,
+                                     int32_t* __restrict__ out_idx)
+{
+  const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const uint64_t key = keys[i];
+  const uint64_t tmask = (1ull << tb) - 1;
+  const uint32_t B = uint32_t(key & tmask), A = uint32_t((key >> tb) & tmask), bc = uint32_t(key >> (2 * tb));
+  out_keys[2 * i] = key;
+  out_keys[2 * i + 1] = pack_row_key(bc, B ^ 1u, A ^ 1u, tb);
+  out_idx[2 * i] = int32_t(i);
+  out_idx[2 * i + 1] = int32_t(i);
+}
+
+struct FinalRow { uint64_t key; unsigned long long links; long long gaps; };
+__global__ void gather_rows_kernel(const uint64_t* __restrict__ keys, const int32_t* __restrict__ idx, uint32_t n,
+                                   const unsigned long long* __restrict__ links, const unsigned long long* __restrict__ gaps,
+                                   FinalRow* __restrict__ out)
+{
+  const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  FinalRow r;
+  r.key = keys[i]; r.links = links[idx[i]]; r.gaps = (long long)gaps[idx[i]];
+  out[i] = r;
 }
 
 // ------------------------------------------------------------------ inspection helpers
@@ -602,15 +754,12 @@ __global__ void bf_contains_kernel(BloomView bf, uint64_t kseed, const uint64_t*
   out[i] = bloom_contains(bf, fwd[i], rev[i], kseed, probes);
 }
 
-// compact occupied pair slots: out[] = {a, b, okey}
-__global__ void pair_compact_kernel(const PairSlot* __restrict__ pairs, uint64_t n_slots, uint64_t* __restrict__ out3,
-                                    uint64_t cap, unsigned long long* __restrict__ count)
+// export the dense pair list with order keys: out[] = {a, b, okey}
+__global__ void pair_export_kernel(PairView pv, uint64_t n_pairs, uint64_t* __restrict__ out3)
 {
-  for (uint64_t i = uint64_t(blockIdx.x) * blockDim.x + threadIdx.x; i < n_slots; i += uint64_t(gridDim.x) * blockDim.x) {
-    const PairSlot s = pairs[i];
-    if (s.a == kEmpty && s.b == kEmpty) continue;
-    const unsigned long long dst = atomicAdd(count, 1ull);
-    if (dst < cap) { out3[dst * 3] = s.a; out3[dst * 3 + 1] = s.b; out3[dst * 3 + 2] = s.okey; }
+  for (uint64_t i = uint64_t(blockIdx.x) * blockDim.x + threadIdx.x; i < n_pairs; i += uint64_t(gridDim.x) * blockDim.x) {
+    const ulonglong2 hk = pv.list[i];
+    out3[i * 3] = hk.x; out3[i * 3 + 1] = hk.y; out3[i * 3 + 2] = pair_okey(pv, hk.x, hk.y);
   }
 }
 

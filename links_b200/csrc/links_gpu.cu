@@ -96,8 +96,9 @@ struct links_ctx {
   DevBuf contig_ascii;
 
   // pair set
-  DevBuf d_pairs;
+  DevBuf d_pairs, d_pair_list;
   uint64_t pair_cap = 0;
+  int extract_ctas_per_sm = 4;
   uint64_t cand_total = 0;   // candidates enqueued so far (upper bound on inserts)
   // asynchronous occupancy snapshots: {n_unique read back after a chunk, cand_total at that point}
   static constexpr int kSnaps = 8;
@@ -116,6 +117,7 @@ struct links_ctx {
   uint64_t table_cap = 0;
 
   // stage-4 scratch (kept across links_reset so repeated jobs do not re-allocate)
+  DevBuf f_final;
   DevBuf f_keys[2], f_vals[2], f_issues, f_tiglen, f_hist, f_scan_tmp, f_flags, f_total, f_okeys, f_olinks, f_ogaps;
   uint64_t issue_cap_hint = 1ull << 16;
 
@@ -206,12 +208,14 @@ TableView table_view(links_ctx* c)
   tv.shift = 64 - log2_ceil(c->table_cap ? c->table_cap : 2);
   return tv;
 }
-PairView pair_view(PairSlot* p, uint64_t cap)
+PairView pair_view(PairSlot* p, uint64_t cap, ulonglong2* list)
 {
   PairView pv;
-  pv.slots = p; pv.mask = cap - 1; pv.shift = 64 - log2_ceil(cap);
+  pv.slots = p; pv.mask = cap ? cap - 1 : 0; pv.shift = 64 - log2_ceil(cap ? cap : 2); pv.list = list;
   return pv;
 }
+uint64_t pair_list_capacity(uint64_t cap) { return cap / 10 * 7 + 1024; }
+size_t extract_smem_bytes(uint32_t k) { return (size_t(k) * 4 + 2 * size_t(kTile)) * sizeof(ulonglong2); }
 BloomView bloom_view(links_ctx* c)
 {
   BloomView bf;
@@ -255,6 +259,31 @@ int device_scan(links_ctx* c, cudaStream_t s, uint32_t* d_in, uint64_t n, uint32
     scan_apply_kernel<<<unsigned(lv[l]), kScanThreads, 0, s>>>(data, cnt, ptr[l], out);
     c->launches++;
   }
+  return LINKS_OK;
+}
+
+// LSD radix sort of (u64 key, i32 payload) over the low `key_bits` bits; buffers ping-pong, `cur`
+// names the one holding the result.  keys[1]/vals[1]/f_hist are grown as needed.
+int radix_sort_pairs(links_ctx* c, cudaStream_t s, DevBuf (&keys)[2], DevBuf (&vals)[2], uint64_t n, int key_bits, int& cur)
+{
+  if (n == 0) return LINKS_OK;
+  if (n >= (1ull << 32)) return fail(c, LINKS_E_LIMIT, "radix sort: more than 2^32 rows");
+  const uint32_t n_blocks = uint32_t((n + kSortTile - 1) / kSortTile);
+  CU(c, keys[cur ^ 1].ensure(n * 8)); CU(c, vals[cur ^ 1].ensure(n * 4));
+  CU(c, c->f_hist.ensure(uint64_t(kRadix) * n_blocks * 4));
+  for (int shift = 0; shift < key_bits; shift += 8) {
+    radix_hist_kernel<<<n_blocks, kSortThreads, 0, s>>>(keys[cur].as<uint64_t>(), n, shift, c->f_hist.as<uint32_t>(), n_blocks);
+    c->launches++;
+    int rc = device_scan(c, s, c->f_hist.as<uint32_t>(), uint64_t(kRadix) * n_blocks, c->f_hist.as<uint32_t>(), c->f_scan_tmp,
+                         c->f_total.as<uint32_t>());
+    if (rc) return rc;
+    radix_scatter_kernel<<<n_blocks, kSortThreads, 0, s>>>(keys[cur].as<uint64_t>(), vals[cur].as<int32_t>(), n, shift,
+                                                          c->f_hist.as<uint32_t>(), n_blocks, keys[cur ^ 1].as<uint64_t>(),
+                                                          vals[cur ^ 1].as<int32_t>());
+    c->launches++;
+    cur ^= 1;
+  }
+  CU(c, cudaGetLastError());
   return LINKS_OK;
 }
 
@@ -360,20 +389,22 @@ int ensure_pair_capacity(links_ctx* c, uint64_t incoming, uint64_t later)
   const double projected = double(c->known_unique) + rate * double(later) + 2.0 * double(incoming);
   const uint64_t want = uint64_t(std::max(projected, double(bound())) / 0.7) + 1024;
   const uint64_t cap = 1ull << log2_ceil(std::max<uint64_t>(want, 1ull << 16));
-  DevBuf nb;
+  DevBuf nb, nl;
   CU(c, nb.ensure(cap * sizeof(PairSlot)));
+  CU(c, nl.ensure(pair_list_capacity(cap) * sizeof(ulonglong2)));
   {
     Span sp(c, F_GROW, c->s_compute);
     CU(c, cudaMemsetAsync(nb.p, 0xFF, cap * sizeof(PairSlot), c->s_compute));
     if (c->pair_cap && c->known_unique) {
       pair_rehash_kernel<<<grid_for(c, c->pair_cap, 256, 8), 256, 0, c->s_compute>>>(
-        c->d_pairs.as<PairSlot>(), c->pair_cap, pair_view(nb.as<PairSlot>(), cap), c->d_ctr.as<Counters>(), 0);
+        c->d_pairs.as<PairSlot>(), c->pair_cap, pair_view(nb.as<PairSlot>(), cap, nl.as<ulonglong2>()), c->d_ctr.as<Counters>(), 0);
       c->launches++;
+      CU(c, cudaMemcpyAsync(nl.p, c->d_pair_list.p, c->known_unique * sizeof(ulonglong2), cudaMemcpyDeviceToDevice, c->s_compute));
     }
   }
   CU(c, cudaStreamSynchronize(c->s_compute));
-  c->d_pairs.release();
-  c->d_pairs = nb;
+  c->d_pairs.release(); c->d_pair_list.release();
+  c->d_pairs = nb; c->d_pair_list = nl;
   c->pair_cap = cap;
   return LINKS_OK;
 }
@@ -486,6 +517,10 @@ int links_create(links_ctx** out, const links_params* p)
     CUC(cudaMemcpy(c->d_minallowed.p, c->min_allowed.data(), p->n_dist * 4, cudaMemcpyHostToDevice));
     CUC(c->d_ctr.ensure(sizeof(Counters)));
     CUC(cudaMemset(c->d_ctr.p, 0, sizeof(Counters)));
+    CUC(cudaFuncSetAttribute(extract_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, int(extract_smem_bytes(p->k))));
+    int occ = 0;
+    CUC(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, extract_kernel, kCtaThreads, extract_smem_bytes(p->k)));
+    c->extract_ctas_per_sm = std::max(occ, 1);
     CUC(cudaHostAlloc(reinterpret_cast<void**>(&c->h_snap), sizeof(Counters) * links_ctx::kSnaps, cudaHostAllocDefault));
     for (int i = 0; i < links_ctx::kSnaps; ++i) CUC(cudaEventCreateWithFlags(&c->ev_snap[i], cudaEventDisableTiming));
   }
@@ -513,9 +548,9 @@ void links_destroy(links_ctx* c)
   for (int i = 0; i < links_ctx::kSnaps; ++i) if (c->ev_snap[i]) cudaEventDestroy(c->ev_snap[i]);
   if (c->h_snap) cudaFreeHost(c->h_snap);
   for (DevBuf* b : {&c->f_keys[0], &c->f_keys[1], &c->f_vals[0], &c->f_vals[1], &c->f_issues, &c->f_tiglen, &c->f_hist,
-                    &c->f_scan_tmp, &c->f_flags, &c->f_total, &c->f_okeys, &c->f_olinks, &c->f_ogaps}) b->release();
+                    &c->f_scan_tmp, &c->f_flags, &c->f_total, &c->f_okeys, &c->f_olinks, &c->f_ogaps, &c->f_final}) b->release();
   c->d_tab.release(); c->d_dist.release(); c->d_step.release(); c->d_minallowed.release();
-  c->d_bloom.release(); c->d_pairs.release(); c->d_ctr.release(); c->d_table.release();
+  c->d_bloom.release(); c->d_pairs.release(); c->d_pair_list.release(); c->d_ctr.release(); c->d_table.release();
   if (c->s_compute && c->own_compute_stream) cudaStreamDestroy(c->s_compute);
   if (c->s_copy) cudaStreamDestroy(c->s_copy);
   cudaGetLastError();
@@ -652,9 +687,9 @@ static int push_read_chunk(links_ctx* c, const char* seq, const uint8_t* dev_seq
                    b.n_seq, b.n_tiles, b.flags.as<uint32_t>(), b.vs.as<unsigned long long>(), b.vrank.as<uint32_t>(),
                    first_read_idx};
       DistParams dp{c->d_dist.as<uint32_t>(), c->d_step.as<uint32_t>(), c->prm.n_dist, c->prm.offset};
-      extract_kernel<<<grid_for(c, b.n_tiles, 1, 8), kCtaThreads, c->prm.k * 4 * sizeof(ulonglong2), c->s_compute>>>(
+      extract_kernel<<<grid_for(c, b.n_tiles, 1, c->extract_ctas_per_sm), kCtaThreads, extract_smem_bytes(c->prm.k), c->s_compute>>>(
         rb, dp, int(c->prm.k), c->kseed, c->d_tab.as<ulonglong2>(), bloom_view(c),
-        pair_view(c->d_pairs.as<PairSlot>(), c->pair_cap), c->d_ctr.as<Counters>());
+        pair_view(c->d_pairs.as<PairSlot>(), c->pair_cap, c->d_pair_list.as<ulonglong2>()), c->d_ctr.as<Counters>());
       c->launches++;
       c->extract_launches++;
       CU(c, cudaGetLastError());
@@ -830,7 +865,7 @@ int links_finalize(links_ctx* c, links_row** rows_out, uint64_t* n_rows_out, lin
 
   const int tb = log2_ceil(uint64_t(c->n_tigs_seen) * 2 + 2);
   DevBuf (&d_keys)[2] = c->f_keys; DevBuf (&d_vals)[2] = c->f_vals;
-  DevBuf &d_issues = c->f_issues, &d_tiglen = c->f_tiglen, &d_hist = c->f_hist, &d_scan_tmp = c->f_scan_tmp, &d_flags = c->f_flags,
+  DevBuf &d_issues = c->f_issues, &d_tiglen = c->f_tiglen, &d_scan_tmp = c->f_scan_tmp, &d_flags = c->f_flags,
          &d_total = c->f_total, &d_okeys = c->f_okeys, &d_olinks = c->f_olinks, &d_ogaps = c->f_ogaps;
   const uint64_t row_cap = std::max<uint64_t>(n_unique, 1);
   uint64_t issue_cap = c->issue_cap_hint;
@@ -844,12 +879,13 @@ int links_finalize(links_ctx* c, links_row** rows_out, uint64_t* n_rows_out, lin
     // reset the stage-4 counters (keeps the stage-2/3 ones)
     CU(c, cudaMemsetAsync(reinterpret_cast<char*>(c->d_ctr.p) + offsetof(Counters, ct_ok_pairs), 0,
                           sizeof(Counters) - offsetof(Counters, ct_ok_pairs), s));
-    if (c->pair_cap) {
+    if (c->pair_cap && n_unique) {
       Span sp(c, F_CLASSIFY, s);
       ClassifyParams cp{c->d_dist.as<uint32_t>(), c->d_minallowed.as<int32_t>(), c->prm.n_dist, d_tiglen.as<uint32_t>(), tb,
                         d_keys[0].as<uint64_t>(), d_vals[0].as<int32_t>(), row_cap, d_issues.as<IssueRec>(), issue_cap};
-      classify_kernel<<<grid_for(c, c->pair_cap, kCtaThreads, 8), kCtaThreads, 0, s>>>(
-        c->d_pairs.as<PairSlot>(), c->pair_cap, table_view(c), cp, int(c->prm.k), c->d_ctr.as<Counters>());
+      classify_kernel<<<grid_for(c, n_unique, kCtaThreads, 8), kCtaThreads, 0, s>>>(
+        pair_view(c->d_pairs.as<PairSlot>(), c->pair_cap, c->d_pair_list.as<ulonglong2>()), n_unique, table_view(c), cp,
+        int(c->prm.k), c->d_ctr.as<Counters>());
       c->launches++;
       CU(c, cudaGetLastError());
     }
@@ -862,27 +898,15 @@ int links_finalize(links_ctx* c, links_row** rows_out, uint64_t* n_rows_out, lin
   const uint64_t n_rows_raw = h.n_rows;
   if (n_rows_raw > row_cap) return fail(c, LINKS_E_CUDA, "links_finalize: internal row overflow");
 
-  // ---- sort + reduce-by-key on the packed row key (K5b)
-  std::vector<uint64_t> hk; std::vector<unsigned long long> hl; std::vector<long long> hg;
-  uint32_t n_seg = 0;
+  // ---- K5b: sort + reduce-by-key on the packed row key, then mirror expansion + a final small sort
+  std::vector<FinalRow> hrows;
+  uint32_t n_seg = 0, n_out32 = 0;
+  const int key_bits = 3 + 2 * tb;
   if (n_rows_raw) {
     Span sp(c, F_SORT, s);
-    const int key_bits = 3 + 2 * tb;
-    const uint32_t n_blocks = uint32_t((n_rows_raw + kSortTile - 1) / kSortTile);
-    CU(c, d_keys[1].ensure(n_rows_raw * 8)); CU(c, d_vals[1].ensure(n_rows_raw * 4));
-    CU(c, d_hist.ensure(uint64_t(kRadix) * n_blocks * 4));
     int cur = 0;
-    for (int shift = 0; shift < key_bits; shift += 8) {
-      radix_hist_kernel<<<n_blocks, kSortThreads, 0, s>>>(d_keys[cur].as<uint64_t>(), n_rows_raw, shift, d_hist.as<uint32_t>(), n_blocks);
-      c->launches++;
-      rc = device_scan(c, s, d_hist.as<uint32_t>(), uint64_t(kRadix) * n_blocks, d_hist.as<uint32_t>(), d_scan_tmp, d_total.as<uint32_t>());
-      if (rc) return rc;
-      radix_scatter_kernel<<<n_blocks, kSortThreads, 0, s>>>(d_keys[cur].as<uint64_t>(), d_vals[cur].as<int32_t>(), n_rows_raw, shift,
-                                                            d_hist.as<uint32_t>(), n_blocks, d_keys[cur ^ 1].as<uint64_t>(),
-                                                            d_vals[cur ^ 1].as<int32_t>());
-      c->launches++;
-      cur ^= 1;
-    }
+    rc = radix_sort_pairs(c, s, d_keys, d_vals, n_rows_raw, key_bits, cur);
+    if (rc) return rc;
     CU(c, d_flags.ensure(n_rows_raw * 4));
     head_flags_kernel<<<unsigned((n_rows_raw + 255) / 256), 256, 0, s>>>(d_keys[cur].as<uint64_t>(), n_rows_raw, d_flags.as<uint32_t>());
     c->launches++;
@@ -898,45 +922,45 @@ int links_finalize(links_ctx* c, links_row** rows_out, uint64_t* n_rows_out, lin
                                                                    d_flags.as<uint32_t>(), d_okeys.as<uint64_t>(),
                                                                    d_olinks.as<unsigned long long>(), d_ogaps.as<unsigned long long>());
     c->launches++;
+    // every canonical row stands for two tsv rows (add_to_pair_map, reference :717-761): expand, sort, gather
+    n_out32 = n_seg * 2;
+    CU(c, d_keys[0].ensure(uint64_t(n_out32) * 8)); CU(c, d_vals[0].ensure(uint64_t(n_out32) * 4));
+    mirror_expand_kernel<<<(n_seg + 255) / 256, 256, 0, s>>>(d_okeys.as<uint64_t>(), n_seg, tb, d_keys[0].as<uint64_t>(), d_vals[0].as<int32_t>());
+    c->launches++;
+    cur = 0;
+    rc = radix_sort_pairs(c, s, d_keys, d_vals, n_out32, key_bits, cur);
+    if (rc) return rc;
+    CU(c, c->f_final.ensure(uint64_t(n_out32) * sizeof(FinalRow)));
+    gather_rows_kernel<<<(n_out32 + 255) / 256, 256, 0, s>>>(d_keys[cur].as<uint64_t>(), d_vals[cur].as<int32_t>(), n_out32,
+                                                           d_olinks.as<unsigned long long>(), d_ogaps.as<unsigned long long>(),
+                                                           c->f_final.as<FinalRow>());
+    c->launches++;
     CU(c, cudaGetLastError());
-    hk.resize(n_seg); hl.resize(n_seg); hg.resize(n_seg);
+    hrows.resize(n_out32);
   }
   std::vector<IssueRec> hi(h.n_issues);
   {
     Span sp(c, F_D2H, s);
-    if (n_seg) {
-      CU(c, cudaMemcpyAsync(hk.data(), d_okeys.p, uint64_t(n_seg) * 8, cudaMemcpyDeviceToHost, s));
-      CU(c, cudaMemcpyAsync(hl.data(), d_olinks.p, uint64_t(n_seg) * 8, cudaMemcpyDeviceToHost, s));
-      CU(c, cudaMemcpyAsync(hg.data(), d_ogaps.p, uint64_t(n_seg) * 8, cudaMemcpyDeviceToHost, s));
-    }
+    if (n_out32) CU(c, cudaMemcpyAsync(hrows.data(), c->f_final.p, uint64_t(n_out32) * sizeof(FinalRow), cudaMemcpyDeviceToHost, s));
     if (h.n_issues) CU(c, cudaMemcpyAsync(hi.data(), d_issues.p, h.n_issues * sizeof(IssueRec), cudaMemcpyDeviceToHost, s));
   }
   CU(c, cudaStreamSynchronize(s));
 
-  // ---- host: expand each canonical row into the two rows add_to_pair_map writes (reference :717-761)
+  // ---- host: unpack (rows arrive in (bin, tig_a, rev_a, tig_b, rev_b) order: the packed key is monotone in it)
   static const int32_t bin_of_code[5] = {-1, 10, 500, 5000, 10000};
-  const uint64_t n_out = uint64_t(n_seg) * 2;
+  const uint64_t n_out = n_out32;
   links_row* rows = static_cast<links_row*>(malloc(std::max<uint64_t>(n_out, 1) * sizeof(links_row)));
   if (!rows) return fail(c, LINKS_E_NOMEM, "links_finalize: out of host memory");
   const uint64_t tmask = (1ull << tb) - 1;
-  for (uint32_t i = 0; i < n_seg; ++i) {
-    const uint64_t key = hk[i];
+  for (uint64_t i = 0; i < n_out; ++i) {
+    const uint64_t key = hrows[i].key;
     const uint32_t B = uint32_t(key & tmask), A = uint32_t((key >> tb) & tmask), bc = uint32_t(key >> (2 * tb));
     links_row r;
     memset(&r, 0, sizeof r);
-    r.bin = bin_of_code[bc]; r.links = hl[i]; r.gaps = hg[i];
+    r.bin = bin_of_code[bc]; r.links = hrows[i].links; r.gaps = hrows[i].gaps;
     r.tig_a = A >> 1; r.rev_a = A & 1; r.tig_b = B >> 1; r.rev_b = B & 1;
-    rows[2 * i] = r;
-    r.tig_a = B >> 1; r.rev_a = (B & 1) ^ 1; r.tig_b = A >> 1; r.rev_b = (A & 1) ^ 1;
-    rows[2 * i + 1] = r;
+    rows[i] = r;
   }
-  std::sort(rows, rows + n_out, [](const links_row& a, const links_row& b) {
-    if (a.bin != b.bin) return a.bin < b.bin;
-    if (a.tig_a != b.tig_a) return a.tig_a < b.tig_a;
-    if (a.rev_a != b.rev_a) return a.rev_a < b.rev_a;
-    if (a.tig_b != b.tig_b) return a.tig_b < b.tig_b;
-    return a.rev_b < b.rev_b;
-  });
   links_issue* issues = nullptr;
   if (issues_out) {
     issues = static_cast<links_issue*>(malloc(std::max<uint64_t>(hi.size(), 1) * sizeof(links_issue)));
@@ -1050,12 +1074,11 @@ int links_pairs_download(links_ctx* c, uint64_t* h_a, uint64_t* h_b, uint32_t* d
   if (!h_a || !h_b || !d_idx) return LINKS_OK;
   if (cap < h.n_unique) return fail(c, LINKS_E_INVAL, "links_pairs_download: cap %llu < %llu", (unsigned long long)cap, (unsigned long long)h.n_unique);
   if (!h.n_unique) return LINKS_OK;
-  DevBuf d_out, d_cnt;
-  struct Cleanup { DevBuf &a, &b; ~Cleanup() { a.release(); b.release(); } } cl{d_out, d_cnt};
-  CU(c, d_out.ensure(h.n_unique * 24)); CU(c, d_cnt.ensure(8));
-  CU(c, cudaMemsetAsync(d_cnt.p, 0, 8, c->s_compute));
-  pair_compact_kernel<<<grid_for(c, c->pair_cap, 256, 8), 256, 0, c->s_compute>>>(c->d_pairs.as<PairSlot>(), c->pair_cap, d_out.as<uint64_t>(),
-                                                                                   h.n_unique, d_cnt.as<unsigned long long>());
+  DevBuf d_out;
+  struct Cleanup { DevBuf& a; ~Cleanup() { a.release(); } } cl{d_out};
+  CU(c, d_out.ensure(h.n_unique * 24));
+  pair_export_kernel<<<grid_for(c, h.n_unique, 256, 8), 256, 0, c->s_compute>>>(
+    pair_view(c->d_pairs.as<PairSlot>(), c->pair_cap, c->d_pair_list.as<ulonglong2>()), h.n_unique, d_out.as<uint64_t>());
   c->launches++;
   CU(c, cudaGetLastError());
   std::vector<uint64_t> tmp(h.n_unique * 3);

@@ -135,6 +135,31 @@ __device__ __forceinline__ bool bloom_contains(const BloomView& bf, uint64_t fwd
   return true;
 }
 
+__device__ __forceinline__ uint32_t bloom_bit(const BloomView& bf, uint64_t h0, uint64_t kseed, uint32_t i)
+{
+  const uint64_t n = bloom_mod(multihash_i(h0, kseed, i), bf);
+  return (__ldg(bf.words + (n >> 5)) >> (n & 31)) & 1u;
+}
+
+// Probes [i0, i1) of one k-mer issued together (independent loads in flight), instead of the
+// reference's one-at-a-time early-exit loop (bloom_filter.hpp:648-659).  Same answer; `probes`
+// is advanced by the number of probes the sequential loop would have made (roofline accounting).
+__device__ __forceinline__ bool bloom_probe_range(const BloomView& bf, uint64_t h0, uint64_t kseed, uint32_t i0, uint32_t i1,
+                                                  uint32_t& probes)
+{
+  while (i0 < i1) {
+    const uint32_t n = min(i1 - i0, 8u);
+    uint32_t miss = 0;
+#pragma unroll
+    for (uint32_t j = 0; j < 8; ++j)
+      if (j < n) miss |= (bloom_bit(bf, h0, kseed, i0 + j) ^ 1u) << j;
+    if (miss) { probes += __ffs(miss); return false; }
+    probes += n;
+    i0 += n;
+  }
+  return true;
+}
+
 __device__ __forceinline__ void bloom_insert(const BloomView& bf, uint64_t fwd, uint64_t rev, uint64_t kseed)
 {
   const uint64_t h0 = rev < fwd ? rev : fwd;
