@@ -222,7 +222,7 @@ def main_ours(args, rank: int, world: int, local_rank: int):
     import torch
     import torch.distributed as dist
 
-    from links_b200 import Links, LinksOptions, _abi, bf_size
+    from links_b200 import Links, LinksOptions, _abi, bf_size, multi
 
     if not torch.cuda.is_available():
         raise SystemExit("bench.py: no CUDA device; the hot path has no CPU fallback (use --impl reference for the CPU arm)")
@@ -250,20 +250,38 @@ def main_ours(args, rank: int, world: int, local_rank: int):
 
     state = {}
 
+    dev = torch.device("cuda", local_rank)
+    first_read = rank * (1 << 22)  # disjoint global read ordinals per rank (order key, n_dist > 1)
+
     def step(resident: bool):
         L.reset()
-        L.bf_alloc(bf_bytes, hash_num)
-        if resident:
+        if world > 1 and rank != 0:
+            pass  # the filter arrives by broadcast below
+        else:
+            L.bf_alloc(bf_bytes, hash_num)
+        if world > 1:
+            # rank 0 builds the Bloom filter from the contigs; NCCL broadcast replicates it (north_star);
+            # the contig k-mer table is rebuilt per rank from the replicated contigs (cheaper than moving it)
+            if rank == 0:
+                (L.push_contigs_dev(d_contigs.data_ptr(), contigs.off, 1) if resident
+                 else L.push_contigs_raw(pc_seq, pc_off, contigs.n, 1))
+            multi.replicate_bloom(L, bf_bytes, hash_num, dist, dev)
+            if rank != 0:
+                (L.push_contigs_dev(d_contigs.data_ptr(), contigs.off, 1) if resident
+                 else L.push_contigs_raw(pc_seq, pc_off, contigs.n, 1))
+        elif resident:
             L.push_contigs_dev(d_contigs.data_ptr(), contigs.off, 1)
-            L.push_reads_dev(d_reads.data_ptr(), reads.off, 0)
         else:
             L.push_contigs_raw(pc_seq, pc_off, contigs.n, 1)
-            L.push_reads_raw(pr_seq, pr_off, reads.n, 0)
+        if resident:
+            L.push_reads_dev(d_reads.data_ptr(), reads.off, first_read)
+        else:
+            L.push_reads_raw(pr_seq, pr_off, reads.n, first_read)
         if world > 1:
-            exchange_pairs(L, rank, world, torch, dist)
+            state["exchange"] = multi.exchange_pairs(L, dist, dev)
         rows, issues, stats = L.finalize()
         if world > 1:
-            rows = merge_rows(rows, rank, world, torch, dist)
+            rows = multi.gather_rows(rows, dist, dev)
         state["rows"], state["issues"], state["stats"] = rows, issues, stats
 
     def timed(resident: bool, steps: int, warmup: int):
@@ -329,7 +347,9 @@ def main_ours(args, rank: int, world: int, local_rank: int):
                        "candidate_pairs_per_gpu": cand, "survivors": stats["n_survivors"], "unique_pairs": stats["n_unique_pairs"],
                        "bf_probes": stats["n_bf_probes"], "rows": n_rows, "rows_digest": digest_res,
                        "l2": "inputs (250 MB reads, GB-scale pair set and contig table) exceed the 126 MB L2; no flush",
-                       "sharding": "reads by rank, contigs replicated" if world > 1 else "single GPU"},
+                       "sharding": ("reads by rank (each rank its own 50x read set), Bloom filter NCCL-broadcast from rank 0, contigs replicated, "
+                                    "distinct pairs routed by one NCCL all-to-all keyed on hash(h_a,h_b), rows summed on rank 0") if world > 1 else "single GPU",
+                       "exchange_rank0": state.get("exchange")},
             "e2e": {"value": cand_total / (ms_e2e * 1e-3), "unit": UNIT, "ms_per_step": ms_e2e, "h2d_bytes_per_step": int(h2d_bytes),
                     "d2h_bytes_per_step": int(d2h_bytes)},
             "gpu_launches": int(tm_res["launches"]),
@@ -358,12 +378,56 @@ def main_ours(args, rank: int, world: int, local_rank: int):
         dist.destroy_process_group()
 
 
-def exchange_pairs(L, rank, world, torch, dist):
-    raise SystemExit("multi-GPU exchange is not wired yet in this revision")
+def check_sharding(args, rank: int, world: int, local_rank: int):
+    """Strong-scaling parity: the SAME reads split over the ranks (contiguous shards, global read
+    ordinals) must give, after the pair exchange and the row merge, exactly the rows one GPU
+    computes for the whole job.  Prints one JSON line on rank 0; not a timing run."""
+    import torch
+    import torch.distributed as dist
 
-
-def merge_rows(rows, rank, world, torch, dist):
-    raise SystemExit("multi-GPU exchange is not wired yet in this revision")
+    from links_b200 import Links, LinksOptions, bf_size, multi
+    from links_b200.seqio import SeqSet
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    contigs, reads, k, d, t = load_workload(args.workload, args.scale)
+    file_bytes = int(contigs.off[-1]) + contigs.n * (2 + len(str(contigs.n)))
+    _m, bf_bytes, hash_num = bf_size(file_bytes, 0.001)
+    lo, hi = reads.n * rank // world, reads.n * (rank + 1) // world
+    with Links(LinksOptions(k=k, distances=d, step_sizes=t, device=local_rank)) as L:
+        if rank == 0:
+            L.bf_alloc(bf_bytes, hash_num)
+            L.push_contigs(contigs)
+        if world > 1:
+            multi.replicate_bloom(L, bf_bytes, hash_num, dist, dev)
+            if rank != 0:
+                L.push_contigs(contigs)
+        L.push_reads(SeqSet(reads.seq, reads.off[lo:hi + 1], []), first_read_idx=lo)
+        ex = multi.exchange_pairs(L, dist, dev) if world > 1 else {}
+        rows, issues, stats = L.finalize()
+        if world > 1:
+            rows = multi.gather_rows(rows, dist, dev)
+    tot = torch.tensor([stats["n_candidates"], stats["n_unique_pairs"], len(issues)], dtype=torch.int64, device=dev)
+    if world > 1:
+        dist.all_reduce(tot)
+    if rank == 0:
+        with Links(LinksOptions(k=k, distances=d, step_sizes=t, device=local_rank)) as L:
+            L.bf_alloc(bf_bytes, hash_num)
+            L.push_contigs(contigs)
+            L.push_reads(reads)
+            rows1, issues1, stats1 = L.finalize()
+        ok = (rows_digest(rows) == rows_digest(rows1) and int(tot[0]) == stats1["n_candidates"]
+              and int(tot[1]) == stats1["n_unique_pairs"] and int(tot[2]) == len(issues1))
+        print(json.dumps({"check_sharding": "ok" if ok else "MISMATCH", "n_gpus": world, "workload": args.workload, "scale": args.scale,
+                          "rows": len(rows1), "rows_digest_sharded": rows_digest(rows), "rows_digest_single": rows_digest(rows1),
+                          "candidates": [int(tot[0]), stats1["n_candidates"]], "unique_pairs": [int(tot[1]), stats1["n_unique_pairs"]],
+                          "issues": [int(tot[2]), len(issues1)], "exchange_rank0": ex}))
+        if not ok:
+            raise SystemExit(1)
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
 
 
 def main():
@@ -376,10 +440,13 @@ def main():
     ap.add_argument("--scale", type=float, default=1.0)
     ap.add_argument("--ref-candidates", type=int, default=4_000_000, help="size of the bounded CPU sample (candidate pairs)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--check-sharding", action="store_true", help="parity of the N-rank path against one GPU (same reads split over ranks)")
     args = ap.parse_args()
     rank, world, local_rank = env_int("RANK", 0), env_int("WORLD_SIZE", 1), env_int("LOCAL_RANK", 0)
     if args.impl == "reference":
         main_reference(args, rank, world)
+    elif args.check_sharding:
+        check_sharding(args, rank, world, local_rank)
     else:
         main_ours(args, rank, world, local_rank)
 

@@ -147,14 +147,31 @@ void links_free_result(links_row* rows, links_issue* issues);
 int links_format_row(const links_row* r, char* dst, size_t cap);
 int links_format_issue(const links_issue* r, char* dst, size_t cap);
 
-/* ---- multi-GPU (reads sharded over ranks).  After every rank has pushed its share
- * of the reads: export the rank's unique pair records bucketed by destination rank, exchange
- * them with any all-to-all (NCCL through torch.distributed in bench.py), import, finalize, and
- * sum the per-rank rows.  Records are 24 bytes: {h_a, h_b, order_key}. */
-int links_pairs_export(links_ctx* ctx, uint32_t n_ranks, void** dev_records, uint64_t* counts /* n_ranks */);
+/* ---- multi-GPU (reads sharded over ranks, contigs replicated).  The reference has no
+ * counterpart: its mate_pair map (src/LINKS.hpp:138-147,354-378) lives in one address space.
+ * After every rank has pushed its share of the reads, each distinct ordered (h_a,h_b) must end
+ * up on exactly ONE rank before link counting (set semantics, first distance wins):
+ *   export : the rank's distinct pairs as 24-byte records {h_a, h_b, order_key}, grouped by owner
+ *            rank (a hash of (h_a,h_b)); counts[r] = records owned by rank r
+ *   clear  : empty this rank's pair set (allocations kept)
+ *   import : insert received records (device memory) into the pair set, minimum order key wins
+ * then links_finalize per rank and sum the ranks' rows by key (rows of different ranks overlap).
+ * The transport between export and import is the caller's: one all-to-all (NCCL in bench.py).
+ * Global read ordinals (first_read_idx) must be disjoint across ranks when n_dist > 1. */
+#define LINKS_PAIR_RECORD_BYTES 24u
+#define LINKS_MAX_RANKS 256u
+/* dev_dst == NULL: only fill counts[0..n_ranks).  Otherwise dev_dst (device memory, room for
+ * cap_records records) receives the records, bucket r starting at sum(counts[0..r)). */
+int links_pairs_export(links_ctx* ctx, uint32_t n_ranks, void* dev_dst, uint64_t cap_records, uint64_t* counts);
 int links_pairs_import(links_ctx* ctx, const void* dev_records, uint64_t n_records);
-/* Replace this context's pair set by an empty one (used between export and import). */
 int links_pairs_clear(links_ctx* ctx);
+/* Owner rank of a pair, the same function the export kernel uses (for hosts that route themselves). */
+uint32_t links_pair_owner(uint64_t h_a, uint64_t h_b, uint32_t n_ranks);
+/* Bloom filter replication: copy the filter's bit array device-to-device out of / into the
+ * context, so a rank that built it can broadcast it (NCCL) and the others adopt it instead of
+ * rebuilding.  links_bf_load_dev == links_bf_load with a device source. */
+int links_bf_download_dev(links_ctx* ctx, void* dev_dst);
+int links_bf_load_dev(links_ctx* ctx, const void* dev_bits, uint64_t bytes, uint32_t hash_num);
 
 /* ---- inspection utilities (used by the parity tests; thin wrappers over the same kernels) ---- */
 /* fwd/rev ntHash2 of every k-mer start of one sequence (btllib NtHash, nthash.hpp:1265-1338);
@@ -166,8 +183,7 @@ int links_bf_contains(links_ctx* ctx, const uint64_t* fwd, const uint64_t* rev, 
 int links_pairs_download(links_ctx* ctx, uint64_t* h_a, uint64_t* h_b, uint32_t* d_idx, uint64_t cap, uint64_t* n);
 /* Device time (ms) and launch counts accumulated per kernel family since create / last reset. */
 typedef struct links_timing {
-  float ms_h2d, ms_pack, ms_bf_build, ms_table_build, ms_extract, ms_classify, ms_sort_reduce, ms_d2h, ms_grow;
-  uint32_t pad_;
+  float ms_h2d, ms_pack, ms_bf_build, ms_table_build, ms_extract, ms_classify, ms_sort_reduce, ms_d2h, ms_grow, ms_exchange;
   uint64_t launches;         /* all kernels launched by this library */
   uint64_t extract_launches; /* launches of the dominant kernel (extract_kernel) */
 } links_timing;

@@ -62,7 +62,7 @@ class LinksStats(C.Structure):
 class LinksTiming(C.Structure):
     _fields_ = [(n, C.c_float) for n in (
         "ms_h2d", "ms_pack", "ms_bf_build", "ms_table_build", "ms_extract", "ms_classify", "ms_sort_reduce",
-        "ms_d2h", "ms_grow")] + [("pad_", C.c_uint32), ("launches", C.c_uint64), ("extract_launches", C.c_uint64)]
+        "ms_d2h", "ms_grow", "ms_exchange")] + [("launches", C.c_uint64), ("extract_launches", C.c_uint64)]
 
 
 # name -> (restype, argtypes); this table is also what tests check against the header
@@ -89,7 +89,10 @@ SIGNATURES = {
     "links_free_result": (None, [C.POINTER(LinksRow), C.POINTER(LinksIssue)]),
     "links_format_row": (C.c_int, [C.POINTER(LinksRow), C.c_char_p, C.c_size_t]),
     "links_format_issue": (C.c_int, [C.POINTER(LinksIssue), C.c_char_p, C.c_size_t]),
-    "links_pairs_export": (C.c_int, [C.c_void_p, C.c_uint32, C.POINTER(C.c_void_p), C.POINTER(C.c_uint64)]),
+    "links_pairs_export": (C.c_int, [C.c_void_p, C.c_uint32, C.c_void_p, C.c_uint64, C.POINTER(C.c_uint64)]),
+    "links_pair_owner": (C.c_uint32, [C.c_uint64, C.c_uint64, C.c_uint32]),
+    "links_bf_download_dev": (C.c_int, [C.c_void_p, C.c_void_p]),
+    "links_bf_load_dev": (C.c_int, [C.c_void_p, C.c_void_p, C.c_uint64, C.c_uint32]),
     "links_pairs_import": (C.c_int, [C.c_void_p, C.c_void_p, C.c_uint64]),
     "links_pairs_clear": (C.c_int, [C.c_void_p]),
     "links_kmer_hashes": (C.c_int, [C.c_void_p, C.c_void_p, C.c_uint64, C.c_void_p, C.c_void_p, C.c_void_p]),

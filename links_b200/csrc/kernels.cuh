@@ -754,6 +754,103 @@ __global__ void bf_contains_kernel(BloomView bf, uint64_t kseed, const uint64_t*
   out[i] = bloom_contains(bf, fwd[i], rev[i], kseed, probes);
 }
 
+// ------------------------------------------------------------------ multi-GPU exchange
+//
+// Reads are sharded over ranks, so the same ordered (h_a,h_b) may sit in several ranks' pair sets;
+// mate_pair's set semantics (ref src/LINKS.hpp:370-373) need one owner per pair.  Owner =
+// dest_rank(h_a,h_b).  The low half of the mixed hash picks the rank, the high bits pick the slot
+// (slot_hash2 >> shift), so an owner's imported pairs still spread over its whole table.
+__host__ __device__ __forceinline__ uint32_t dest_rank_of_hash(uint64_t mixed, uint32_t n_ranks)
+{
+#ifdef __CUDA_ARCH__
+  // explicit mul.hi: nvcc 12.9 folded the 64-bit form ((lo32 * n) >> 32) << 2 of the shared-memory
+  // index into lo32 * ((n << 2) >> 32) == 0 in pair_bucket_count_kernel (seen in the SASS)
+  return __umulhi(uint32_t(mixed), n_ranks);
+#else
+  return uint32_t((uint64_t(uint32_t(mixed)) * uint64_t(n_ranks)) >> 32);
+#endif
+}
+__device__ __forceinline__ uint32_t dest_rank(uint64_t a, uint64_t b, uint32_t n_ranks)
+{
+  return dest_rank_of_hash(slot_hash2(a, b), n_ranks);
+}
+
+constexpr int kMaxRanks = 256;
+
+// pass 1: records per destination rank (block-local histogram, one global atomic per block and rank)
+__global__ void __launch_bounds__(kCtaThreads) pair_bucket_count_kernel(const ulonglong2* __restrict__ list, uint64_t n,
+                                                                        uint32_t n_ranks, unsigned long long* __restrict__ counts)
+{
+  __shared__ uint32_t s_hist[kMaxRanks];
+  for (uint32_t i = threadIdx.x; i < n_ranks; i += blockDim.x) s_hist[i] = 0;
+  __syncthreads();
+  for (uint64_t i = uint64_t(blockIdx.x) * blockDim.x + threadIdx.x; i < n; i += uint64_t(gridDim.x) * blockDim.x) {
+    const ulonglong2 hk = __ldg(list + i);
+    atomicAdd(&s_hist[dest_rank(hk.x, hk.y, n_ranks)], 1u);
+  }
+  __syncthreads();
+  for (uint32_t i = threadIdx.x; i < n_ranks; i += blockDim.x)
+    if (s_hist[i]) atomicAdd(counts + i, (unsigned long long)s_hist[i]);
+}
+
+// pass 2: scatter {a, b, okey} records into per-rank buckets.  cursors[] start at the bucket
+// offsets; every block reserves one range per rank per tile, lanes take block-local offsets.
+__global__ void __launch_bounds__(kCtaThreads) pair_bucket_scatter_kernel(PairView pv, uint64_t n, uint32_t n_ranks, int with_okey,
+                                                                          unsigned long long* __restrict__ cursors,
+                                                                          uint64_t* __restrict__ out3)
+{
+  __shared__ uint32_t s_hist[kMaxRanks];
+  __shared__ unsigned long long s_base[kMaxRanks];
+  const uint64_t stride = uint64_t(gridDim.x) * blockDim.x;
+  const uint64_t n_round = (n + stride - 1) / stride * stride;
+  for (uint64_t i = uint64_t(blockIdx.x) * blockDim.x + threadIdx.x; i < n_round; i += stride) {
+    for (uint32_t r = threadIdx.x; r < n_ranks; r += blockDim.x) s_hist[r] = 0;
+    __syncthreads();
+    ulonglong2 hk = make_ulonglong2(0, 0);
+    uint32_t dst = 0, local = 0;
+    if (i < n) {
+      hk = __ldg(pv.list + i);
+      dst = dest_rank(hk.x, hk.y, n_ranks);
+      local = atomicAdd(&s_hist[dst], 1u);
+    }
+    __syncthreads();
+    for (uint32_t r = threadIdx.x; r < n_ranks; r += blockDim.x)
+      if (s_hist[r]) s_base[r] = atomicAdd(cursors + r, (unsigned long long)s_hist[r]);
+    __syncthreads();
+    if (i < n) {
+      const uint64_t o = (s_base[dst] + local) * 3;
+      out3[o] = hk.x; out3[o + 1] = hk.y;
+      out3[o + 2] = with_okey ? pair_okey(pv, hk.x, hk.y) : 0ull;
+    }
+    __syncthreads();
+  }
+}
+
+// insert received {a, b, okey} records; fresh pairs are appended to the dense list (one global
+// atomic per warp).  Same first-wins rule as extract_kernel: minimum order key.
+__global__ void __launch_bounds__(kCtaThreads) pair_import_kernel(const uint64_t* __restrict__ rec3, uint64_t n, PairView pv,
+                                                                  int multi_d, Counters* __restrict__ ctr)
+{
+  const int lane = threadIdx.x & 31;
+  const uint64_t stride = uint64_t(gridDim.x) * blockDim.x;
+  const uint64_t n_round = (n + stride - 1) / stride * stride; // whole warps stay in the loop
+  for (uint64_t i = uint64_t(blockIdx.x) * blockDim.x + threadIdx.x; i < n_round; i += stride) {
+    bool fresh = false;
+    uint64_t a = 0, b = 0;
+    if (i < n) {
+      a = __ldg(rec3 + i * 3); b = __ldg(rec3 + i * 3 + 1);
+      fresh = pair_insert(pv, a, b, __ldg(rec3 + i * 3 + 2), multi_d != 0);
+    }
+    const uint32_t m = __ballot_sync(0xffffffffu, fresh);
+    if (m) {
+      unsigned long long base = 0;
+      if (lane == __ffs(m) - 1) base = atomicAdd(&ctr->n_unique, (unsigned long long)__popc(m));
+      base = __shfl_sync(0xffffffffu, base, __ffs(m) - 1);
+      if (fresh) pv.list[base + __popc(m & ((1u << lane) - 1u))] = make_ulonglong2(a, b);
+    }
+  }
+}
+
 // export the dense pair list with order keys: out[] = {a, b, okey}
 __global__ void pair_export_kernel(PairView pv, uint64_t n_pairs, uint64_t* __restrict__ out3)
 {

@@ -51,7 +51,7 @@ struct SeqBatchDev { // device-resident packed sequences of one push/chunk
   void release() { packed.release(); inv.release(); off.release(); segs.release(); flags.release(); vs.release(); vrank.release(); }
 };
 
-enum Family { F_H2D, F_PACK, F_BF, F_TABLE, F_EXTRACT, F_CLASSIFY, F_SORT, F_D2H, F_GROW, F_COUNT };
+enum Family { F_H2D, F_PACK, F_BF, F_TABLE, F_EXTRACT, F_CLASSIFY, F_SORT, F_D2H, F_GROW, F_EXCHANGE, F_COUNT };
 
 struct TimedSpan { int fam; cudaEvent_t a, b; };
 
@@ -118,7 +118,7 @@ struct links_ctx {
 
   // stage-4 scratch (kept across links_reset so repeated jobs do not re-allocate)
   DevBuf f_final;
-  DevBuf f_keys[2], f_vals[2], f_issues, f_tiglen, f_hist, f_scan_tmp, f_flags, f_total, f_okeys, f_olinks, f_ogaps;
+  DevBuf f_keys[2], f_vals[2], f_issues, f_tiglen, f_hist, f_scan_tmp, f_flags, f_total, f_okeys, f_olinks, f_ogaps, f_exch;
   uint64_t issue_cap_hint = 1ull << 16;
 
   // timing
@@ -548,7 +548,7 @@ void links_destroy(links_ctx* c)
   for (int i = 0; i < links_ctx::kSnaps; ++i) if (c->ev_snap[i]) cudaEventDestroy(c->ev_snap[i]);
   if (c->h_snap) cudaFreeHost(c->h_snap);
   for (DevBuf* b : {&c->f_keys[0], &c->f_keys[1], &c->f_vals[0], &c->f_vals[1], &c->f_issues, &c->f_tiglen, &c->f_hist,
-                    &c->f_scan_tmp, &c->f_flags, &c->f_total, &c->f_okeys, &c->f_olinks, &c->f_ogaps, &c->f_final}) b->release();
+                    &c->f_scan_tmp, &c->f_flags, &c->f_total, &c->f_okeys, &c->f_olinks, &c->f_ogaps, &c->f_final, &c->f_exch}) b->release();
   c->d_tab.release(); c->d_dist.release(); c->d_step.release(); c->d_minallowed.release();
   c->d_bloom.release(); c->d_pairs.release(); c->d_pair_list.release(); c->d_ctr.release(); c->d_table.release();
   if (c->s_compute && c->own_compute_stream) cudaStreamDestroy(c->s_compute);
@@ -816,6 +816,7 @@ int links_get_timing(links_ctx* c, links_timing* t, int reset)
   t->ms_h2d = c->fam_ms[F_H2D]; t->ms_pack = c->fam_ms[F_PACK]; t->ms_bf_build = c->fam_ms[F_BF];
   t->ms_table_build = c->fam_ms[F_TABLE]; t->ms_extract = c->fam_ms[F_EXTRACT]; t->ms_classify = c->fam_ms[F_CLASSIFY];
   t->ms_sort_reduce = c->fam_ms[F_SORT]; t->ms_d2h = c->fam_ms[F_D2H]; t->ms_grow = c->fam_ms[F_GROW];
+  t->ms_exchange = c->fam_ms[F_EXCHANGE];
   t->launches = c->launches; t->extract_launches = c->extract_launches;
   if (reset) { for (auto& m : c->fam_ms) m = 0; c->launches = 0; c->extract_launches = 0; }
   return LINKS_OK;
@@ -1093,19 +1094,117 @@ int links_pairs_download(links_ctx* c, uint64_t* h_a, uint64_t* h_b, uint32_t* d
 
 // ---------------------------------------------------------------- multi-GPU exchange hooks
 
-int links_pairs_export(links_ctx* c, uint32_t n_ranks, void** dev_records, uint64_t* counts)
+uint32_t links_pair_owner(uint64_t h_a, uint64_t h_b, uint32_t n_ranks)
 {
-  (void)n_ranks; (void)dev_records; (void)counts;
-  return fail(c, LINKS_E_INVAL, "links_pairs_export: not implemented yet");
+  uint64_t x = h_a * 0x9E3779B97F4A7C15ULL + h_b; // slot_hash2, host copy
+  x ^= x >> 32;
+  x *= 0xD6E8FEB86659FD93ULL;
+  return dest_rank_of_hash(x, n_ranks ? n_ranks : 1);
 }
-int links_pairs_import(links_ctx* c, const void* dev_records, uint64_t n_records)
+
+int links_pairs_export(links_ctx* c, uint32_t n_ranks, void* dev_dst, uint64_t cap_records, uint64_t* counts)
 {
-  (void)dev_records; (void)n_records;
-  return fail(c, LINKS_E_INVAL, "links_pairs_import: not implemented yet");
+  if (!c || !counts) return LINKS_E_INVAL;
+  if (n_ranks == 0 || n_ranks > LINKS_MAX_RANKS) return fail(c, LINKS_E_LIMIT, "links_pairs_export: n_ranks must be 1..%u", LINKS_MAX_RANKS);
+  CU(c, cudaSetDevice(c->device));
+  cudaStream_t s = c->s_compute;
+  CU(c, cudaStreamSynchronize(c->s_copy));
+  CU(c, cudaStreamSynchronize(s));
+  Counters h;
+  CU(c, cudaMemcpy(&h, c->d_ctr.p, sizeof h, cudaMemcpyDeviceToHost));
+  const uint64_t n = h.n_unique;
+  for (uint32_t r = 0; r < n_ranks; ++r) counts[r] = 0;
+  if (!n) return LINKS_OK;
+  CU(c, c->f_exch.ensure(size_t(kMaxRanks) * 2 * 8));
+  unsigned long long* d_counts = c->f_exch.as<unsigned long long>();
+  unsigned long long* d_cursors = d_counts + kMaxRanks;
+  const PairView pv = pair_view(c->d_pairs.as<PairSlot>(), c->pair_cap, c->d_pair_list.as<ulonglong2>());
+  {
+    Span sp(c, F_EXCHANGE, s);
+    CU(c, cudaMemsetAsync(d_counts, 0, size_t(kMaxRanks) * 8, s));
+    pair_bucket_count_kernel<<<grid_for(c, n, kCtaThreads * 8, 8), kCtaThreads, 0, s>>>(pv.list, n, n_ranks, d_counts);
+    c->launches++;
+    CU(c, cudaGetLastError());
+  }
+  std::vector<unsigned long long> hc(n_ranks), start(n_ranks);
+  CU(c, cudaMemcpyAsync(hc.data(), d_counts, size_t(n_ranks) * 8, cudaMemcpyDeviceToHost, s));
+  CU(c, cudaStreamSynchronize(s));
+  unsigned long long run = 0;
+  for (uint32_t r = 0; r < n_ranks; ++r) { counts[r] = hc[r]; start[r] = run; run += hc[r]; }
+  if (!dev_dst) return LINKS_OK;
+  if (cap_records < n) return fail(c, LINKS_E_INVAL, "links_pairs_export: room for %llu records, %llu needed", (unsigned long long)cap_records, (unsigned long long)n);
+  {
+    Span sp(c, F_EXCHANGE, s);
+    CU(c, cudaMemcpyAsync(d_cursors, start.data(), size_t(n_ranks) * 8, cudaMemcpyHostToDevice, s));
+    pair_bucket_scatter_kernel<<<grid_for(c, n, kCtaThreads, 8), kCtaThreads, 0, s>>>(pv, n, n_ranks, c->prm.n_dist > 1 ? 1 : 0, d_cursors,
+                                                                                     static_cast<uint64_t*>(dev_dst));
+    c->launches++;
+    CU(c, cudaGetLastError());
+  }
+  CU(c, cudaStreamSynchronize(s)); // `start` is pageable host memory; also: records are complete on return
+  return LINKS_OK;
 }
+
 int links_pairs_clear(links_ctx* c)
 {
-  return fail(c, LINKS_E_INVAL, "links_pairs_clear: not implemented yet");
+  if (!c) return LINKS_E_INVAL;
+  CU(c, cudaSetDevice(c->device));
+  CU(c, cudaStreamSynchronize(c->s_copy));
+  CU(c, cudaStreamSynchronize(c->s_compute));
+  poll_snapshots(c);
+  for (int i = 0; i < links_ctx::kSnaps; ++i) c->snap_live[i] = false;
+  c->known_unique = 0; c->known_cand = c->cand_total;
+  Span sp(c, F_EXCHANGE, c->s_compute);
+  CU(c, cudaMemsetAsync(reinterpret_cast<char*>(c->d_ctr.p) + offsetof(Counters, n_unique), 0, sizeof(unsigned long long), c->s_compute));
+  if (c->pair_cap) CU(c, cudaMemsetAsync(c->d_pairs.p, 0xFF, c->pair_cap * sizeof(PairSlot), c->s_compute));
+  return LINKS_OK;
+}
+
+int links_pairs_import(links_ctx* c, const void* dev_records, uint64_t n_records)
+{
+  if (!c || (!dev_records && n_records)) return LINKS_E_INVAL;
+  if (c->finalized) return fail(c, LINKS_E_INVAL, "links_pairs_import: context already finalized (links_reset first)");
+  if (!n_records) return LINKS_OK;
+  CU(c, cudaSetDevice(c->device));
+  int rc = ensure_pair_capacity(c, n_records, 0);
+  if (rc) return rc;
+  {
+    Span sp(c, F_EXCHANGE, c->s_compute);
+    pair_import_kernel<<<grid_for(c, n_records, kCtaThreads, 8), kCtaThreads, 0, c->s_compute>>>(
+      static_cast<const uint64_t*>(dev_records), n_records,
+      pair_view(c->d_pairs.as<PairSlot>(), c->pair_cap, c->d_pair_list.as<ulonglong2>()), c->prm.n_dist > 1 ? 1 : 0, c->d_ctr.as<Counters>());
+    c->launches++;
+    CU(c, cudaGetLastError());
+  }
+  // the records may be freed by the caller on return; the next capacity check needs the exact occupancy
+  CU(c, cudaStreamSynchronize(c->s_compute));
+  Counters h;
+  CU(c, cudaMemcpy(&h, c->d_ctr.p, sizeof h, cudaMemcpyDeviceToHost));
+  c->known_unique = h.n_unique; c->known_cand = c->cand_total;
+  return LINKS_OK;
+}
+
+int links_bf_download_dev(links_ctx* c, void* dev_dst)
+{
+  if (!c || !dev_dst) return LINKS_E_INVAL;
+  if (!c->bf_ready) return fail(c, LINKS_E_INVAL, "links_bf_download_dev: no Bloom filter");
+  CU(c, cudaSetDevice(c->device));
+  CU(c, cudaMemcpyAsync(dev_dst, c->d_bloom.p, c->bf_bytes, cudaMemcpyDeviceToDevice, c->s_compute));
+  CU(c, cudaStreamSynchronize(c->s_compute));
+  return LINKS_OK;
+}
+
+int links_bf_load_dev(links_ctx* c, const void* dev_bits, uint64_t bytes, uint32_t hash_num)
+{
+  if (!c || !dev_bits) return LINKS_E_INVAL;
+  if (bytes == 0 || (bytes & 3) || hash_num == 0 || hash_num > LINKS_MAX_HASH_NUM)
+    return fail(c, LINKS_E_INVAL, "links_bf_load_dev: bytes must be a positive multiple of 4 and hash_num in 1..%u", LINKS_MAX_HASH_NUM);
+  CU(c, cudaSetDevice(c->device));
+  CU(c, c->d_bloom.ensure(bytes));
+  CU(c, cudaMemcpyAsync(c->d_bloom.p, dev_bits, bytes, cudaMemcpyDeviceToDevice, c->s_compute));
+  CU(c, cudaStreamSynchronize(c->s_compute));
+  c->bf_bytes = bytes; c->hash_num = hash_num; c->bf_ready = true; c->bf_insert = false;
+  return LINKS_OK;
 }
 
 } // extern "C"

@@ -195,6 +195,31 @@ class Links:
         self._check(self._lib.links_contigs_push_dev(self._h, dev_ptr, off.ctypes.data, len(off) - 1, first_tig_id))
         self._n_contigs = max(self._n_contigs, first_tig_id + len(off) - 2)
 
+    # ------------------------------------------------------------------ multi-GPU hooks (links_b200/multi.py drives them)
+    def n_unique(self) -> int:
+        n = C.c_uint64()
+        self._check(self._lib.links_pairs_download(self._h, None, None, None, 0, C.byref(n)))
+        return int(n.value)
+
+    def pairs_export(self, n_ranks: int, dev_dst: int | None, cap_records: int = 0) -> list[int]:
+        """Distinct pairs as {h_a,h_b,order_key} records grouped by owner rank; returns counts per rank."""
+        counts = (C.c_uint64 * n_ranks)()
+        self._check(self._lib.links_pairs_export(self._h, n_ranks, dev_dst, cap_records, counts))
+        return [int(v) for v in counts]
+
+    def pairs_clear(self) -> None:
+        self._check(self._lib.links_pairs_clear(self._h))
+
+    def pairs_import(self, dev_records: int, n_records: int) -> None:
+        self._check(self._lib.links_pairs_import(self._h, dev_records, n_records))
+
+    def bf_download_dev(self, dev_dst: int) -> None:
+        self._check(self._lib.links_bf_download_dev(self._h, dev_dst))
+
+    def bf_load_dev(self, dev_bits: int, nbytes: int, hash_num: int) -> None:
+        self._check(self._lib.links_bf_load_dev(self._h, dev_bits, nbytes, hash_num))
+        self.bf_bytes, self.hash_num = nbytes, hash_num
+
     def set_stream(self, cuda_stream: int) -> None:
         self._check(self._lib.links_set_stream(self._h, cuda_stream))
 

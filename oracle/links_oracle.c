@@ -388,9 +388,33 @@ static int issue_cmp(const void* pa, const void* pb)
 
 /* ------------------------------------------------------------------ whole path */
 
+static lo_result* run_impl(const lo_params* p, const uint8_t* bf_bits, uint64_t bf_bytes, unsigned hash_num,
+                           const char* contigs, const uint64_t* contig_off, uint64_t n_contigs,
+                           const char* reads, const uint64_t* read_off, uint64_t n_reads, int keep_obs,
+                           const uint64_t* preset_a, const uint64_t* preset_b, const uint32_t* preset_d, uint64_t n_preset);
+
 lo_result* lo_run(const lo_params* p, const uint8_t* bf_bits, uint64_t bf_bytes, unsigned hash_num,
                   const char* contigs, const uint64_t* contig_off, uint64_t n_contigs,
                   const char* reads, const uint64_t* read_off, uint64_t n_reads, int keep_obs)
+{
+  return run_impl(p, bf_bits, bf_bytes, hash_num, contigs, contig_off, n_contigs, reads, read_off, n_reads, keep_obs,
+                  NULL, NULL, NULL, 0);
+}
+
+/* Stages 3-4 on a GIVEN mate_pair content (distinct ordered pairs with their winning distance
+ * index) instead of extracting it from reads: what one rank of the multi-GPU path computes after
+ * the pair exchange.  Test infrastructure for tests/test_multi_rank.py. */
+lo_result* lo_run_from_pairs(const lo_params* p, const char* contigs, const uint64_t* contig_off, uint64_t n_contigs,
+                             const uint64_t* h_a, const uint64_t* h_b, const uint32_t* d_idx, uint64_t n_pairs)
+{
+  static const uint8_t no_bits[8] = {0};
+  return run_impl(p, no_bits, 8, 1, contigs, contig_off, n_contigs, NULL, NULL, 0, 0, h_a, h_b, d_idx, n_pairs);
+}
+
+static lo_result* run_impl(const lo_params* p, const uint8_t* bf_bits, uint64_t bf_bytes, unsigned hash_num,
+                           const char* contigs, const uint64_t* contig_off, uint64_t n_contigs,
+                           const char* reads, const uint64_t* read_off, uint64_t n_reads, int keep_obs,
+                           const uint64_t* preset_a, const uint64_t* preset_b, const uint32_t* preset_d, uint64_t n_preset)
 {
   lo_result* res = (lo_result*)calloc(1, sizeof(lo_result));
   if (!res) return NULL;
@@ -449,6 +473,13 @@ lo_result* lo_run(const lo_params* p, const uint8_t* bf_bits, uint64_t bf_bytes,
           u64map_upsert(&mates, h_b, &f);
         }
       }
+    }
+  }
+  for (uint64_t i = 0; i < n_preset; ++i) {
+    if (pairmap_insert(&mate_pair, preset_a[i], preset_b[i], preset_d[i])) {
+      int f;
+      u64map_upsert(&mates, preset_a[i], &f);
+      u64map_upsert(&mates, preset_b[i], &f);
     }
   }
   res->stats.n_unique_pairs = mate_pair.n;

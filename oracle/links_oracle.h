@@ -130,6 +130,10 @@ typedef struct lo_result {
 lo_result* lo_run(const lo_params* p, const uint8_t* bf_bits, uint64_t bf_bytes, unsigned hash_num,
                   const char* contigs, const uint64_t* contig_off, uint64_t n_contigs,
                   const char* reads, const uint64_t* read_off, uint64_t n_reads, int keep_obs);
+/* Stages 3-4 only, on a given set of distinct ordered pairs (h_a, h_b, winning distance index):
+ * the share of pair_contigs (src/LINKS.hpp:780-1041) one rank of the multi-GPU path owns. */
+lo_result* lo_run_from_pairs(const lo_params* p, const char* contigs, const uint64_t* contig_off, uint64_t n_contigs,
+                             const uint64_t* h_a, const uint64_t* h_b, const uint32_t* d_idx, uint64_t n_pairs);
 void lo_free(lo_result* r);
 
 /* Formatting helpers: write one row / issue exactly as the reference prints them. */

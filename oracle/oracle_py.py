@@ -58,6 +58,9 @@ def load() -> C.CDLL:
         lib.lo_run.restype = C.POINTER(LoResult)
         lib.lo_run.argtypes = [C.POINTER(LoParams), C.c_void_p, C.c_uint64, C.c_uint, C.c_void_p, C.c_void_p, C.c_uint64,
                                C.c_void_p, C.c_void_p, C.c_uint64, C.c_int]
+        lib.lo_run_from_pairs.restype = C.POINTER(LoResult)
+        lib.lo_run_from_pairs.argtypes = [C.POINTER(LoParams), C.c_void_p, C.c_void_p, C.c_uint64, C.c_void_p, C.c_void_p,
+                                          C.c_void_p, C.c_uint64]
         lib.lo_free.argtypes = [C.POINTER(LoResult)]
         lib.lo_bf_size.argtypes = [C.c_uint64, C.c_float, C.POINTER(C.c_uint64), C.POINTER(C.c_uint64), C.POINTER(C.c_uint)]
         lib.lo_bf_insert_seq.argtypes = [C.c_void_p, C.c_uint64, C.c_uint, C.c_uint, C.c_void_p, C.c_uint64]
@@ -166,6 +169,37 @@ def run(k: int, dist: list[int], step: list[int], offset: int, insert_stdev: flo
     finally:
         lib.lo_free(res)
     return rows, issues, stats, obs
+
+
+def run_from_pairs(k: int, dist: list[int], step: list[int], offset: int, insert_stdev: float, contig_seq: np.ndarray,
+                   contig_off: np.ndarray, h_a: np.ndarray, h_b: np.ndarray, d_idx: np.ndarray):
+    """Stages 3-4 on a given distinct pair set.  Returns (rows, issues, stats dict)."""
+    lib = load()
+    n = len(dist)
+    d = (C.c_uint32 * n)(*dist)
+    s = (C.c_uint16 * n)(*step)
+    p = LoParams(k, n, d, s, offset, insert_stdev)
+    cs = np.ascontiguousarray(contig_seq, np.uint8)
+    co = np.ascontiguousarray(contig_off, np.uint64)
+    a = np.ascontiguousarray(h_a, np.uint64)
+    b = np.ascontiguousarray(h_b, np.uint64)
+    di = np.ascontiguousarray(d_idx, np.uint32)
+    res = lib.lo_run_from_pairs(C.byref(p), cs.ctypes.data, co.ctypes.data, len(co) - 1, a.ctypes.data, b.ctypes.data,
+                                di.ctypes.data, len(a))
+    if not res:
+        raise MemoryError("lo_run_from_pairs failed")
+    try:
+        r = res.contents
+        rows = np.empty(r.n_rows, ROW_DTYPE)
+        if r.n_rows:
+            C.memmove(rows.ctypes.data, r.rows, r.n_rows * ROW_DTYPE.itemsize)
+        issues = np.empty(r.n_issues, ISSUE_DTYPE)
+        if r.n_issues:
+            C.memmove(issues.ctypes.data, r.issues, r.n_issues * ISSUE_DTYPE.itemsize)
+        stats = {nm: int(getattr(r.stats, nm)) for nm in STAT_NAMES}
+    finally:
+        lib.lo_free(res)
+    return rows, issues, stats
 
 
 def format_rows(rows: np.ndarray) -> bytes:

@@ -230,3 +230,63 @@ def test_argument_errors(gpu_lib):
             L.push_reads(SeqSet.from_records([b"ACGT" * 100]))  # no Bloom filter yet
         with pytest.raises(LinksError):
             L.bf_alloc(12, 3)  # not a multiple of 8
+
+
+@pytest.mark.parametrize("name,n_ranks", [("adv_tandem", 2), ("adv_offset_k20", 3), ("c1", 2)])
+def test_pair_exchange_between_contexts_equals_single_context(gpu_lib, name, n_ranks):
+    """The multi-GPU path on one device: n contexts each take a contiguous shard of the reads
+    (global read ordinals), export their distinct pairs bucketed by owner, every owner imports its
+    buckets, finalizes, and the summed partial rows must equal the reference's rows for the job."""
+    import torch
+
+    from links_b200 import Links, LinksOptions, bf_size, multi
+    from links_b200.pairing import ROW_DTYPE
+    from links_b200.seqio import SeqSet
+    c = GoldenCase(name)
+    contigs, reads = c.contigs(), c.reads()
+    _m, nbytes, h = bf_size(c.meta["contigs_file_bytes"], c.opts["p"])
+    opts = dict(k=c.opts["k"], distances=c.opts["d"], step_sizes=c.opts["t"], offset=c.opts["o"], insert_stdev=c.opts["e"])
+    ctxs = [Links(LinksOptions(**opts)) for _ in range(n_ranks)]
+    try:
+        # rank 0 builds the filter, the others adopt its bits device-to-device
+        ctxs[0].bf_alloc(nbytes, h)
+        ctxs[0].push_contigs(contigs)
+        bf = torch.empty(nbytes, dtype=torch.uint8, device="cuda")
+        ctxs[0].bf_download_dev(bf.data_ptr())
+        for L in ctxs[1:]:
+            L.bf_load_dev(bf.data_ptr(), nbytes, h)
+            L.push_contigs(contigs)
+        sends, counts = [], []
+        n_cand = 0
+        for r, L in enumerate(ctxs):
+            lo, hi = reads.n * r // n_ranks, reads.n * (r + 1) // n_ranks
+            L.push_reads(SeqSet(reads.seq, reads.off[lo:hi + 1], reads.names[lo:hi]), first_read_idx=lo)
+            n = L.n_unique()
+            buf = torch.empty((max(n, 1), 3), dtype=torch.int64, device="cuda")
+            only_counts = L.pairs_export(n_ranks, None, 0)
+            cnt = L.pairs_export(n_ranks, buf.data_ptr(), max(n, 1))
+            assert cnt == only_counts and sum(cnt) == n
+            rec = buf[:n].cpu().numpy().view(np.uint64)
+            owner = multi.pair_owner(rec[:, 0], rec[:, 1], n_ranks)
+            assert np.array_equal(owner, np.repeat(np.arange(n_ranks), cnt).astype(np.uint32))  # grouped by owner
+            a, b, _d = L.pairs()
+            assert set(zip(a.tolist(), b.tolist())) == set(zip(rec[:, 0].tolist(), rec[:, 1].tolist()))
+            sends.append(buf); counts.append(cnt)
+        parts, issue_txt = [], b""
+        for r, L in enumerate(ctxs):
+            L.pairs_clear()
+            assert L.n_unique() == 0
+            for s in range(n_ranks):
+                off = sum(counts[s][:r])
+                if counts[s][r]:
+                    L.pairs_import(sends[s][off:off + counts[s][r]].data_ptr(), counts[s][r])
+            rows, issues, stats = L.finalize()
+            n_cand += stats["n_candidates"]
+            parts.append(rows)
+            issue_txt += L.format_issues(issues)
+        merged = multi.sum_rows(parts, ROW_DTYPE)
+        assert sort_lines(ctxs[0].format_rows(merged)) == c.expected_tsv()
+        assert sort_issue_records(issue_txt) == c.expected_issues()
+    finally:
+        for L in ctxs:
+            L.close()
