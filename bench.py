@@ -253,8 +253,26 @@ def main_ours(args, rank: int, world: int, local_rank: int):
     dev = torch.device("cuda", local_rank)
     first_read = rank * (1 << 22)  # disjoint global read ordinals per rank (order key, n_dist > 1)
 
+    phases = os.environ.get("LINKS_BENCH_PHASES") == "1"  # diagnostic: host wall time per phase (adds syncs; not a bench number)
+    ph: dict[str, float] = {}
+    ph_t = [0.0]
+
+    def mark(name: str | None):
+        if not phases:
+            return
+        torch.cuda.synchronize()
+        now = time.perf_counter()
+        if name:
+            ph[name] = (now - ph_t[0]) * 1e3  # last step wins: steady state, not the first-call set-up costs
+        ph_t[0] = now
+
     def step(resident: bool):
+        mark(None)
+        _step(resident)
+
+    def _step(resident: bool):
         L.reset()
+        mark("reset")
         if world > 1 and rank != 0:
             pass  # the filter arrives by broadcast below
         else:
@@ -273,15 +291,20 @@ def main_ours(args, rank: int, world: int, local_rank: int):
             L.push_contigs_dev(d_contigs.data_ptr(), contigs.off, 1)
         else:
             L.push_contigs_raw(pc_seq, pc_off, contigs.n, 1)
+        mark("bloom+contigs")
         if resident:
             L.push_reads_dev(d_reads.data_ptr(), reads.off, first_read)
         else:
             L.push_reads_raw(pr_seq, pr_off, reads.n, first_read)
+        mark("reads")
         if world > 1:
-            state["exchange"] = multi.exchange_pairs(L, dist, dev)
+            state["exchange"] = multi.exchange_pairs(L, dist, dev, profile=phases)
+            mark("exchange")
         rows, issues, stats = L.finalize()
+        mark("finalize")
         if world > 1:
-            rows = multi.gather_rows(rows, dist, dev)
+            rows = multi.gather_rows(rows, dist, dev, merge=L.rows_merge)
+            mark("gather_rows")
         state["rows"], state["issues"], state["stats"] = rows, issues, stats
 
     def timed(resident: bool, steps: int, warmup: int):
@@ -313,6 +336,8 @@ def main_ours(args, rank: int, world: int, local_rank: int):
     stats = dict(state["stats"])
     ms_e2e, tm_e2e = timed(False, args.steps, max(args.warmup, 1))
     clk = clocks.stop()
+    if phases:
+        print(f"[rank {rank}] host ms per phase, last step: " + json.dumps({k2: round(v, 2) for k2, v in ph.items()}), file=sys.stderr)
     digest_e2e = rows_digest(state["rows"]) if rank == 0 else ""
 
     cand = stats["n_candidates"]

@@ -165,6 +165,9 @@ int links_format_issue(const links_issue* r, char* dst, size_t cap);
 int links_pairs_export(links_ctx* ctx, uint32_t n_ranks, void* dev_dst, uint64_t cap_records, uint64_t* counts);
 int links_pairs_import(links_ctx* ctx, const void* dev_records, uint64_t n_records);
 int links_pairs_clear(links_ctx* ctx);
+/* Sum rows that share (bin, tig_a, rev_a, tig_b, rev_b) -- the ranks' partial link tables after a
+ * gather -- on the device; *out is malloc'd (links_free_result(*out, NULL)), sorted like links_finalize's. */
+int links_rows_merge(links_ctx* ctx, const links_row* rows, uint64_t n, links_row** out, uint64_t* n_out);
 /* Owner rank of a pair, the same function the export kernel uses (for hosts that route themselves). */
 uint32_t links_pair_owner(uint64_t h_a, uint64_t h_b, uint32_t n_ranks);
 /* Bloom filter replication: copy the filter's bit array device-to-device out of / into the

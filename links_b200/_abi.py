@@ -90,6 +90,7 @@ SIGNATURES = {
     "links_format_row": (C.c_int, [C.POINTER(LinksRow), C.c_char_p, C.c_size_t]),
     "links_format_issue": (C.c_int, [C.POINTER(LinksIssue), C.c_char_p, C.c_size_t]),
     "links_pairs_export": (C.c_int, [C.c_void_p, C.c_uint32, C.c_void_p, C.c_uint64, C.POINTER(C.c_uint64)]),
+    "links_rows_merge": (C.c_int, [C.c_void_p, C.c_void_p, C.c_uint64, C.POINTER(C.POINTER(LinksRow)), C.POINTER(C.c_uint64)]),
     "links_pair_owner": (C.c_uint32, [C.c_uint64, C.c_uint64, C.c_uint32]),
     "links_bf_download_dev": (C.c_int, [C.c_void_p, C.c_void_p]),
     "links_bf_load_dev": (C.c_int, [C.c_void_p, C.c_void_p, C.c_uint64, C.c_uint32]),

@@ -228,4 +228,21 @@ __global__ void reduce_by_key_kernel(const uint64_t* __restrict__ keys, const in
   atomicAdd(out_gaps + seg, (unsigned long long)gaps);
 }
 
+// Sum already-aggregated rows that share a key (merging the partial link tables of several
+// ranks): item i of the sorted order adds in_links/in_gaps[idx[i]] to its segment.
+__global__ void rows_segment_sum_kernel(const uint64_t* __restrict__ keys, const int32_t* __restrict__ idx, uint64_t n,
+                                        const uint32_t* __restrict__ seg_excl, const unsigned long long* __restrict__ in_links,
+                                        const unsigned long long* __restrict__ in_gaps, uint64_t* __restrict__ out_keys,
+                                        unsigned long long* __restrict__ out_links, unsigned long long* __restrict__ out_gaps)
+{
+  const uint64_t i = uint64_t(blockIdx.x) * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const uint64_t key = keys[i];
+  const bool head = (i == 0 || keys[i - 1] != key);
+  const uint32_t seg = seg_excl[i] + (head ? 1u : 0u) - 1u;
+  if (head) out_keys[seg] = key;
+  atomicAdd(out_links + seg, in_links[idx[i]]);
+  atomicAdd(out_gaps + seg, in_gaps[idx[i]]);
+}
+
 } // namespace links

@@ -118,7 +118,7 @@ struct links_ctx {
 
   // stage-4 scratch (kept across links_reset so repeated jobs do not re-allocate)
   DevBuf f_final;
-  DevBuf f_keys[2], f_vals[2], f_issues, f_tiglen, f_hist, f_scan_tmp, f_flags, f_total, f_okeys, f_olinks, f_ogaps, f_exch;
+  DevBuf f_keys[2], f_vals[2], f_issues, f_tiglen, f_hist, f_scan_tmp, f_flags, f_total, f_okeys, f_olinks, f_ogaps, f_exch, f_il, f_ig;
   uint64_t issue_cap_hint = 1ull << 16;
 
   // timing
@@ -548,7 +548,7 @@ void links_destroy(links_ctx* c)
   for (int i = 0; i < links_ctx::kSnaps; ++i) if (c->ev_snap[i]) cudaEventDestroy(c->ev_snap[i]);
   if (c->h_snap) cudaFreeHost(c->h_snap);
   for (DevBuf* b : {&c->f_keys[0], &c->f_keys[1], &c->f_vals[0], &c->f_vals[1], &c->f_issues, &c->f_tiglen, &c->f_hist,
-                    &c->f_scan_tmp, &c->f_flags, &c->f_total, &c->f_okeys, &c->f_olinks, &c->f_ogaps, &c->f_final, &c->f_exch}) b->release();
+                    &c->f_scan_tmp, &c->f_flags, &c->f_total, &c->f_okeys, &c->f_olinks, &c->f_ogaps, &c->f_final, &c->f_exch, &c->f_il, &c->f_ig}) b->release();
   c->d_tab.release(); c->d_dist.release(); c->d_step.release(); c->d_minallowed.release();
   c->d_bloom.release(); c->d_pairs.release(); c->d_pair_list.release(); c->d_ctr.release(); c->d_table.release();
   if (c->s_compute && c->own_compute_stream) cudaStreamDestroy(c->s_compute);
@@ -1093,6 +1093,79 @@ int links_pairs_download(links_ctx* c, uint64_t* h_a, uint64_t* h_b, uint32_t* d
 }
 
 // ---------------------------------------------------------------- multi-GPU exchange hooks
+
+// Sum rows with equal (bin, tig_a, rev_a, tig_b, rev_b): the per-rank partial link tables of the
+// multi-GPU path, gathered on one rank.  Same sort + segmented reduction as stage 4, on the device.
+int links_rows_merge(links_ctx* c, const links_row* rows, uint64_t n, links_row** out, uint64_t* n_out)
+{
+  if (!c || !out || !n_out || (!rows && n)) return LINKS_E_INVAL;
+  *out = nullptr; *n_out = 0;
+  if (n >= (1ull << 31)) return fail(c, LINKS_E_LIMIT, "links_rows_merge: more than 2^31 rows");
+  links_row* res = static_cast<links_row*>(malloc(std::max<uint64_t>(n, 1) * sizeof(links_row)));
+  if (!res) return fail(c, LINKS_E_NOMEM, "links_rows_merge: out of host memory");
+  *out = res;
+  if (!n) return LINKS_OK;
+  CU(c, cudaSetDevice(c->device));
+  cudaStream_t s = c->s_compute;
+  uint32_t max_tig = 0;
+  for (uint64_t i = 0; i < n; ++i) max_tig = std::max(max_tig, std::max(rows[i].tig_a, rows[i].tig_b));
+  const int tb = log2_ceil(uint64_t(max_tig) * 2 + 2);
+  std::vector<uint64_t> hk(n), hl(n), hg(n);
+  std::vector<int32_t> hidx(n);
+  for (uint64_t i = 0; i < n; ++i) {
+    const links_row& r = rows[i];
+    const uint32_t bc = r.bin < 0 ? 0 : r.bin == 10 ? 1 : r.bin == 500 ? 2 : r.bin == 5000 ? 3 : 4;
+    hk[i] = pack_row_key(bc, (r.tig_a << 1) | (r.rev_a & 1u), (r.tig_b << 1) | (r.rev_b & 1u), tb);
+    hl[i] = r.links; hg[i] = uint64_t(r.gaps); hidx[i] = int32_t(i);
+  }
+  DevBuf (&d_keys)[2] = c->f_keys; DevBuf (&d_vals)[2] = c->f_vals;
+  DevBuf &d_il = c->f_il, &d_ig = c->f_ig;
+  CU(c, d_keys[0].ensure(n * 8)); CU(c, d_vals[0].ensure(n * 4)); CU(c, d_il.ensure(n * 8)); CU(c, d_ig.ensure(n * 8));
+  CU(c, c->f_flags.ensure(n * 4)); CU(c, c->f_total.ensure(64));
+  uint32_t n_seg = 0;
+  int cur = 0;
+  {
+    Span sp(c, F_SORT, s);
+    CU(c, cudaMemcpyAsync(d_keys[0].p, hk.data(), n * 8, cudaMemcpyHostToDevice, s));
+    CU(c, cudaMemcpyAsync(d_vals[0].p, hidx.data(), n * 4, cudaMemcpyHostToDevice, s));
+    CU(c, cudaMemcpyAsync(d_il.p, hl.data(), n * 8, cudaMemcpyHostToDevice, s));
+    CU(c, cudaMemcpyAsync(d_ig.p, hg.data(), n * 8, cudaMemcpyHostToDevice, s));
+    int rc = radix_sort_pairs(c, s, d_keys, d_vals, n, 3 + 2 * tb, cur);
+    if (rc) return rc;
+    head_flags_kernel<<<unsigned((n + 255) / 256), 256, 0, s>>>(d_keys[cur].as<uint64_t>(), n, c->f_flags.as<uint32_t>());
+    c->launches++;
+    rc = device_scan(c, s, c->f_flags.as<uint32_t>(), n, c->f_flags.as<uint32_t>(), c->f_scan_tmp, c->f_total.as<uint32_t>());
+    if (rc) return rc;
+    CU(c, cudaMemcpyAsync(&n_seg, c->f_total.p, 4, cudaMemcpyDeviceToHost, s));
+    CU(c, cudaStreamSynchronize(s));
+    CU(c, c->f_okeys.ensure(uint64_t(n_seg) * 8)); CU(c, c->f_olinks.ensure(uint64_t(n_seg) * 8)); CU(c, c->f_ogaps.ensure(uint64_t(n_seg) * 8));
+    CU(c, cudaMemsetAsync(c->f_olinks.p, 0, uint64_t(n_seg) * 8, s));
+    CU(c, cudaMemsetAsync(c->f_ogaps.p, 0, uint64_t(n_seg) * 8, s));
+    rows_segment_sum_kernel<<<unsigned((n + 255) / 256), 256, 0, s>>>(
+      d_keys[cur].as<uint64_t>(), d_vals[cur].as<int32_t>(), n, c->f_flags.as<uint32_t>(), d_il.as<unsigned long long>(),
+      d_ig.as<unsigned long long>(), c->f_okeys.as<uint64_t>(), c->f_olinks.as<unsigned long long>(), c->f_ogaps.as<unsigned long long>());
+    c->launches++;
+    CU(c, cudaGetLastError());
+    hk.resize(n_seg); hl.resize(n_seg); hg.resize(n_seg);
+    CU(c, cudaMemcpyAsync(hk.data(), c->f_okeys.p, uint64_t(n_seg) * 8, cudaMemcpyDeviceToHost, s));
+    CU(c, cudaMemcpyAsync(hl.data(), c->f_olinks.p, uint64_t(n_seg) * 8, cudaMemcpyDeviceToHost, s));
+    CU(c, cudaMemcpyAsync(hg.data(), c->f_ogaps.p, uint64_t(n_seg) * 8, cudaMemcpyDeviceToHost, s));
+    CU(c, cudaStreamSynchronize(s));
+  }
+  static const int32_t bin_of_code[5] = {-1, 10, 500, 5000, 10000};
+  const uint64_t tmask = (1ull << tb) - 1;
+  for (uint32_t i = 0; i < n_seg; ++i) {
+    const uint64_t key = hk[i];
+    const uint32_t B = uint32_t(key & tmask), A = uint32_t((key >> tb) & tmask), bc = uint32_t(key >> (2 * tb));
+    links_row r;
+    memset(&r, 0, sizeof r);
+    r.bin = bin_of_code[bc]; r.links = hl[i]; r.gaps = int64_t(hg[i]);
+    r.tig_a = A >> 1; r.rev_a = A & 1; r.tig_b = B >> 1; r.rev_b = B & 1;
+    res[i] = r;
+  }
+  *n_out = n_seg;
+  return LINKS_OK;
+}
 
 uint32_t links_pair_owner(uint64_t h_a, uint64_t h_b, uint32_t n_ranks)
 {

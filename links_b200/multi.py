@@ -43,18 +43,39 @@ def exchange_records(send, counts, dist, group=None):
     return recv
 
 
-def exchange_pairs(L, dist, device, group=None) -> dict:
-    """export -> all-to-all -> clear -> import on a Links context.  Returns byte/record counts."""
+def exchange_pairs(L, dist, device, group=None, profile: bool = False) -> dict:
+    """export -> all-to-all -> clear -> import on a Links context.  Returns byte/record counts
+    (and, with profile=True, host milliseconds per phase measured with device syncs)."""
+    import time
+
     import torch
     world = dist.get_world_size(group)
+    t = [time.perf_counter()]
+    ms: dict[str, float] = {}
+
+    def mark(name):
+        if profile:
+            torch.cuda.synchronize()
+            now = time.perf_counter()
+            ms[name] = (now - t[0]) * 1e3
+            t[0] = now
+
     n = L.n_unique()
     send = torch.empty((max(n, 1), RECORD_WORDS), dtype=torch.int64, device=device)
+    mark("alloc")
     counts = L.pairs_export(world, send.data_ptr(), max(n, 1))
+    mark("export")
     recv = exchange_records(send[:n], counts, dist, group)
+    mark("all_to_all")
     L.pairs_clear()
+    mark("clear")
     if recv.shape[0]:
         L.pairs_import(recv.data_ptr(), recv.shape[0])
-    return {"sent_records": int(n), "recv_records": int(recv.shape[0]), "sent_bytes": int(n) * 8 * RECORD_WORDS}
+    mark("import")
+    out = {"sent_records": int(n), "recv_records": int(recv.shape[0]), "sent_bytes": int(n) * 8 * RECORD_WORDS}
+    if profile:
+        out["host_ms"] = {k: round(v, 3) for k, v in ms.items()}
+    return out
 
 
 def replicate_bloom(L, nbytes: int, hash_num: int, dist, device, src: int = 0, group=None) -> None:
@@ -68,10 +89,16 @@ def replicate_bloom(L, nbytes: int, hash_num: int, dist, device, src: int = 0, g
         L.bf_load_dev(buf.data_ptr(), nbytes, hash_num)
 
 
-def _row_keys(rows: np.ndarray) -> np.ndarray:
-    k = np.empty((len(rows), 5), dtype=np.int64)
-    k[:, 0], k[:, 1], k[:, 2], k[:, 3], k[:, 4] = rows["bin"], rows["tig_a"], rows["rev_a"], rows["tig_b"], rows["rev_b"]
-    return k
+_BIN_CODE = {-1: 0, 10: 1, 500: 2, 5000: 3, 10000: 4}  # get_distance_bin's range (src/LINKS.hpp:764-770)
+
+
+def _row_key(rows: np.ndarray) -> np.ndarray:
+    """One u64 per row, monotone in (bin, tig_a, rev_a, tig_b, rev_b); tig < 2^29 (LINKS_MAX_TIGS)."""
+    b = rows["bin"].astype(np.int64)
+    code = np.select([b < 0, b == 10, b == 500, b == 5000], [0, 1, 2, 3], default=4).astype(np.uint64)
+    a = (rows["tig_a"].astype(np.uint64) << np.uint64(1)) | rows["rev_a"].astype(np.uint64)
+    c = (rows["tig_b"].astype(np.uint64) << np.uint64(1)) | rows["rev_b"].astype(np.uint64)
+    return (code << np.uint64(60)) | (a << np.uint64(30)) | c
 
 
 def sum_rows(parts: list[np.ndarray], row_dtype) -> np.ndarray:
@@ -81,11 +108,11 @@ def sum_rows(parts: list[np.ndarray], row_dtype) -> np.ndarray:
     if not parts:
         return np.empty(0, dtype=row_dtype)
     rows = np.concatenate(parts)
-    k = _row_keys(rows)
-    order = np.lexsort((k[:, 4], k[:, 3], k[:, 2], k[:, 1], k[:, 0]))
-    rows, k = rows[order], k[order]
+    key = _row_key(rows)
+    order = np.argsort(key, kind="stable")
+    rows, key = rows[order], key[order]
     head = np.ones(len(rows), dtype=bool)
-    head[1:] = (k[1:] != k[:-1]).any(axis=1)
+    head[1:] = key[1:] != key[:-1]
     idx = np.flatnonzero(head)
     out = rows[idx].copy()
     out["links"] = np.add.reduceat(rows["links"].astype(np.uint64), idx)
@@ -93,22 +120,26 @@ def sum_rows(parts: list[np.ndarray], row_dtype) -> np.ndarray:
     return out
 
 
-def gather_rows(rows: np.ndarray, dist, device, dst: int = 0, group=None):
-    """Collect every rank's partial rows on rank `dst` and sum them; other ranks get None."""
+def gather_rows(rows: np.ndarray, dist, device, dst: int = 0, group=None, merge=None):
+    """Collect every rank's partial rows on rank `dst` and sum them; other ranks get None.
+    `merge` (e.g. Links.rows_merge, the device sort + segmented sum) replaces the numpy sum_rows."""
     import torch
     world, rank = dist.get_world_size(group), dist.get_rank(group)
-    raw = np.frombuffer(rows.tobytes(), dtype=np.uint8)
-    n = torch.tensor([raw.size], dtype=torch.int64, device=device)
-    sizes = [torch.zeros(1, dtype=torch.int64, device=device) for _ in range(world)]
-    dist.all_gather(sizes, n, group=group)
-    sizes = [int(s.item()) for s in sizes]
+    item = rows.dtype.itemsize
+    n = torch.tensor([len(rows)], dtype=torch.int64, device=device)
+    sizes = torch.empty(world, dtype=torch.int64, device=device)
+    dist.all_gather_into_tensor(sizes, n, group=group)
+    sizes = [int(v) for v in sizes.tolist()]
     cap = max(max(sizes), 1)
-    mine = torch.zeros(cap, dtype=torch.uint8, device=device)
-    if raw.size:
-        mine[:raw.size] = torch.from_numpy(raw.copy()).to(device)
-    bufs = [torch.empty(cap, dtype=torch.uint8, device=device) for _ in range(world)]
-    dist.all_gather(bufs, mine, group=group)
+    mine = torch.empty(cap * item, dtype=torch.uint8, device=device)
+    if len(rows):
+        mine[:len(rows) * item] = torch.from_numpy(rows.view(np.uint8).reshape(-1)).to(device)
+    allbuf = torch.empty(world * cap * item, dtype=torch.uint8, device=device)
+    dist.all_gather_into_tensor(allbuf, mine, group=group)
     if rank != dst:
         return None
-    parts = [np.frombuffer(b[:s].cpu().numpy().tobytes(), dtype=rows.dtype) for b, s in zip(bufs, sizes)]
+    host = allbuf.cpu().numpy().reshape(world, cap * item)
+    parts = [host[r, :sizes[r] * item].view(rows.dtype) for r in range(world)]
+    if merge is not None:
+        return merge(np.concatenate(parts))
     return sum_rows(parts, rows.dtype)

@@ -213,6 +213,20 @@ class Links:
     def pairs_import(self, dev_records: int, n_records: int) -> None:
         self._check(self._lib.links_pairs_import(self._h, dev_records, n_records))
 
+    def rows_merge(self, rows: np.ndarray) -> np.ndarray:
+        """Sum rows with equal key on the device (partial link tables of several ranks)."""
+        rows = np.ascontiguousarray(rows, dtype=ROW_DTYPE)
+        out_p = C.POINTER(_abi.LinksRow)()
+        n_out = C.c_uint64()
+        self._check(self._lib.links_rows_merge(self._h, rows.ctypes.data, len(rows), C.byref(out_p), C.byref(n_out)))
+        try:
+            out = np.empty(n_out.value, dtype=ROW_DTYPE)
+            if n_out.value:
+                C.memmove(out.ctypes.data, out_p, n_out.value * ROW_DTYPE.itemsize)
+        finally:
+            self._lib.links_free_result(out_p, None)
+        return out
+
     def bf_download_dev(self, dev_dst: int) -> None:
         self._check(self._lib.links_bf_download_dev(self._h, dev_dst))
 

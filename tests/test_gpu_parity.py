@@ -286,6 +286,9 @@ def test_pair_exchange_between_contexts_equals_single_context(gpu_lib, name, n_r
             issue_txt += L.format_issues(issues)
         merged = multi.sum_rows(parts, ROW_DTYPE)
         assert sort_lines(ctxs[0].format_rows(merged)) == c.expected_tsv()
+        on_device = ctxs[0].rows_merge(np.concatenate(parts))  # links_rows_merge: same sum, device sort + segmented reduce
+        assert on_device.tobytes() == merged.tobytes()
+        assert len(ctxs[0].rows_merge(np.empty(0, ROW_DTYPE))) == 0
         assert sort_issue_records(issue_txt) == c.expected_issues()
     finally:
         for L in ctxs:
