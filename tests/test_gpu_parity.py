@@ -2,6 +2,8 @@
 golden fixtures.  Integer / byte / index work: every comparison is bit-exact."""
 from __future__ import annotations
 
+import os
+
 import numpy as np
 import pytest
 
@@ -293,3 +295,33 @@ def test_pair_exchange_between_contexts_equals_single_context(gpu_lib, name, n_r
     finally:
         for L in ctxs:
             L.close()
+
+
+@pytest.mark.parametrize("name", ["c1", "adv_offset_k20", "adv_ns_lower"])
+def test_links_cpp_binary_writes_reference_files(gpu_lib, tmp_path, name):
+    """The C++ host LINKS_CPP, run as the reference binary is run (bin/LINKS-make:121-122): same
+    options in, byte-identical .bloom, and .tigpair_checkpoint.tsv / .pairing_issues equal to the
+    unmodified reference's after the sort the reference's CI applies."""
+    import subprocess
+    from links_b200 import build
+    c = GoldenCase(name)
+    cpath, fof = c.materialize(str(tmp_path))
+    base = str(tmp_path / "out")
+    cmd = [build.HOST_BIN, "-f", cpath, "-s", fof, "-b", base, "-k", str(c.opts["k"]), "-d", ",".join(map(str, c.opts["d"])),
+           "-t", ",".join(map(str, c.opts["t"])), "-o", str(c.opts["o"]), "-e", str(c.opts["e"]), "-p", str(c.opts["p"]), "-j", "3"]
+    env = dict(os.environ, LINKS_STAGE_MB="2")  # small staging buffer: several pushes per file
+    if name == "c1":
+        env["LINKS_STAGE_MB"] = "8"  # its single 1 Mbp read must fit
+    r = subprocess.run(cmd, capture_output=True, text=True, env=env)
+    assert r.returncode == 0, r.stderr
+    for banner in ("STAGE: Bloom filter construction/read", "STAGE: Reading sequence reads", "STAGE: Reading contigs",
+                   "STAGE: Pairing contigs", "Pair contig stage completed in: "):
+        assert banner in r.stdout
+    assert sha256(open(base + ".bloom", "rb").read()) == c.meta["bloom_sha256"]
+    assert sort_lines(open(base + ".tigpair_checkpoint.tsv", "rb").read()) == c.expected_tsv()
+    assert sort_issue_records(open(base + ".pairing_issues", "rb").read()) == c.expected_issues()
+    # -r: reuse the filter just written
+    r = subprocess.run(cmd[:6] + [base + "2"] + cmd[7:] + ["-r", base + ".bloom"], capture_output=True, text=True, env=env)
+    assert r.returncode == 0, r.stderr
+    assert sort_lines(open(base + "2.tigpair_checkpoint.tsv", "rb").read()) == c.expected_tsv()
+    assert not os.path.exists(base + "2.bloom")
