@@ -5,7 +5,7 @@ import ctypes as C
 import os
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(HERE, "liblinks_gpu.so")
+LIB_PATH = os.environ.get("LINKS_GPU_LIB") or os.path.join(HERE, "liblinks_gpu.so")  # override: kernel-variant experiments
 
 LINKS_OK = 0
 LINKS_E_INVAL, LINKS_E_CUDA, LINKS_E_NOMEM, LINKS_E_LIMIT, LINKS_E_NODEVICE = -1, -2, -3, -4, -5

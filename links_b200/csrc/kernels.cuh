@@ -4,7 +4,7 @@
 //   rank_build_kernel    per flagged record: valid-k-mer-start bitmap + prefix ranks (rank/select)
 //   bf_build_kernel      K2: contig k-mers -> Bloom bits            (ref src/LINKS.hpp:316-324)
 //   table_build_kernel   K4a: contig k-mers -> open-addressing table (ref :569-601,379-402)
-//   extract_kernel       K3+K5a: read k-mer pairs -> Bloom probe -> pair-set insert (ref :515-567,354-378)
+//   extract_kernel       K3+K5a (extract.cuh): read k-mer pairs -> Bloom probe -> pair-set insert (ref :515-567,354-378)
 //   classify_kernel      K4b: unique pairs -> table lookups -> link rows / issues (ref :824-968)
 //
 // HBM layout (all device arrays are flat, 256-byte aligned cudaMalloc blocks):
@@ -295,15 +295,6 @@ __global__ void __launch_bounds__(kCtaThreads) contig_kernel(ContigBatch cb, int
 
 // ------------------------------------------------------------------ reads: extract + probe + pair-set insert
 
-struct ReadBatch {
-  const uint32_t* packed; const uint32_t* inv; const uint64_t* off; uint64_t base0;
-  const uint32_t* seg_tile_start; uint32_t n_seq, n_tiles;
-  const uint32_t* flags; const unsigned long long* vs; const uint32_t* vrank;
-  uint64_t first_read_idx;
-};
-
-struct DistParams { const uint32_t* dist; const uint32_t* step; uint32_t n_dist; uint64_t offset; };
-
 __device__ __forceinline__ ulonglong2 cas128(PairSlot* slot, ulonglong2 cmp, ulonglong2 val)
 {
   ulonglong2 old;
@@ -361,199 +352,6 @@ __host__ __device__ __forceinline__ uint64_t make_okey(uint64_t read_idx, uint32
 __host__ __device__ __forceinline__ uint32_t okey_d_idx(uint64_t okey)
 {
   return uint32_t(okey >> kOkeyRankBits) & ((1u << kOkeyDistBits) - 1u);
-}
-
-// Shared-memory work queue push: every thread of the block calls it (uniform trip counts), `pass`
-// lanes append their candidate id.  One shared atomic per warp.
-__device__ __forceinline__ void queue_push(bool pass, uint16_t q, uint16_t* queue, uint32_t* counter)
-{
-  const uint32_t m = __ballot_sync(0xffffffffu, pass);
-  if (!m) return;
-  const int lane = threadIdx.x & 31;
-  uint32_t base = 0;
-  if (lane == (__ffs(m) - 1)) base = atomicAdd(counter, uint32_t(__popc(m)));
-  base = __shfl_sync(0xffffffffu, base, __ffs(m) - 1);
-  if (pass) queue[base + __popc(m & ((1u << lane) - 1u))] = q;
-}
-
-// K3 (+K5a): one tile = up to kTile candidates (rank n = j*t + t-1) of one (read, distance).
-// The reference's per-candidate sequence  hash A -> probe A -> hash B -> probe B -> insert
-// (src/LINKS.hpp:530-564) is run as five block-wide stages with a shared-memory compaction
-// between them, so that after every filter step the surviving candidates are re-packed onto
-// consecutive lanes (ONT-like reads: ~46 % of k-mers survive the filter; un-compacted, the
-// warps ran at 17 of 32 lanes).  Within a stage the Bloom probes of one k-mer are issued
-// together (2 first, the rest after) instead of one dependent load at a time.
-__global__ void __launch_bounds__(kCtaThreads, 4) extract_kernel(ReadBatch rb, DistParams dp, int k, uint64_t kseed,
-                                                                 const ulonglong2* __restrict__ g_tab, BloomView bf,
-                                                                 PairView pv, Counters* __restrict__ ctr)
-{
-  extern __shared__ ulonglong2 s_dyn[];
-  ulonglong2* s_tab = s_dyn;          // [k*4]
-  ulonglong2* sA = s_dyn + k * 4;     // [kTile] fwd/rev hash of k-mer A
-  ulonglong2* sB = sA + kTile;        // [kTile] fwd/rev hash of k-mer B, later (h_a,h_b) of fresh pairs
-  __shared__ uint16_t s_q[2][kTile];
-  __shared__ uint32_t s_n[5];
-  __shared__ uint32_t s_seg, s_va0, s_vb0;
-  __shared__ unsigned long long s_cnt, s_list_base;
-  for (int i = threadIdx.x; i < k * 4; i += blockDim.x) s_tab[i] = g_tab[i];
-  __syncthreads();
-  unsigned long long n_cand = 0, n_surv = 0, n_probe_acc = 0;
-  const bool multi_d = dp.n_dist > 1;
-  const uint32_t h_first = min(bf.hash_num, 2u);
-  for (uint32_t tile = blockIdx.x; tile < rb.n_tiles; tile += gridDim.x) {
-    const uint32_t n_seg = rb.n_seq * dp.n_dist;
-    if (threadIdx.x == 0) {
-      const uint32_t s = find_segment(rb.seg_tile_start, n_seg, tile);
-      s_seg = s;
-      const uint32_t r = s / dp.n_dist, di = s - r * dp.n_dist;
-      const uint64_t len = rb.off[r + 1] - rb.off[r];
-      const uint64_t npos = len - k + 1; // segments of reads shorter than k own zero tiles
-      const uint64_t o = dp.offset, d = dp.dist[di], t = dp.step[di];
-      unsigned long long cnt = 0;
-      if (!rb.flags[r]) {
-        // no invalid base: a[n] = o+n, b[n] = o+d+n, n < npos-o-d
-        if (npos > o + d) cnt = (npos - o - d) / t;
-      } else {
-        const uint64_t g0 = rb.off[r] - rb.base0;
-        RankView rv;
-        rv.vs = rb.vs; rv.vrank = rb.vrank; rv.wb = (g0 >> 6) + 2ull * r; rv.npos = npos;
-        rv.nwords = (npos + 63) >> 6; rv.total = rb.vrank[rv.wb + rv.nwords];
-        const uint32_t va0 = rank_of(rv, o), vb0 = rank_of(rv, o + d);
-        const uint32_t na = rv.total - va0, nb = rv.total - vb0;
-        cnt = (na < nb ? na : nb) / t;
-        s_va0 = va0; s_vb0 = vb0;
-      }
-      s_cnt = cnt;
-      s_n[0] = s_n[1] = s_n[2] = s_n[3] = s_n[4] = 0;
-    }
-    __syncthreads();
-    const uint32_t s = s_seg;
-    const uint32_t r = s / dp.n_dist, di = s - r * dp.n_dist;
-    const uint64_t g0 = rb.off[r] - rb.base0;
-    const uint64_t d = dp.dist[di], t = dp.step[di];
-    const unsigned long long cnt = s_cnt;
-    const bool flagged = rb.flags[r] != 0;
-    const uint64_t j_begin = uint64_t(tile - rb.seg_tile_start[s]) * kTile;
-    const uint32_t n_tile = j_begin < cnt ? uint32_t(min((unsigned long long)kTile, cnt - j_begin)) : 0u;
-    RankView rv;
-    uint32_t va0 = 0, vb0 = 0;
-    if (flagged) {
-      const uint64_t len = rb.off[r + 1] - rb.off[r];
-      rv.vs = rb.vs; rv.vrank = rb.vrank; rv.wb = (g0 >> 6) + 2ull * r; rv.npos = len - k + 1;
-      rv.nwords = (rv.npos + 63) >> 6; rv.total = rb.vrank[rv.wb + rv.nwords];
-      va0 = s_va0; vb0 = s_vb0;
-    }
-    uint32_t n_probe = 0;
-
-    // ---- stage 1: hash k-mer A, first two probes
-    for (uint32_t base = 0; base < n_tile; base += kCtaThreads) {
-      const uint32_t q = base + threadIdx.x;
-      bool pass = false;
-      if (q < n_tile) {
-        const uint64_t n = (j_begin + q) * t + (t - 1); // rank among valid k-mers of each stream (ref :530-543)
-        const uint64_t a = flagged ? select_of(rv, va0 + uint32_t(n)) : dp.offset + n;
-        uint64_t f, rr;
-        hash_kmer(rb.packed, g0 + a, k, s_tab, f, rr);
-        sA[q] = make_ulonglong2(f, rr);
-        pass = bloom_probe_range(bf, rr < f ? rr : f, kseed, 0, h_first, n_probe);
-      }
-      queue_push(pass, uint16_t(q), s_q[0], &s_n[0]);
-    }
-    n_cand += (threadIdx.x < n_tile) ? ((n_tile - threadIdx.x + kCtaThreads - 1) / kCtaThreads) : 0;
-    __syncthreads();
-    // ---- stage 2: remaining probes of A
-    {
-      const uint32_t n1 = s_n[0];
-      for (uint32_t base = 0; base < n1; base += kCtaThreads) {
-        const uint32_t i = base + threadIdx.x;
-        bool pass = false;
-        uint16_t q = 0;
-        if (i < n1) {
-          q = s_q[0][i];
-          const ulonglong2 h = sA[q];
-          pass = bloom_probe_range(bf, h.y < h.x ? h.y : h.x, kseed, h_first, bf.hash_num, n_probe);
-        }
-        queue_push(pass, q, s_q[1], &s_n[1]);
-      }
-    }
-    __syncthreads();
-    // ---- stage 3: hash k-mer B, first two probes (ref :554 evaluates B only if A is in the filter)
-    {
-      const uint32_t n2 = s_n[1];
-      for (uint32_t base = 0; base < n2; base += kCtaThreads) {
-        const uint32_t i = base + threadIdx.x;
-        bool pass = false;
-        uint16_t q = 0;
-        if (i < n2) {
-          q = s_q[1][i];
-          const uint64_t n = (j_begin + q) * t + (t - 1);
-          const uint64_t b = flagged ? select_of(rv, vb0 + uint32_t(n)) : dp.offset + n + d;
-          uint64_t f, rr;
-          hash_kmer(rb.packed, g0 + b, k, s_tab, f, rr);
-          sB[q] = make_ulonglong2(f, rr);
-          pass = bloom_probe_range(bf, rr < f ? rr : f, kseed, 0, h_first, n_probe);
-        }
-        queue_push(pass, q, s_q[0], &s_n[2]);
-      }
-    }
-    __syncthreads();
-    // ---- stage 4: remaining probes of B
-    {
-      const uint32_t n3 = s_n[2];
-      for (uint32_t base = 0; base < n3; base += kCtaThreads) {
-        const uint32_t i = base + threadIdx.x;
-        bool pass = false;
-        uint16_t q = 0;
-        if (i < n3) {
-          q = s_q[0][i];
-          const ulonglong2 h = sB[q];
-          pass = bloom_probe_range(bf, h.y < h.x ? h.y : h.x, kseed, h_first, bf.hash_num, n_probe);
-        }
-        queue_push(pass, q, s_q[1], &s_n[3]);
-      }
-    }
-    __syncthreads();
-    // ---- stage 5: pair key + first-wins insert; fresh pairs are staged for the dense list
-    {
-      const uint32_t n4 = s_n[3];
-      for (uint32_t base = 0; base < n4; base += kCtaThreads) {
-        const uint32_t i = base + threadIdx.x;
-        bool fresh = false;
-        uint16_t q = 0;
-        if (i < n4) {
-          q = s_q[1][i];
-          const ulonglong2 ha = sA[q], hb = sB[q];
-          uint64_t h_a, h_b; // ref :546-552
-          if (ha.x < hb.y) { h_a = hb.y; h_b = ha.y; } else { h_a = ha.x; h_b = hb.x; }
-          const uint64_t n = (j_begin + q) * t + (t - 1);
-          fresh = pair_insert(pv, h_a, h_b, make_okey(rb.first_read_idx + r, di, n), multi_d);
-          if (fresh) sB[q] = make_ulonglong2(h_a, h_b);
-        }
-        queue_push(fresh, q, s_q[0], &s_n[4]);
-      }
-      if (threadIdx.x == 0) n_surv += n4;
-    }
-    __syncthreads();
-    // ---- append the tile's fresh pairs to the dense unique-pair list (one global atomic per tile)
-    {
-      const uint32_t n5 = s_n[4];
-      if (n5) {
-        if (threadIdx.x == 0) s_list_base = atomicAdd(&ctr->n_unique, (unsigned long long)n5);
-        __syncthreads();
-        const unsigned long long lb = s_list_base;
-        for (uint32_t i = threadIdx.x; i < n5; i += kCtaThreads) pv.list[lb + i] = sB[s_q[0][i]];
-      }
-    }
-    n_probe_acc += n_probe;
-    __syncthreads();
-  }
-  n_cand = warp_sum_ull(n_cand); n_surv = warp_sum_ull(n_surv);
-  n_probe_acc = warp_sum_ull(n_probe_acc);
-  if ((threadIdx.x & 31) == 0) {
-    if (n_cand) atomicAdd(&ctr->n_candidates, n_cand);
-    if (n_surv) atomicAdd(&ctr->n_survivors, n_surv);
-    if (n_probe_acc) atomicAdd(&ctr->n_bf_probes, n_probe_acc);
-  }
 }
 
 // re-insert every occupied slot of `src` into `dst` (growth) -- also used by links_pairs_import

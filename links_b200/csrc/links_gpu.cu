@@ -8,6 +8,7 @@
 //                  -> reduce-by-key -> D2H rows -> mirror expansion + final ordering on the host
 // There is no CPU implementation of any of these stages in this library.
 #include "../../include/links_gpu.h"
+#include "extract.cuh"
 #include "kernels.cuh"
 
 #include <algorithm>
@@ -69,7 +70,7 @@ struct links_ctx {
   bool own_compute_stream = true;
 
   // ntHash table + distance params on device
-  DevBuf d_tab, d_dist, d_step, d_minallowed;
+  DevBuf d_tab, d_tab2, d_dist, d_step, d_minallowed, d_cursor;
   uint64_t kseed = 0;
 
   // Bloom filter
@@ -215,7 +216,6 @@ PairView pair_view(PairSlot* p, uint64_t cap, ulonglong2* list)
   return pv;
 }
 uint64_t pair_list_capacity(uint64_t cap) { return cap / 10 * 7 + 1024; }
-size_t extract_smem_bytes(uint32_t k) { return (size_t(k) * 4 + 2 * size_t(kTile)) * sizeof(ulonglong2); }
 BloomView bloom_view(links_ctx* c)
 {
   BloomView bf;
@@ -225,6 +225,23 @@ BloomView bloom_view(links_ctx* c)
   bf.hash_num = c->hash_num;
   return bf;
 }
+
+// extract_kernel is instantiated for the Bloom hash counts LINKS produces in practice
+// (hash_num = floor(-log2(fpr)): 9 for the default -p 0.001) and once with a runtime count.
+using ExtractFn = void (*)(ReadBatch, DistParams, int, uint64_t, const ulonglong2*, BloomView, PairView, Counters*);
+ExtractFn extract_fn_for(uint32_t hash_num)
+{
+  switch (hash_num) {
+  case 6: return extract_kernel<6>;
+  case 7: return extract_kernel<7>;
+  case 8: return extract_kernel<8>;
+  case 9: return extract_kernel<9>;
+  case 10: return extract_kernel<10>;
+  case 13: return extract_kernel<13>;
+  default: return extract_kernel<0>;
+  }
+}
+const uint32_t kExtractVariants[] = {0, 6, 7, 8, 9, 10, 13};
 
 // exclusive scan of n u32 (in place allowed); total written to *d_total (device)
 int device_scan(links_ctx* c, cudaStream_t s, uint32_t* d_in, uint64_t n, uint32_t* d_out, DevBuf& tmp, uint32_t* d_total)
@@ -517,10 +534,17 @@ int links_create(links_ctx** out, const links_params* p)
     CUC(cudaMemcpy(c->d_minallowed.p, c->min_allowed.data(), p->n_dist * 4, cudaMemcpyHostToDevice));
     CUC(c->d_ctr.ensure(sizeof(Counters)));
     CUC(cudaMemset(c->d_ctr.p, 0, sizeof(Counters)));
-    CUC(cudaFuncSetAttribute(extract_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, int(extract_smem_bytes(p->k))));
+    std::vector<ulonglong2> tab2(size_t(nthash_pair_count(p->k)) * 16);
+    build_nthash_pair_table(p->k, tab2.data());
+    CUC(c->d_tab2.ensure(tab2.size() * sizeof(ulonglong2)));
+    CUC(cudaMemcpy(c->d_tab2.p, tab2.data(), tab2.size() * sizeof(ulonglong2), cudaMemcpyHostToDevice));
+    CUC(c->d_cursor.ensure(64));
     int occ = 0;
-    CUC(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, extract_kernel, kCtaThreads, extract_smem_bytes(p->k)));
-    c->extract_ctas_per_sm = std::max(occ, 1);
+    for (uint32_t h : kExtractVariants) {
+      CUC(cudaFuncSetAttribute(extract_fn_for(h), cudaFuncAttributeMaxDynamicSharedMemorySize, int(extract_smem_bytes(p->k))));
+      CUC(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, extract_fn_for(h), kCtaThreads, extract_smem_bytes(p->k)));
+      c->extract_ctas_per_sm = std::max(occ, 1);
+    }
     CUC(cudaHostAlloc(reinterpret_cast<void**>(&c->h_snap), sizeof(Counters) * links_ctx::kSnaps, cudaHostAllocDefault));
     for (int i = 0; i < links_ctx::kSnaps; ++i) CUC(cudaEventCreateWithFlags(&c->ev_snap[i], cudaEventDisableTiming));
   }
@@ -549,7 +573,7 @@ void links_destroy(links_ctx* c)
   if (c->h_snap) cudaFreeHost(c->h_snap);
   for (DevBuf* b : {&c->f_keys[0], &c->f_keys[1], &c->f_vals[0], &c->f_vals[1], &c->f_issues, &c->f_tiglen, &c->f_hist,
                     &c->f_scan_tmp, &c->f_flags, &c->f_total, &c->f_okeys, &c->f_olinks, &c->f_ogaps, &c->f_final, &c->f_exch, &c->f_il, &c->f_ig}) b->release();
-  c->d_tab.release(); c->d_dist.release(); c->d_step.release(); c->d_minallowed.release();
+  c->d_tab.release(); c->d_tab2.release(); c->d_cursor.release(); c->d_dist.release(); c->d_step.release(); c->d_minallowed.release();
   c->d_bloom.release(); c->d_pairs.release(); c->d_pair_list.release(); c->d_ctr.release(); c->d_table.release();
   if (c->s_compute && c->own_compute_stream) cudaStreamDestroy(c->s_compute);
   if (c->s_copy) cudaStreamDestroy(c->s_copy);
@@ -685,10 +709,12 @@ static int push_read_chunk(links_ctx* c, const char* seq, const uint8_t* dev_seq
       Span sp(c, F_EXTRACT, c->s_compute);
       ReadBatch rb{b.packed.as<uint32_t>(), b.inv.as<uint32_t>(), b.off.as<uint64_t>(), b.base0, b.segs.as<uint32_t>(),
                    b.n_seq, b.n_tiles, b.flags.as<uint32_t>(), b.vs.as<unsigned long long>(), b.vrank.as<uint32_t>(),
-                   first_read_idx};
+                   first_read_idx, c->d_cursor.as<unsigned int>()};
       DistParams dp{c->d_dist.as<uint32_t>(), c->d_step.as<uint32_t>(), c->prm.n_dist, c->prm.offset};
-      extract_kernel<<<grid_for(c, b.n_tiles, 1, c->extract_ctas_per_sm), kCtaThreads, extract_smem_bytes(c->prm.k), c->s_compute>>>(
-        rb, dp, int(c->prm.k), c->kseed, c->d_tab.as<ulonglong2>(), bloom_view(c),
+      CU(c, cudaMemsetAsync(c->d_cursor.p, 0, sizeof(unsigned int), c->s_compute));
+      extract_fn_for(c->hash_num)<<<grid_for(c, b.n_tiles, kWarpsPerCta, c->extract_ctas_per_sm), kCtaThreads,
+                                    extract_smem_bytes(c->prm.k), c->s_compute>>>(
+        rb, dp, int(c->prm.k), c->kseed, c->d_tab2.as<ulonglong2>(), bloom_view(c),
         pair_view(c->d_pairs.as<PairSlot>(), c->pair_cap, c->d_pair_list.as<ulonglong2>()), c->d_ctr.as<Counters>());
       c->launches++;
       c->extract_launches++;
@@ -714,10 +740,14 @@ static int reads_push_impl(links_ctx* c, const char* seq, const uint8_t* dev_seq
   const uint32_t k = c->prm.k, nd = c->prm.n_dist;
   const uint64_t o = c->prm.offset;
   // chunk the push at record boundaries so copies overlap kernels
-  static const uint64_t kChunkBases = []() {
+  // Chunk size in bases.  Host pushes ramp up (8 MB, 16, 32, then 64 MB chunks) so the first copy that
+  // nothing can overlap is short while later launches are long enough to amortise their tails;
+  // device-resident pushes have no copy to overlap and take 64 MB chunks from the start.
+  static const uint64_t kChunkMax = []() {
     const char* e = getenv("LINKS_CHUNK_BASES");
-    return e ? strtoull(e, nullptr, 10) : (16ull << 20);
+    return e ? strtoull(e, nullptr, 10) : (64ull << 20);
   }();
+  uint64_t kChunkBases = dev_seq ? kChunkMax : std::min<uint64_t>(kChunkMax, 8ull << 20);
   const uint64_t kChunkCand = 1ull << 27;
   // upper bound on candidates per (read, distance): exact when the read has no invalid base (reference src/LINKS.hpp:525-543)
   auto seg_count = [&](uint64_t len, uint32_t di) -> uint64_t {
@@ -745,7 +775,7 @@ static int reads_push_impl(links_ctx* c, const char* seq, const uint8_t* dev_seq
       for (uint32_t di = 0; di < nd; ++di) {
         segs.push_back(uint32_t(tiles));
         const uint64_t cnt = seg_count(len, di);
-        tiles += (cnt + kTile - 1) / kTile;
+        tiles += (cnt + kExtractTile - 1) / kExtractTile;
         cand += cnt;
       }
       if (tiles >= (1ull << 31)) return fail(c, LINKS_E_LIMIT, "links_reads_push: chunk too large");
@@ -755,6 +785,7 @@ static int reads_push_impl(links_ctx* c, const char* seq, const uint8_t* dev_seq
     int rc = push_read_chunk(c, seq, dev_seq, off + i0, i - i0, first_read_idx + i0, segs, cand, total_cand - done_cand);
     if (rc) return rc;
     i0 = i;
+    kChunkBases = std::min(kChunkMax, kChunkBases * 2);
   }
   CU(c, cudaStreamSynchronize(c->s_copy)); // host buffers reusable
   return LINKS_OK;

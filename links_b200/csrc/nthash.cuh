@@ -10,6 +10,7 @@
 #pragma once
 #include <cstdint>
 #include <cuda_runtime.h>
+#include <vector>
 
 namespace links {
 
@@ -67,6 +68,59 @@ __device__ __forceinline__ void hash_kmer(const uint32_t* __restrict__ packed, u
     for (int b = 0; b < 16; ++b) {
       if (b < nb) {
         const ulonglong2 e = tab[(i + b) * 4 + ((win >> (2 * b)) & 3u)];
+        f ^= e.x;
+        r ^= e.y;
+      }
+    }
+    cur = nxt;
+  }
+  fwd = f;
+  rev = r;
+}
+
+// ---- two bases per lookup.  Because the hash is XOR-linear, the contributions of k-mer offsets
+// 2p and 2p+1 can be pre-XORed: tab2[p*16 + c4] with c4 = code(2p) | code(2p+1)<<2 (the 4 bits
+// the packed stream already holds).  Halves the shared-memory loads and the XORs per k-mer.
+// For odd k the last entry ignores its high two bits (the base after the k-mer).
+inline unsigned nthash_pair_count(unsigned k) { return (k + 1) / 2; }
+inline void build_nthash_pair_table(unsigned k, ulonglong2* tab2)
+{
+  std::vector<ulonglong2> one(size_t(k) * 4);
+  build_nthash_table(k, one.data());
+  for (unsigned p = 0; p < nthash_pair_count(k); ++p)
+    for (unsigned c4 = 0; c4 < 16; ++c4) {
+      ulonglong2 e = one[(2 * p) * 4 + (c4 & 3)];
+      if (2 * p + 1 < k) {
+        const ulonglong2 e2 = one[(2 * p + 1) * 4 + (c4 >> 2)];
+        e.x ^= e2.x;
+        e.y ^= e2.y;
+      }
+      tab2[p * 16 + c4] = e;
+    }
+}
+
+__device__ __forceinline__ void hash_kmer2(const uint32_t* __restrict__ packed, uint64_t g, int k,
+                                           const ulonglong2* __restrict__ tab2, uint64_t& fwd, uint64_t& rev)
+{
+  const uint64_t w = g >> 4;
+  const int sh = int(g & 15) * 2;
+  const int npairs = (k + 1) >> 1;
+  uint32_t cur = __ldg(packed + w);
+  uint64_t f = 0, r = 0;
+  for (int p0 = 0; p0 < npairs; p0 += 8) {
+    const uint32_t nxt = __ldg(packed + w + 1 + (p0 >> 3));
+    const uint32_t win = __funnelshift_r(cur, nxt, sh);
+    const ulonglong2* t = tab2 + p0 * 16;
+    if (npairs - p0 >= 8) {
+#pragma unroll
+      for (int p = 0; p < 8; ++p) {
+        const ulonglong2 e = t[p * 16 + ((win >> (4 * p)) & 15u)];
+        f ^= e.x;
+        r ^= e.y;
+      }
+    } else {
+      for (int p = 0; p < npairs - p0; ++p) {
+        const ulonglong2 e = t[p * 16 + ((win >> (4 * p)) & 15u)];
         f ^= e.x;
         r ^= e.y;
       }
@@ -156,6 +210,35 @@ __device__ __forceinline__ bool bloom_probe_range(const BloomView& bf, uint64_t 
     if (miss) { probes += __ffs(miss); return false; }
     probes += n;
     i0 += n;
+  }
+  return true;
+}
+
+// N probes starting at i0, N known at compile time: all loads in flight together, no predicated-off
+// bodies.  Accounting as in bloom_probe_range.
+template <int N>
+__device__ __forceinline__ bool bloom_probe_fixed(const BloomView& bf, uint64_t h0, uint64_t kseed, uint32_t i0, uint32_t& probes)
+{
+  if (N <= 0) return true;
+  uint32_t miss = 0;
+#pragma unroll
+  for (int j = 0; j < N; ++j) miss |= (bloom_bit(bf, h0, kseed, i0 + j) ^ 1u) << j;
+  if (miss) { probes += __ffs(miss); return false; }
+  probes += N;
+  return true;
+}
+
+// runtime count, groups of four then singles (generic hash_num)
+__device__ __forceinline__ bool bloom_probe_loop(const BloomView& bf, uint64_t h0, uint64_t kseed, uint32_t i0, uint32_t i1,
+                                                 uint32_t& probes)
+{
+  while (i0 + 4 <= i1) {
+    if (!bloom_probe_fixed<4>(bf, h0, kseed, i0, probes)) return false;
+    i0 += 4;
+  }
+  for (; i0 < i1; ++i0) {
+    ++probes;
+    if (!bloom_bit(bf, h0, kseed, i0)) return false;
   }
   return true;
 }
