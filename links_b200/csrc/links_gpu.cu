@@ -66,7 +66,7 @@ struct links_ctx {
   std::vector<uint32_t> step;
   std::vector<int32_t> min_allowed;
   std::string err;
-  cudaStream_t s_compute = nullptr, s_copy = nullptr;
+  cudaStream_t s_compute = nullptr, s_copy = nullptr, s_aux = nullptr;
   bool own_compute_stream = true;
 
   // ntHash table + distance params on device
@@ -82,13 +82,14 @@ struct links_ctx {
   // contigs (resident)
   std::vector<SeqBatchDev*> contig_batches;
   std::vector<SeqBatchDev*> contig_pool; // released by links_reset, buffers kept
-  cudaEvent_t ev_contig = nullptr;
+  cudaEvent_t ev_contig = nullptr, ev_contig_packed = nullptr, ev_cleared = nullptr;
+  bool contig_pack_pending = false;
   std::vector<uint32_t> tig_len; // [0] = 0
   uint64_t contig_positions = 0;
   uint32_t n_tigs_seen = 0;
 
   // read chunk slots
-  static constexpr int kSlots = 2;
+  static constexpr int kSlots = 3;
   SeqBatchDev slot[kSlots];
   DevBuf slot_ascii[kSlots];
   cudaEvent_t ev_copied[kSlots]{}, ev_done[kSlots]{};
@@ -113,9 +114,12 @@ struct links_ctx {
   // counters
   DevBuf d_ctr;
 
-  // contig table
+  // contig table (built on s_aux while the reads stream in; finalize waits on ev_table)
   DevBuf d_table;
   uint64_t table_cap = 0;
+  cudaEvent_t ev_table = nullptr, ev_fork = nullptr;
+  size_t table_batches_built = 0;
+  bool table_started = false;
 
   // stage-4 scratch (kept across links_reset so repeated jobs do not re-allocate)
   DevBuf f_final;
@@ -516,7 +520,12 @@ int links_create(links_ctx** out, const links_params* p)
   c->sm_count = prop.multiProcessorCount;
   CUC(cudaStreamCreateWithFlags(&c->s_compute, cudaStreamNonBlocking));
   CUC(cudaStreamCreateWithFlags(&c->s_copy, cudaStreamNonBlocking));
+  CUC(cudaStreamCreateWithFlags(&c->s_aux, cudaStreamNonBlocking));
+  CUC(cudaEventCreateWithFlags(&c->ev_table, cudaEventDisableTiming));
+  CUC(cudaEventCreateWithFlags(&c->ev_fork, cudaEventDisableTiming));
   CUC(cudaEventCreateWithFlags(&c->ev_contig, cudaEventDisableTiming));
+  CUC(cudaEventCreateWithFlags(&c->ev_contig_packed, cudaEventDisableTiming));
+  CUC(cudaEventCreateWithFlags(&c->ev_cleared, cudaEventDisableTiming));
   for (int i = 0; i < links_ctx::kSlots; ++i) {
     CUC(cudaEventCreateWithFlags(&c->ev_copied[i], cudaEventDisableTiming));
     CUC(cudaEventCreateWithFlags(&c->ev_done[i], cudaEventDisableTiming));
@@ -563,6 +572,8 @@ void links_destroy(links_ctx* c)
   for (auto* b : c->contig_batches) { b->release(); delete b; }
   for (auto* b : c->contig_pool) { b->release(); delete b; }
   if (c->ev_contig) cudaEventDestroy(c->ev_contig);
+  if (c->ev_contig_packed) cudaEventDestroy(c->ev_contig_packed);
+  if (c->ev_cleared) cudaEventDestroy(c->ev_cleared);
   for (int i = 0; i < links_ctx::kSlots; ++i) {
     c->slot[i].release(); c->slot_ascii[i].release();
     if (c->ev_copied[i]) cudaEventDestroy(c->ev_copied[i]);
@@ -577,6 +588,9 @@ void links_destroy(links_ctx* c)
   c->d_bloom.release(); c->d_pairs.release(); c->d_pair_list.release(); c->d_ctr.release(); c->d_table.release();
   if (c->s_compute && c->own_compute_stream) cudaStreamDestroy(c->s_compute);
   if (c->s_copy) cudaStreamDestroy(c->s_copy);
+  if (c->s_aux) cudaStreamDestroy(c->s_aux);
+  if (c->ev_table) cudaEventDestroy(c->ev_table);
+  if (c->ev_fork) cudaEventDestroy(c->ev_fork);
   cudaGetLastError();
   delete c;
 }
@@ -586,6 +600,7 @@ int links_sync(links_ctx* c)
   if (!c) return LINKS_E_INVAL;
   CU(c, cudaSetDevice(c->device));
   CU(c, cudaStreamSynchronize(c->s_copy));
+  CU(c, cudaStreamSynchronize(c->s_aux));
   CU(c, cudaStreamSynchronize(c->s_compute));
   return LINKS_OK;
 }
@@ -659,9 +674,11 @@ static int contigs_push_impl(links_ctx* c, const char* seq, const uint8_t* dev_s
   b->first_id = first_tig_id;
   cudaEvent_t ev = c->ev_contig;
   // the single contig staging buffer is reused: wait until the previous pack consumed it
-  if (!dev_seq) CU(c, cudaStreamSynchronize(c->s_compute));
+  if (!dev_seq && c->contig_pack_pending) CU(c, cudaEventSynchronize(c->ev_contig_packed));
   int rc = upload_and_pack(c, *b, c->contig_ascii, seq, dev_seq, off, n, segs, false, c->s_copy, c->s_compute, ev);
   if (rc) { b->release(); delete b; return rc; }
+  CU(c, cudaEventRecord(c->ev_contig_packed, c->s_compute));
+  c->contig_pack_pending = true;
   c->contig_batches.push_back(b);
   c->contig_positions += positions;
   c->n_tigs_seen = std::max(c->n_tigs_seen, first_tig_id + n - 1);
@@ -697,6 +714,7 @@ static int push_read_chunk(links_ctx* c, const char* seq, const uint8_t* dev_seq
     // the slot's previous chunk must have been consumed by its kernels before we overwrite it
     CU(c, cudaEventSynchronize(c->ev_done[si]));
   }
+  CU(c, cudaStreamWaitEvent(c->s_compute, c->ev_cleared, 0));  // links_reset clears the pair set on s_aux
   int rc = ensure_pair_capacity(c, cand, later);
   if (rc) return rc;
   SeqBatchDev& b = c->slot[si];
@@ -728,6 +746,8 @@ static int push_read_chunk(links_ctx* c, const char* seq, const uint8_t* dev_seq
   return LINKS_OK;
 }
 
+static int start_table_build(links_ctx* c);
+
 static int reads_push_impl(links_ctx* c, const char* seq, const uint8_t* dev_seq, const uint64_t* off, uint32_t n,
                            uint64_t first_read_idx)
 {
@@ -737,6 +757,10 @@ static int reads_push_impl(links_ctx* c, const char* seq, const uint8_t* dev_seq
   if (n == 0) return LINKS_OK;
   if (first_read_idx + n >= (1ull << 28)) return fail(c, LINKS_E_LIMIT, "links_reads_push: more than 2^28 reads");
   CU(c, cudaSetDevice(c->device));
+  {
+    const int rc = start_table_build(c);
+    if (rc) return rc;
+  }
   const uint32_t k = c->prm.k, nd = c->prm.n_dist;
   const uint64_t o = c->prm.offset;
   // chunk the push at record boundaries so copies overlap kernels
@@ -769,9 +793,11 @@ static int reads_push_impl(links_ctx* c, const char* seq, const uint8_t* dev_seq
     segs.clear();
     uint64_t tiles = 0, cand = 0;
     uint32_t i = i0;
+    // host pushes also taper off: the last chunk's kernels run after its copy with nothing left to overlap
+    const uint64_t chunk_limit = dev_seq ? kChunkBases : std::min(kChunkBases, std::max<uint64_t>((off[n] - off[i0]) / 2, 8ull << 20));
     for (; i < n; ++i) {
       const uint64_t len = off[i + 1] - off[i];
-      if (i > i0 && (off[i + 1] - off[i0] > kChunkBases || cand > kChunkCand || uint64_t(i - i0) * nd > (1ull << 26))) break;
+      if (i > i0 && (off[i + 1] - off[i0] > chunk_limit || cand > kChunkCand || uint64_t(i - i0) * nd > (1ull << 26))) break;
       for (uint32_t di = 0; di < nd; ++di) {
         segs.push_back(uint32_t(tiles));
         const uint64_t cnt = seg_count(len, di);
@@ -818,7 +844,9 @@ int links_reset(links_ctx* c)
   if (!c) return LINKS_E_INVAL;
   CU(c, cudaSetDevice(c->device));
   CU(c, cudaStreamSynchronize(c->s_copy));
+  CU(c, cudaStreamSynchronize(c->s_aux));
   CU(c, cudaStreamSynchronize(c->s_compute));
+  c->table_started = false; c->table_batches_built = 0;
   poll_snapshots(c);
   for (auto* b : c->contig_batches) c->contig_pool.push_back(b);
   c->contig_batches.clear();
@@ -830,9 +858,12 @@ int links_reset(links_ctx* c)
   for (int i = 0; i < links_ctx::kSlots; ++i) c->slot_used[i] = false;
   CU(c, cudaMemsetAsync(c->d_ctr.p, 0, sizeof(Counters), c->s_compute));
   if (c->pair_cap) {
-    Span sp(c, F_GROW, c->s_compute);
-    CU(c, cudaMemsetAsync(c->d_pairs.p, 0xFF, c->pair_cap * sizeof(PairSlot), c->s_compute));
+    // off the compute stream: the Bloom build and the first copies do not have to wait for it
+    Span sp(c, F_GROW, c->s_aux);
+    CU(c, cudaMemsetAsync(c->d_pairs.p, 0xFF, c->pair_cap * sizeof(PairSlot), c->s_aux));
   }
+  CU(c, cudaEventRecord(c->ev_cleared, c->s_aux));
+  c->contig_pack_pending = false;
   c->finalized = false;
   return LINKS_OK;
 }
@@ -842,6 +873,7 @@ int links_get_timing(links_ctx* c, links_timing* t, int reset)
   if (!c || !t) return LINKS_E_INVAL;
   CU(c, cudaSetDevice(c->device));
   CU(c, cudaStreamSynchronize(c->s_copy));
+  CU(c, cudaStreamSynchronize(c->s_aux));
   CU(c, cudaStreamSynchronize(c->s_compute));
   resolve_spans(c);
   t->ms_h2d = c->fam_ms[F_H2D]; t->ms_pack = c->fam_ms[F_PACK]; t->ms_bf_build = c->fam_ms[F_BF];
@@ -853,26 +885,44 @@ int links_get_timing(links_ctx* c, links_timing* t, int reset)
   return LINKS_OK;
 }
 
-static int build_table(links_ctx* c)
+static int build_table(links_ctx* c, cudaStream_t st)
 {
   const uint32_t k = c->prm.k;
   const uint64_t entries = c->contig_positions * 2;
   const uint64_t cap = 1ull << log2_ceil(std::max<uint64_t>(entries * 2, 1ull << 10));
   CU(c, c->d_table.ensure((cap + 1) * sizeof(TableSlot)));
   c->table_cap = cap;
-  Span sp(c, F_TABLE, c->s_compute);
+  Span sp(c, F_TABLE, st);
+  CU(c, cudaMemsetAsync(reinterpret_cast<char*>(c->d_ctr.p) + offsetof(Counters, n_contig_kmers), 0, sizeof(unsigned long long), st));
   // keys = EMPTY (all ones), vals = 0
-  table_init_kernel<<<grid_for(c, cap + 1, 256 * 4, 16), 256, 0, c->s_compute>>>(c->d_table.as<TableSlot>(), cap + 1);
+  table_init_kernel<<<grid_for(c, cap + 1, 256 * 4, 16), 256, 0, st>>>(c->d_table.as<TableSlot>(), cap + 1);
   c->launches++;
   for (auto* b : c->contig_batches) {
     if (!b->n_tiles) continue;
     ContigBatch cb{b->packed.as<uint32_t>(), b->inv.as<uint32_t>(), b->off.as<uint64_t>(), b->base0,
                    b->segs.as<uint32_t>(), b->n_seq, b->n_tiles, b->first_id};
-    contig_kernel<1><<<grid_for(c, b->n_tiles, 1, 8), kCtaThreads, k * 4 * sizeof(ulonglong2), c->s_compute>>>(
+    contig_kernel<1><<<grid_for(c, b->n_tiles, 1, 8), kCtaThreads, k * 4 * sizeof(ulonglong2), st>>>(
       cb, int(k), c->kseed, c->d_tab.as<ulonglong2>(), bloom_view(c), table_view(c), c->d_ctr.as<Counters>());
     c->launches++;
   }
   CU(c, cudaGetLastError());
+  c->table_batches_built = c->contig_batches.size();
+  return LINKS_OK;
+}
+
+// The contig k-mer table needs only the contigs, which are resident before the first read
+// arrives (call order of the reference: Bloom filter -> reads -> contigs; here the contigs come
+// with the filter).  Start it on the auxiliary stream at the first reads push so it runs under the
+// reads' H2D copies and extract launches instead of in front of stage 4.
+static int start_table_build(links_ctx* c)
+{
+  if (c->table_started || c->contig_batches.empty()) return LINKS_OK;
+  CU(c, cudaEventRecord(c->ev_fork, c->s_compute));  // contig packs (and the counter reset) are ordered before
+  CU(c, cudaStreamWaitEvent(c->s_aux, c->ev_fork, 0));
+  int rc = build_table(c, c->s_aux);
+  if (rc) return rc;
+  CU(c, cudaEventRecord(c->ev_table, c->s_aux));
+  c->table_started = true;
   return LINKS_OK;
 }
 
@@ -886,8 +936,15 @@ int links_finalize(links_ctx* c, links_row** rows_out, uint64_t* n_rows_out, lin
   CU(c, cudaSetDevice(c->device));
   cudaStream_t s = c->s_compute;
   CU(c, cudaStreamSynchronize(c->s_copy));
-  int rc = build_table(c);
-  if (rc) return rc;
+  CU(c, cudaStreamWaitEvent(s, c->ev_cleared, 0));
+  int rc = LINKS_OK;
+  if (c->table_started && c->table_batches_built == c->contig_batches.size()) {
+    CU(c, cudaStreamWaitEvent(s, c->ev_table, 0));
+  } else {  // no read was pushed, or contigs arrived after the early build: (re)build here
+    if (c->table_started) CU(c, cudaStreamSynchronize(c->s_aux));
+    rc = build_table(c, s);
+    if (rc) return rc;
+  }
   // unique pair count sizes the row buffers
   CU(c, cudaStreamSynchronize(s));
   Counters h;
@@ -1270,6 +1327,7 @@ int links_pairs_import(links_ctx* c, const void* dev_records, uint64_t n_records
   if (c->finalized) return fail(c, LINKS_E_INVAL, "links_pairs_import: context already finalized (links_reset first)");
   if (!n_records) return LINKS_OK;
   CU(c, cudaSetDevice(c->device));
+  CU(c, cudaStreamWaitEvent(c->s_compute, c->ev_cleared, 0));
   int rc = ensure_pair_capacity(c, n_records, 0);
   if (rc) return rc;
   {
