@@ -13,7 +13,8 @@
 //   bloom    u32[bytes/4]          btllib byte array viewed as little-endian words
 //   table    {u64 key,u64 val}[cap+1]   key = ntHash (fwd or rev) of a contig k-mer, EMPTY = ~0
 //                                  val = pos<<32 | tig<<3 | orient<<2 | multiple<<1 | present
-//   pairs    {u64 h_a,u64 h_b,u64 okey,u64 pad}[cap]   32 B = one DRAM sector per probe
+//   pairs    {u64 h_a,u64 h_b}[cap]         16 B slots, two per DRAM sector; 128-bit CAS claims a slot
+//   okeys    u64[cap]                       order key of the slot's pair (only allocated when n_dist > 1)
 //   rows     u64 key[] + i32 distance[]  (dense packed row key, see pack_row_key)
 #pragma once
 #include "device_prims.cuh"
@@ -29,10 +30,14 @@ constexpr int kTile = 1024;        // candidates (or contig positions) per sched
 constexpr int kCtaThreads = 256;
 
 struct TableSlot { uint64_t key, val; };
-struct PairSlot { uint64_t a, b, okey, pad; };
+struct PairSlot { uint64_t a, b; };
 
 struct TableView { TableSlot* slots; uint64_t mask; int shift; /* 64 - log2(cap) */ };
-struct PairView { PairSlot* slots; uint64_t mask; int shift; ulonglong2* list; /* dense (h_a,h_b) of every distinct pair, in insertion order */ };
+struct PairView {
+  PairSlot* slots; uint64_t mask; int shift;
+  ulonglong2* list;            // dense (h_a,h_b) of every distinct pair, in insertion order
+  unsigned long long* okeys;   // per-slot minimum order key; nullptr when there is a single distance
+};
 
 // counters accumulated on the device (one atomic per warp at kernel end)
 struct Counters {
@@ -101,13 +106,24 @@ __global__ void __launch_bounds__(kCtaThreads) pack_kernel(const uint8_t* __rest
       bytes[j] = v;
     }
   }
+  // four bases per step, SWAR on the 32-bit word (bytes b0..b3 = bases j..j+3):
+  //   code   = (byte >> 1) & 3; the multiply gathers the four 2-bit codes into one byte
+  //            (terms land on disjoint even bit positions, so no carries)
+  //   valid  = byte & 0xDF in {A,C,G,T,U}: with v = (byte & 0xDF) ^ 0x40 that is v in {1,3,7,20,21},
+  //            i.e. top three bits clear and  (~b4 & ~b3 & b0 & (~b2 | b1)) | (b4 & ~b3 & b2 & ~b1)
   uint32_t p[2] = {0, 0};
   uint32_t m = 0;
 #pragma unroll
-  for (int j = 0; j < 32; ++j) {
-    const uint32_t c = (bytes[j >> 2] >> (8 * (j & 3))) & 0xFFu;
-    p[j >> 4] |= base_code(c) << (2 * (j & 15));
-    m |= (base_valid(c) ? 0u : 1u) << j;
+  for (int j = 0; j < 8; ++j) {
+    const uint32_t w = bytes[j];
+    const uint32_t x = (w >> 1) & 0x03030303u;
+    p[j >> 2] |= (((x * 0x00041041u) >> 18) & 0xFFu) << (8 * (j & 3));
+    const uint32_t v = (w & 0xDFDFDFDFu) ^ 0x40404040u;
+    const uint32_t b0 = v, b1 = v >> 1, b2 = v >> 2, b3 = v >> 3, b4 = v >> 4;
+    const uint32_t hi = (v >> 5) | (v >> 6) | (v >> 7);
+    const uint32_t ok = ((~b4 & ~b3 & b0 & (~b2 | b1)) | (b4 & ~b3 & b2 & ~b1)) & ~hi;
+    const uint32_t bad = ~ok & 0x01010101u;
+    m |= (((bad * 0x01020408u) >> 24) & 0xFu) << (4 * j);
   }
   packed[t * 2] = p[0];
   packed[t * 2 + 1] = p[1];
@@ -324,7 +340,7 @@ __device__ __forceinline__ bool pair_insert(const PairView& pv, uint64_t a, uint
       if (cur.x == kEmpty && cur.y == kEmpty) { fresh = true; cur = make_ulonglong2(a, b); }
     }
     if (cur.x == a && cur.y == b) {
-      if (multi_d) atomicMin(reinterpret_cast<unsigned long long*>(&s->okey), (unsigned long long)okey);
+      if (multi_d) atomicMin(pv.okeys + i, (unsigned long long)okey);
       return fresh;
     }
     i = (i + 1) & pv.mask;
@@ -338,7 +354,7 @@ __device__ __forceinline__ uint64_t pair_okey(const PairView& pv, uint64_t a, ui
   for (;;) {
     const PairSlot* s = pv.slots + i;
     const ulonglong2 cur = __ldg(reinterpret_cast<const ulonglong2*>(s));
-    if (cur.x == a && cur.y == b) return s->okey;
+    if (cur.x == a && cur.y == b) return pv.okeys ? pv.okeys[i] : 0ull;
     if (cur.x == kEmpty && cur.y == kEmpty) return kEmpty; // not present (cannot happen for listed pairs)
     i = (i + 1) & pv.mask;
   }
@@ -355,13 +371,14 @@ __host__ __device__ __forceinline__ uint32_t okey_d_idx(uint64_t okey)
 }
 
 // re-insert every occupied slot of `src` into `dst` (growth) -- also used by links_pairs_import
-__global__ void pair_rehash_kernel(const PairSlot* __restrict__ src, uint64_t n_src, PairView dst, Counters* ctr, int count_unique)
+__global__ void pair_rehash_kernel(const PairSlot* __restrict__ src, const unsigned long long* __restrict__ src_okeys, uint64_t n_src,
+                                   PairView dst, Counters* ctr, int count_unique)
 {
   unsigned long long fresh = 0;
   for (uint64_t i = uint64_t(blockIdx.x) * blockDim.x + threadIdx.x; i < n_src; i += uint64_t(gridDim.x) * blockDim.x) {
     const PairSlot s = src[i];
     if (s.a == kEmpty && s.b == kEmpty) continue;
-    if (pair_insert(dst, s.a, s.b, s.okey, true)) ++fresh;
+    if (pair_insert(dst, s.a, s.b, src_okeys ? src_okeys[i] : 0ull, src_okeys != nullptr)) ++fresh;
   }
   if (count_unique) {
     fresh = warp_sum_ull(fresh);

@@ -66,7 +66,7 @@ struct links_ctx {
   std::vector<uint32_t> step;
   std::vector<int32_t> min_allowed;
   std::string err;
-  cudaStream_t s_compute = nullptr, s_copy = nullptr, s_aux = nullptr;
+  cudaStream_t s_compute = nullptr, s_copy = nullptr, s_aux = nullptr, s_pack = nullptr;
   bool own_compute_stream = true;
 
   // ntHash table + distance params on device
@@ -89,16 +89,16 @@ struct links_ctx {
   uint32_t n_tigs_seen = 0;
 
   // read chunk slots
-  static constexpr int kSlots = 3;
+  static constexpr int kSlots = 5;
   SeqBatchDev slot[kSlots];
   DevBuf slot_ascii[kSlots];
-  cudaEvent_t ev_copied[kSlots]{}, ev_done[kSlots]{};
+  cudaEvent_t ev_copied[kSlots]{}, ev_done[kSlots]{}, ev_packed[kSlots]{};
   bool slot_used[kSlots] = {false, false};
   int next_slot = 0;
   DevBuf contig_ascii;
 
   // pair set
-  DevBuf d_pairs, d_pair_list;
+  DevBuf d_pairs, d_pair_list, d_pair_okeys;  // okeys only when n_dist > 1
   uint64_t pair_cap = 0;
   int extract_ctas_per_sm = 4;
   uint64_t cand_total = 0;   // candidates enqueued so far (upper bound on inserts)
@@ -180,6 +180,19 @@ struct Span {
 
 void resolve_spans(links_ctx* c)
 {
+  static const bool dbg = getenv("LINKS_DEBUG_TIMELINE") != nullptr;  // device timeline of every span since the last resolve
+  if (dbg && !c->spans.empty()) {
+    static const char* names[] = {"h2d", "pack", "bf", "table", "extract", "classify", "sort", "d2h", "grow", "exchange"};
+    cudaEvent_t t0 = c->spans.front().a;
+    for (auto& sp : c->spans) {
+      float a = 0, b = 0;
+      cudaEventSynchronize(sp.b);
+      cudaEventElapsedTime(&a, t0, sp.a);
+      cudaEventElapsedTime(&b, t0, sp.b);
+      fprintf(stderr, "[links timeline] %-8s %8.3f -> %8.3f ms\n", names[sp.fam], a, b);
+    }
+    fprintf(stderr, "[links timeline] ----\n");
+  }
   for (auto& sp : c->spans) {
     float ms = 0;
     if (cudaEventSynchronize(sp.b) == cudaSuccess && cudaEventElapsedTime(&ms, sp.a, sp.b) == cudaSuccess) c->fam_ms[sp.fam] += ms;
@@ -213,11 +226,16 @@ TableView table_view(links_ctx* c)
   tv.shift = 64 - log2_ceil(c->table_cap ? c->table_cap : 2);
   return tv;
 }
-PairView pair_view(PairSlot* p, uint64_t cap, ulonglong2* list)
+PairView pair_view(PairSlot* p, uint64_t cap, ulonglong2* list, unsigned long long* okeys)
 {
   PairView pv;
-  pv.slots = p; pv.mask = cap ? cap - 1 : 0; pv.shift = 64 - log2_ceil(cap ? cap : 2); pv.list = list;
+  pv.slots = p; pv.mask = cap ? cap - 1 : 0; pv.shift = 64 - log2_ceil(cap ? cap : 2); pv.list = list; pv.okeys = okeys;
   return pv;
+}
+PairView pair_view(links_ctx* c)
+{
+  return pair_view(c->d_pairs.as<PairSlot>(), c->pair_cap, c->d_pair_list.as<ulonglong2>(),
+                   c->prm.n_dist > 1 ? c->d_pair_okeys.as<unsigned long long>() : nullptr);
 }
 uint64_t pair_list_capacity(uint64_t cap) { return cap / 10 * 7 + 1024; }
 BloomView bloom_view(links_ctx* c)
@@ -398,6 +416,10 @@ int ensure_pair_capacity(links_ctx* c, uint64_t incoming, uint64_t later)
   poll_snapshots(c);
   if (fits(c->pair_cap)) return LINKS_OK;
   // tighten with the exact count
+  static const bool dbg = getenv("LINKS_DEBUG") != nullptr;
+  if (dbg) fprintf(stderr, "[links] pair-set capacity check blocks: cap=%llu known_unique=%llu in-flight cand=%llu incoming=%llu\n",
+                   (unsigned long long)c->pair_cap, (unsigned long long)c->known_unique,
+                   (unsigned long long)(c->cand_total - c->known_cand), (unsigned long long)incoming);
   CU(c, cudaStreamSynchronize(c->s_compute));
   poll_snapshots(c);
   Counters h;
@@ -410,22 +432,26 @@ int ensure_pair_capacity(links_ctx* c, uint64_t incoming, uint64_t later)
   const double projected = double(c->known_unique) + rate * double(later) + 2.0 * double(incoming);
   const uint64_t want = uint64_t(std::max(projected, double(bound())) / 0.7) + 1024;
   const uint64_t cap = 1ull << log2_ceil(std::max<uint64_t>(want, 1ull << 16));
-  DevBuf nb, nl;
+  DevBuf nb, nl, nk;
+  const bool multi_d = c->prm.n_dist > 1;
   CU(c, nb.ensure(cap * sizeof(PairSlot)));
   CU(c, nl.ensure(pair_list_capacity(cap) * sizeof(ulonglong2)));
+  if (multi_d) CU(c, nk.ensure(cap * 8));
   {
     Span sp(c, F_GROW, c->s_compute);
     CU(c, cudaMemsetAsync(nb.p, 0xFF, cap * sizeof(PairSlot), c->s_compute));
+    if (multi_d) CU(c, cudaMemsetAsync(nk.p, 0xFF, cap * 8, c->s_compute));
     if (c->pair_cap && c->known_unique) {
       pair_rehash_kernel<<<grid_for(c, c->pair_cap, 256, 8), 256, 0, c->s_compute>>>(
-        c->d_pairs.as<PairSlot>(), c->pair_cap, pair_view(nb.as<PairSlot>(), cap, nl.as<ulonglong2>()), c->d_ctr.as<Counters>(), 0);
+        c->d_pairs.as<PairSlot>(), multi_d ? c->d_pair_okeys.as<unsigned long long>() : nullptr, c->pair_cap,
+        pair_view(nb.as<PairSlot>(), cap, nl.as<ulonglong2>(), multi_d ? nk.as<unsigned long long>() : nullptr), c->d_ctr.as<Counters>(), 0);
       c->launches++;
       CU(c, cudaMemcpyAsync(nl.p, c->d_pair_list.p, c->known_unique * sizeof(ulonglong2), cudaMemcpyDeviceToDevice, c->s_compute));
     }
   }
   CU(c, cudaStreamSynchronize(c->s_compute));
-  c->d_pairs.release(); c->d_pair_list.release();
-  c->d_pairs = nb; c->d_pair_list = nl;
+  c->d_pairs.release(); c->d_pair_list.release(); c->d_pair_okeys.release();
+  c->d_pairs = nb; c->d_pair_list = nl; c->d_pair_okeys = nk;
   c->pair_cap = cap;
   return LINKS_OK;
 }
@@ -521,6 +547,7 @@ int links_create(links_ctx** out, const links_params* p)
   CUC(cudaStreamCreateWithFlags(&c->s_compute, cudaStreamNonBlocking));
   CUC(cudaStreamCreateWithFlags(&c->s_copy, cudaStreamNonBlocking));
   CUC(cudaStreamCreateWithFlags(&c->s_aux, cudaStreamNonBlocking));
+  CUC(cudaStreamCreateWithFlags(&c->s_pack, cudaStreamNonBlocking));
   CUC(cudaEventCreateWithFlags(&c->ev_table, cudaEventDisableTiming));
   CUC(cudaEventCreateWithFlags(&c->ev_fork, cudaEventDisableTiming));
   CUC(cudaEventCreateWithFlags(&c->ev_contig, cudaEventDisableTiming));
@@ -529,6 +556,7 @@ int links_create(links_ctx** out, const links_params* p)
   for (int i = 0; i < links_ctx::kSlots; ++i) {
     CUC(cudaEventCreateWithFlags(&c->ev_copied[i], cudaEventDisableTiming));
     CUC(cudaEventCreateWithFlags(&c->ev_done[i], cudaEventDisableTiming));
+    CUC(cudaEventCreateWithFlags(&c->ev_packed[i], cudaEventDisableTiming));
   }
   {
     std::vector<ulonglong2> tab(size_t(p->k) * 4);
@@ -578,6 +606,7 @@ void links_destroy(links_ctx* c)
     c->slot[i].release(); c->slot_ascii[i].release();
     if (c->ev_copied[i]) cudaEventDestroy(c->ev_copied[i]);
     if (c->ev_done[i]) cudaEventDestroy(c->ev_done[i]);
+    if (c->ev_packed[i]) cudaEventDestroy(c->ev_packed[i]);
   }
   c->contig_ascii.release();
   for (int i = 0; i < links_ctx::kSnaps; ++i) if (c->ev_snap[i]) cudaEventDestroy(c->ev_snap[i]);
@@ -585,10 +614,11 @@ void links_destroy(links_ctx* c)
   for (DevBuf* b : {&c->f_keys[0], &c->f_keys[1], &c->f_vals[0], &c->f_vals[1], &c->f_issues, &c->f_tiglen, &c->f_hist,
                     &c->f_scan_tmp, &c->f_flags, &c->f_total, &c->f_okeys, &c->f_olinks, &c->f_ogaps, &c->f_final, &c->f_exch, &c->f_il, &c->f_ig}) b->release();
   c->d_tab.release(); c->d_tab2.release(); c->d_cursor.release(); c->d_dist.release(); c->d_step.release(); c->d_minallowed.release();
-  c->d_bloom.release(); c->d_pairs.release(); c->d_pair_list.release(); c->d_ctr.release(); c->d_table.release();
+  c->d_bloom.release(); c->d_pairs.release(); c->d_pair_list.release(); c->d_pair_okeys.release(); c->d_ctr.release(); c->d_table.release();
   if (c->s_compute && c->own_compute_stream) cudaStreamDestroy(c->s_compute);
   if (c->s_copy) cudaStreamDestroy(c->s_copy);
   if (c->s_aux) cudaStreamDestroy(c->s_aux);
+  if (c->s_pack) cudaStreamDestroy(c->s_pack);
   if (c->ev_table) cudaEventDestroy(c->ev_table);
   if (c->ev_fork) cudaEventDestroy(c->ev_fork);
   cudaGetLastError();
@@ -719,8 +749,11 @@ static int push_read_chunk(links_ctx* c, const char* seq, const uint8_t* dev_seq
   if (rc) return rc;
   SeqBatchDev& b = c->slot[si];
   b.first_read_idx = first_read_idx;
-  rc = upload_and_pack(c, b, c->slot_ascii[si], seq, dev_seq, off, n, segs, true, c->s_copy, c->s_compute, c->ev_copied[si]);
+  // copy on s_copy, pack on s_pack, extract on s_compute: chunk i+1 is packed while chunk i is being extracted
+  rc = upload_and_pack(c, b, c->slot_ascii[si], seq, dev_seq, off, n, segs, true, c->s_copy, c->s_pack, c->ev_copied[si]);
   if (rc) return rc;
+  CU(c, cudaEventRecord(c->ev_packed[si], c->s_pack));
+  CU(c, cudaStreamWaitEvent(c->s_compute, c->ev_packed[si], 0));
   c->cand_total += cand;
   if (b.n_tiles) {
     {
@@ -733,7 +766,7 @@ static int push_read_chunk(links_ctx* c, const char* seq, const uint8_t* dev_seq
       extract_fn_for(c->hash_num)<<<grid_for(c, b.n_tiles, kWarpsPerCta, c->extract_ctas_per_sm), kCtaThreads,
                                     extract_smem_bytes(c->prm.k), c->s_compute>>>(
         rb, dp, int(c->prm.k), c->kseed, c->d_tab2.as<ulonglong2>(), bloom_view(c),
-        pair_view(c->d_pairs.as<PairSlot>(), c->pair_cap, c->d_pair_list.as<ulonglong2>()), c->d_ctr.as<Counters>());
+        pair_view(c), c->d_ctr.as<Counters>());
       c->launches++;
       c->extract_launches++;
       CU(c, cudaGetLastError());
@@ -856,11 +889,13 @@ int links_reset(links_ctx* c)
   c->cand_total = 0; c->known_unique = 0; c->known_cand = 0;
   for (int i = 0; i < links_ctx::kSnaps; ++i) c->snap_live[i] = false;
   for (int i = 0; i < links_ctx::kSlots; ++i) c->slot_used[i] = false;
+  c->next_slot = 0;  // same chunk -> slot assignment every job: slot buffers stop growing after the first one
   CU(c, cudaMemsetAsync(c->d_ctr.p, 0, sizeof(Counters), c->s_compute));
   if (c->pair_cap) {
     // off the compute stream: the Bloom build and the first copies do not have to wait for it
     Span sp(c, F_GROW, c->s_aux);
     CU(c, cudaMemsetAsync(c->d_pairs.p, 0xFF, c->pair_cap * sizeof(PairSlot), c->s_aux));
+    if (c->prm.n_dist > 1) CU(c, cudaMemsetAsync(c->d_pair_okeys.p, 0xFF, c->pair_cap * 8, c->s_aux));
   }
   CU(c, cudaEventRecord(c->ev_cleared, c->s_aux));
   c->contig_pack_pending = false;
@@ -973,7 +1008,7 @@ int links_finalize(links_ctx* c, links_row** rows_out, uint64_t* n_rows_out, lin
       ClassifyParams cp{c->d_dist.as<uint32_t>(), c->d_minallowed.as<int32_t>(), c->prm.n_dist, d_tiglen.as<uint32_t>(), tb,
                         d_keys[0].as<uint64_t>(), d_vals[0].as<int32_t>(), row_cap, d_issues.as<IssueRec>(), issue_cap};
       classify_kernel<<<grid_for(c, n_unique, kCtaThreads, 8), kCtaThreads, 0, s>>>(
-        pair_view(c->d_pairs.as<PairSlot>(), c->pair_cap, c->d_pair_list.as<ulonglong2>()), n_unique, table_view(c), cp,
+        pair_view(c), n_unique, table_view(c), cp,
         int(c->prm.k), c->d_ctr.as<Counters>());
       c->launches++;
       CU(c, cudaGetLastError());
@@ -1167,7 +1202,7 @@ int links_pairs_download(links_ctx* c, uint64_t* h_a, uint64_t* h_b, uint32_t* d
   struct Cleanup { DevBuf& a; ~Cleanup() { a.release(); } } cl{d_out};
   CU(c, d_out.ensure(h.n_unique * 24));
   pair_export_kernel<<<grid_for(c, h.n_unique, 256, 8), 256, 0, c->s_compute>>>(
-    pair_view(c->d_pairs.as<PairSlot>(), c->pair_cap, c->d_pair_list.as<ulonglong2>()), h.n_unique, d_out.as<uint64_t>());
+    pair_view(c), h.n_unique, d_out.as<uint64_t>());
   c->launches++;
   CU(c, cudaGetLastError());
   std::vector<uint64_t> tmp(h.n_unique * 3);
@@ -1279,7 +1314,7 @@ int links_pairs_export(links_ctx* c, uint32_t n_ranks, void* dev_dst, uint64_t c
   CU(c, c->f_exch.ensure(size_t(kMaxRanks) * 2 * 8));
   unsigned long long* d_counts = c->f_exch.as<unsigned long long>();
   unsigned long long* d_cursors = d_counts + kMaxRanks;
-  const PairView pv = pair_view(c->d_pairs.as<PairSlot>(), c->pair_cap, c->d_pair_list.as<ulonglong2>());
+  const PairView pv = pair_view(c);
   {
     Span sp(c, F_EXCHANGE, s);
     CU(c, cudaMemsetAsync(d_counts, 0, size_t(kMaxRanks) * 8, s));
@@ -1318,6 +1353,7 @@ int links_pairs_clear(links_ctx* c)
   Span sp(c, F_EXCHANGE, c->s_compute);
   CU(c, cudaMemsetAsync(reinterpret_cast<char*>(c->d_ctr.p) + offsetof(Counters, n_unique), 0, sizeof(unsigned long long), c->s_compute));
   if (c->pair_cap) CU(c, cudaMemsetAsync(c->d_pairs.p, 0xFF, c->pair_cap * sizeof(PairSlot), c->s_compute));
+  if (c->pair_cap && c->prm.n_dist > 1) CU(c, cudaMemsetAsync(c->d_pair_okeys.p, 0xFF, c->pair_cap * 8, c->s_compute));
   return LINKS_OK;
 }
 
@@ -1334,7 +1370,7 @@ int links_pairs_import(links_ctx* c, const void* dev_records, uint64_t n_records
     Span sp(c, F_EXCHANGE, c->s_compute);
     pair_import_kernel<<<grid_for(c, n_records, kCtaThreads, 8), kCtaThreads, 0, c->s_compute>>>(
       static_cast<const uint64_t*>(dev_records), n_records,
-      pair_view(c->d_pairs.as<PairSlot>(), c->pair_cap, c->d_pair_list.as<ulonglong2>()), c->prm.n_dist > 1 ? 1 : 0, c->d_ctr.as<Counters>());
+      pair_view(c), c->prm.n_dist > 1 ? 1 : 0, c->d_ctr.as<Counters>());
     c->launches++;
     CU(c, cudaGetLastError());
   }
