@@ -86,10 +86,12 @@ typedef struct links_stats {
   uint64_t n_candidates;   /* (A,B) k-mer pairs visited (before the Bloom test) */
   uint64_t n_survivors;    /* passed both Bloom tests (src/LINKS.hpp:554-555) */
   uint64_t n_unique_pairs; /* distinct ordered (h_a,h_b) = mate_pair.size() */
-  uint64_t n_bf_probes;    /* Bloom bit tests actually performed (roofline accounting) */
+  uint64_t n_bf_probes;    /* Bloom bit tests of the reference's early-exit loop (bloom_filter.hpp:648-659) over these k-mers (roofline accounting) */
   uint64_t n_contig_kmers; /* valid contig k-mer positions hashed into the table (x2 strands) */
   uint64_t ct_ok_pairs, ct_problem_pairs, ct_ok_contig, ct_iz_issues, ct_illogical, ct_gate_fail;
   uint64_t n_rows;
+  uint64_t n_bf_loads;       /* Bloom bit tests the kernels issued (proven members skip theirs, see links_bf_covers_contigs) */
+  uint64_t n_member_sectors; /* 32-byte sectors of the exact member set read instead */
 } links_stats;
 
 /* ---- lifetime ---- */
@@ -117,6 +119,13 @@ int links_bf_size(uint64_t assembly_file_bytes, float fpr, uint64_t* m_bits, uin
 int links_bf_alloc(links_ctx* ctx, uint64_t bytes, uint32_t hash_num);
 /* new KmerBloomFilter(path) (-r): caller parsed the file; bits are uploaded, contigs_push will NOT insert. */
 int links_bf_load(links_ctx* ctx, const uint8_t* bits, uint64_t bytes, uint32_t hash_num);
+/* The device keeps, beside the filter, the exact set of canonical hashes this context inserted into it;
+ * a read k-mer found there is known to pass BloomFilter::contains (no false negatives,
+ * bloom_filter.hpp:639-659) and skips its hash_num probes.  After links_bf_load* the contigs are not
+ * inserted, so that shortcut is off unless the caller vouches that the loaded bits were built from (a
+ * superset of) the contigs about to be pushed: yes = 1, before the first links_contigs_push.
+ * Results are identical either way; wrongly vouching is the caller's error. */
+int links_bf_covers_contigs(links_ctx* ctx, int yes);
 /* Raw bit array for KmerBloomFilter::save (bloom_filter.hpp:866-888); dst holds `bytes`. */
 int links_bf_download(links_ctx* ctx, uint8_t* dst);
 /* Exact header text of the .bloom file; returns its length (0 if cap too small). */

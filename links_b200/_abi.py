@@ -56,7 +56,7 @@ class LinksStats(C.Structure):
     _fields_ = [(n, C.c_uint64) for n in (
         "n_candidates", "n_survivors", "n_unique_pairs", "n_bf_probes", "n_contig_kmers",
         "ct_ok_pairs", "ct_problem_pairs", "ct_ok_contig", "ct_iz_issues", "ct_illogical", "ct_gate_fail",
-        "n_rows")]
+        "n_rows", "n_bf_loads", "n_member_sectors")]
 
 
 class LinksTiming(C.Structure):
@@ -81,6 +81,7 @@ SIGNATURES = {
     "links_bf_alloc": (C.c_int, [C.c_void_p, C.c_uint64, C.c_uint32]),
     "links_bf_load": (C.c_int, [C.c_void_p, C.c_void_p, C.c_uint64, C.c_uint32]),
     "links_bf_download": (C.c_int, [C.c_void_p, C.c_void_p]),
+    "links_bf_covers_contigs": (C.c_int, [C.c_void_p, C.c_int]),
     "links_bf_header": (C.c_size_t, [C.c_char_p, C.c_size_t, C.c_uint32, C.c_uint32, C.c_uint64]),
     "links_contigs_push": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint32, C.c_uint32]),
     "links_reads_push": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint32, C.c_uint64]),

@@ -68,7 +68,7 @@ __device__ __forceinline__ uint32_t warp_push_slot(bool pass, uint32_t n, uint32
 template <int H>
 __global__ void __launch_bounds__(kCtaThreads, LINKS_EXTRACT_MIN_CTAS) extract_kernel(ReadBatch rb, DistParams dp, int k, uint64_t kseed,
                                                                  const ulonglong2* __restrict__ g_tab2, BloomView bf,
-                                                                 PairView pv, Counters* __restrict__ ctr)
+                                                                 MemberView mv, PairView pv, Counters* __restrict__ ctr)
 {
   extern __shared__ ulonglong2 s_dyn[];
   const int n_tab = ((k + 1) >> 1) * 16;
@@ -85,8 +85,9 @@ __global__ void __launch_bounds__(kCtaThreads, LINKS_EXTRACT_MIN_CTAS) extract_k
   constexpr int kRest = H >= 2 ? H - 2 : 0;
   const uint32_t n_seg = rb.n_seq * dp.n_dist;
   unsigned long long n_cand = 0, n_surv = 0;
-  uint32_t n_probe = 0;
-  unsigned long long n_probe_acc = 0;
+  uint32_t n_probe = 0, n_load = 0, n_msec = 0;  // reference-order bit tests, bit tests issued, member-set sectors
+  unsigned long long n_probe_acc = 0, n_load_acc = 0, n_msec_acc = 0;
+  const bool has_set = mv.buckets != nullptr;
 
   for (;;) {
     uint32_t tile = 0;
@@ -143,18 +144,27 @@ __global__ void __launch_bounds__(kCtaThreads, LINKS_EXTRACT_MIN_CTAS) extract_k
 
       if (stage == 1) {  // ---- S1: hash A, first probes
         const uint32_t q = next_q + lane;
-        bool pass = false;
+        bool pass = false, member = false;
         uint64_t h0 = 0;
         if (q < n_tile) {
           uint64_t f, rr;
           hash_kmer2(rb.packed, pos_a(rank_n(q)), k, s_tab, f, rr);
           h0 = rr < f ? rr : f;
-          pass = H ? bloom_probe_fixed<kFirst>(bf, h0, kseed, 0, n_probe) : bloom_probe_loop(bf, h0, kseed, 0, h_first, n_probe);
+          if (has_set) member = member_contains(mv, h0, n_msec);
+          if (member) n_probe += hn;  // the filter holds every set key: all hash_num bits are set, no need to look
+          else {
+            pass = H ? bloom_probe_fixed<kFirst>(bf, h0, kseed, 0, n_probe) : bloom_probe_loop(bf, h0, kseed, 0, h_first, n_probe);
+            n_load += h_first;
+          }
         }
         next_q += 32;
         uint32_t slot;
         n1 = warp_push_slot(pass, n1, slot);
         if (pass) { Q.q1_i[slot] = uint16_t(q); Q.q1_h[slot] = h0; }
+        if (has_set) {  // proven members skip S2
+          n2 = warp_push_slot(member, n2, slot);
+          if (member) Q.q2_i[slot] = uint16_t(q);
+        }
       } else if (stage == 2) {  // ---- S2: remaining probes of A
         const uint32_t take = n1 < 32u ? n1 : 32u;
         n1 -= take;
@@ -164,6 +174,7 @@ __global__ void __launch_bounds__(kCtaThreads, LINKS_EXTRACT_MIN_CTAS) extract_k
           q = Q.q1_i[n1 + lane];
           const uint64_t h0 = Q.q1_h[n1 + lane];
           pass = H ? bloom_probe_fixed<kRest>(bf, h0, kseed, kFirst, n_probe) : bloom_probe_loop(bf, h0, kseed, h_first, hn, n_probe);
+          n_load += hn - h_first;
         }
         __syncwarp();
         uint32_t slot;
@@ -172,19 +183,28 @@ __global__ void __launch_bounds__(kCtaThreads, LINKS_EXTRACT_MIN_CTAS) extract_k
       } else if (stage == 3) {  // ---- S3: hash B, first probes (ref :554 tests B only if A is in the filter)
         const uint32_t take = n2 < 32u ? n2 : 32u;
         n2 -= take;
-        bool pass = false;
+        bool pass = false, member = false;
         uint16_t q = 0;
         uint64_t f = 0, rr = 0;
         if (uint32_t(lane) < take) {
           q = Q.q2_i[n2 + lane];
           hash_kmer2(rb.packed, pos_b(rank_n(q)), k, s_tab, f, rr);
           const uint64_t h0 = rr < f ? rr : f;
-          pass = H ? bloom_probe_fixed<kFirst>(bf, h0, kseed, 0, n_probe) : bloom_probe_loop(bf, h0, kseed, 0, h_first, n_probe);
+          if (has_set) member = member_contains(mv, h0, n_msec);
+          if (member) n_probe += hn;
+          else {
+            pass = H ? bloom_probe_fixed<kFirst>(bf, h0, kseed, 0, n_probe) : bloom_probe_loop(bf, h0, kseed, 0, h_first, n_probe);
+            n_load += h_first;
+          }
         }
         __syncwarp();
         uint32_t slot;
         n3 = warp_push_slot(pass, n3, slot);
         if (pass) { Q.q3_i[slot] = q; Q.q3_f[slot] = f; Q.q3_r[slot] = rr; }
+        if (has_set) {  // proven members skip S4
+          n4 = warp_push_slot(member, n4, slot);
+          if (member) { Q.q4_i[slot] = q; Q.q4_f[slot] = f; Q.q4_r[slot] = rr; }
+        }
       } else if (stage == 4) {  // ---- S4: remaining probes of B
         const uint32_t take = n3 < 32u ? n3 : 32u;
         n3 -= take;
@@ -195,6 +215,7 @@ __global__ void __launch_bounds__(kCtaThreads, LINKS_EXTRACT_MIN_CTAS) extract_k
           q = Q.q3_i[n3 + lane]; f = Q.q3_f[n3 + lane]; rr = Q.q3_r[n3 + lane];
           const uint64_t h0 = rr < f ? rr : f;
           pass = H ? bloom_probe_fixed<kRest>(bf, h0, kseed, kFirst, n_probe) : bloom_probe_loop(bf, h0, kseed, h_first, hn, n_probe);
+          n_load += hn - h_first;
         }
         __syncwarp();
         uint32_t slot;
@@ -229,14 +250,18 @@ __global__ void __launch_bounds__(kCtaThreads, LINKS_EXTRACT_MIN_CTAS) extract_k
       }
       __syncwarp();
     }
-    n_probe_acc += n_probe;
-    n_probe = 0;
+    n_probe_acc += n_probe; n_load_acc += n_load; n_msec_acc += n_msec;
+    n_probe = 0; n_load = 0; n_msec = 0;
   }
   n_probe_acc = warp_sum_ull(n_probe_acc);
+  n_load_acc = warp_sum_ull(n_load_acc);
+  n_msec_acc = warp_sum_ull(n_msec_acc);
   if (lane == 0) {
     if (n_cand) atomicAdd(&ctr->n_candidates, n_cand);
     if (n_surv) atomicAdd(&ctr->n_survivors, n_surv);
     if (n_probe_acc) atomicAdd(&ctr->n_bf_probes, n_probe_acc);
+    if (n_load_acc) atomicAdd(&ctr->n_bf_loads, n_load_acc);
+    if (n_msec_acc) atomicAdd(&ctr->n_member_sectors, n_msec_acc);
   }
 }
 

@@ -41,7 +41,7 @@ struct PairView {
 
 // counters accumulated on the device (one atomic per warp at kernel end)
 struct Counters {
-  unsigned long long n_candidates, n_survivors, n_unique, n_bf_probes, n_contig_kmers;
+  unsigned long long n_candidates, n_survivors, n_unique, n_bf_probes, n_contig_kmers, n_bf_loads, n_member_sectors;
   unsigned long long ct_ok_pairs, ct_problem_pairs, ct_ok_contig, ct_iz_issues, ct_illogical, ct_gate_fail;
   unsigned long long n_rows, n_issues, issue_overflow;
 };
@@ -65,6 +65,56 @@ __device__ __forceinline__ uint64_t slot_hash2(uint64_t a, uint64_t b)
   uint64_t x = a * 0x9E3779B97F4A7C15ULL + b;
   x ^= x >> 32;
   return x * 0xD6E8FEB86659FD93ULL;
+}
+
+// ------------------------------------------------------------------ exact member set of the Bloom filter's keys
+//
+// A Bloom filter has no false negatives: every canonical hash h0 inserted by the contig pass
+// answers `contains` with true (bloom_filter.hpp:639-659).  The set below holds exactly those h0,
+// so "h0 in set" proves the filter's answer with ONE 32-byte sector instead of hash_num probes;
+// only k-mers outside the set (read errors, false-positive candidates) take the real probes.
+// Results are identical by construction; the set exists only when this context inserted the
+// contigs into the filter itself (or the caller vouched for it, links_bf_assume_covers_contigs).
+// Layout: buckets of four u64 keys = one DRAM/L2 sector, home bucket = mulhi(slot_hash1(h0), n_buckets)
+// (any bucket count, so the set is exactly as big as its load factor asks -- at 5 Mbp it stays
+// L2-sized), overflow spills to the next bucket (load <= 0.5, so ~1.15 sectors per lookup).  ~0 marks a free
+// slot; the value ~0 itself is never stored (it simply takes the probe path).
+struct __align__(32) MemberBucket { unsigned long long s[4]; };
+struct MemberView { MemberBucket* buckets; uint64_t n_buckets; };
+
+__device__ __forceinline__ MemberBucket ld_bucket(const MemberBucket* p)
+{
+  MemberBucket r;
+  asm volatile("ld.global.nc.v4.u64 {%0,%1,%2,%3}, [%4];" : "=l"(r.s[0]), "=l"(r.s[1]), "=l"(r.s[2]), "=l"(r.s[3]) : "l"(p));
+  return r;
+}
+
+__device__ __forceinline__ void member_insert(const MemberView& mv, uint64_t h0)
+{
+  if (h0 == kEmpty) return;
+  uint64_t b = __umul64hi(slot_hash1(h0), mv.n_buckets);
+  for (;;) {
+    unsigned long long* s = mv.buckets[b].s;
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      unsigned long long cur = *reinterpret_cast<volatile unsigned long long*>(s + j);
+      if (cur == kEmpty) cur = atomicCAS(s + j, kEmpty, h0);
+      if (cur == kEmpty || cur == h0) return;
+    }
+    b = b + 1 == mv.n_buckets ? 0 : b + 1;
+  }
+}
+
+__device__ __forceinline__ bool member_contains(const MemberView& mv, uint64_t h0, uint32_t& sectors)
+{
+  uint64_t b = __umul64hi(slot_hash1(h0), mv.n_buckets);
+  for (;;) {
+    const MemberBucket v = ld_bucket(mv.buckets + b);
+    ++sectors;
+    if (v.s[0] == h0 || v.s[1] == h0 || v.s[2] == h0 || v.s[3] == h0) return h0 != kEmpty;
+    if (v.s[3] == kEmpty) return false;  // slots fill front to back: a free last slot ends the chain
+    b = b + 1 == mv.n_buckets ? 0 : b + 1;
+  }
 }
 
 // ------------------------------------------------------------------ pack
@@ -267,12 +317,13 @@ __device__ __forceinline__ uint64_t table_lookup(const TableView& tv, uint64_t h
   }
 }
 
-// MODE 0: Bloom insert (KmerBloomFilter::insert, bloom_filter.hpp:814-821)
+// MODE 0: Bloom insert (KmerBloomFilter::insert, bloom_filter.hpp:814-821) + member-set insert (mv.buckets != nullptr)
 // MODE 1: table insert of fwd and rev hash of every valid position (populate_mate_info, :577-598)
+// MODE 2: member-set insert only (the filter's bits came from links_bf_load*, the caller vouches they cover these contigs)
 template <int MODE>
 __global__ void __launch_bounds__(kCtaThreads) contig_kernel(ContigBatch cb, int k, uint64_t kseed,
                                                              const ulonglong2* __restrict__ g_tab, BloomView bf,
-                                                             TableView tv, Counters* __restrict__ ctr)
+                                                             TableView tv, MemberView mv, Counters* __restrict__ ctr)
 {
   extern __shared__ ulonglong2 s_tab[];
   for (int i = threadIdx.x; i < k * 4; i += blockDim.x) s_tab[i] = g_tab[i];
@@ -294,6 +345,9 @@ __global__ void __launch_bounds__(kCtaThreads) contig_kernel(ContigBatch cb, int
       hash_kmer(cb.packed, g0 + p, k, s_tab, f, r);
       if (MODE == 0) {
         bloom_insert(bf, f, r, kseed);
+        if (mv.buckets) member_insert(mv, r < f ? r : f);
+      } else if (MODE == 2) {
+        member_insert(mv, r < f ? r : f);
       } else {
         const uint64_t payload = (p << 32) | (uint64_t(cb.first_tig + c) << 3);
         table_insert(tv, f, payload);

@@ -78,6 +78,13 @@ struct links_ctx {
   uint64_t bf_bytes = 0;
   uint32_t hash_num = 0;
   bool bf_ready = false, bf_insert = false;
+  bool bf_covers_contigs = false;  // links_bf_covers_contigs(): a loaded filter is vouched to hold every pushed contig k-mer
+
+  // exact member set of the filter's keys (kernels.cuh MemberView); empty when disabled or not provable
+  DevBuf d_members;
+  uint64_t member_buckets = 0;   // buckets of the current job's set (0: none)
+  uint64_t member_positions = 0; // contig positions inserted so far
+  bool member_off = false;       // this job runs without the set (memory budget, LINKS_MEMBER_SET=0)
 
   // contigs (resident)
   std::vector<SeqBatchDev*> contig_batches;
@@ -238,6 +245,13 @@ PairView pair_view(links_ctx* c)
                    c->prm.n_dist > 1 ? c->d_pair_okeys.as<unsigned long long>() : nullptr);
 }
 uint64_t pair_list_capacity(uint64_t cap) { return cap / 10 * 7 + 1024; }
+MemberView member_view(links_ctx* c)
+{
+  MemberView mv;
+  mv.buckets = c->member_buckets ? c->d_members.as<MemberBucket>() : nullptr;
+  mv.n_buckets = c->member_buckets;
+  return mv;
+}
 BloomView bloom_view(links_ctx* c)
 {
   BloomView bf;
@@ -250,7 +264,7 @@ BloomView bloom_view(links_ctx* c)
 
 // extract_kernel is instantiated for the Bloom hash counts LINKS produces in practice
 // (hash_num = floor(-log2(fpr)): 9 for the default -p 0.001) and once with a runtime count.
-using ExtractFn = void (*)(ReadBatch, DistParams, int, uint64_t, const ulonglong2*, BloomView, PairView, Counters*);
+using ExtractFn = void (*)(ReadBatch, DistParams, int, uint64_t, const ulonglong2*, BloomView, MemberView, PairView, Counters*);
 ExtractFn extract_fn_for(uint32_t hash_num)
 {
   switch (hash_num) {
@@ -453,6 +467,39 @@ int ensure_pair_capacity(links_ctx* c, uint64_t incoming, uint64_t later)
   c->d_pairs.release(); c->d_pair_list.release(); c->d_pair_okeys.release();
   c->d_pairs = nb; c->d_pair_list = nl; c->d_pair_okeys = nk;
   c->pair_cap = cap;
+  return LINKS_OK;
+}
+
+// Member set sizing (kernels.cuh MemberView): two slots per contig k-mer position (load <= 0.5).
+// Called with the new batch already counted in contig_positions and listed last in contig_batches.
+// First sizing uses the filter's own size as the estimate of the assembly (make_bf gives it
+// ~1.8 bytes per base, src/LINKS.hpp:297-302) so that a multi-batch push rarely regrows.
+int ensure_member_capacity(links_ctx* c)
+{
+  static const bool env_off = []() { const char* e = getenv("LINKS_MEMBER_SET"); return e && e[0] == '0'; }();
+  if (env_off || c->member_off) { c->member_buckets = 0; c->member_off = true; return LINKS_OK; }
+  const uint64_t need_buckets = c->contig_positions / 2 + 1;  // 4 slots per bucket, load 0.5
+  if (c->member_buckets >= need_buckets) return LINKS_OK;
+  const uint64_t estimate = c->member_buckets ? need_buckets + need_buckets / 2 : std::max(need_buckets, c->bf_bytes * 9 / 32);
+  size_t free_b = 0, total_b = 0;
+  CU(c, cudaMemGetInfo(&free_b, &total_b));
+  if (estimate * sizeof(MemberBucket) > total_b / 8 && estimate * sizeof(MemberBucket) > c->d_members.cap) {
+    c->member_buckets = 0; c->member_off = true;  // large assemblies: every k-mer takes the probe path
+    return LINKS_OK;
+  }
+  CU(c, c->d_members.ensure(estimate * sizeof(MemberBucket)));
+  c->member_buckets = estimate;
+  CU(c, cudaMemsetAsync(c->d_members.p, 0xFF, estimate * sizeof(MemberBucket), c->s_compute));
+  for (size_t i = 0; i + 1 < c->contig_batches.size(); ++i) {  // earlier batches of this job
+    SeqBatchDev* b = c->contig_batches[i];
+    if (!b->n_tiles) continue;
+    ContigBatch cb{b->packed.as<uint32_t>(), b->inv.as<uint32_t>(), b->off.as<uint64_t>(), b->base0,
+                   b->segs.as<uint32_t>(), b->n_seq, b->n_tiles, b->first_id};
+    contig_kernel<2><<<grid_for(c, b->n_tiles, 1, 8), kCtaThreads, c->prm.k * 4 * sizeof(ulonglong2), c->s_compute>>>(
+      cb, int(c->prm.k), c->kseed, c->d_tab.as<ulonglong2>(), bloom_view(c), TableView{nullptr, 0, 0}, member_view(c), c->d_ctr.as<Counters>());
+    c->launches++;
+  }
+  CU(c, cudaGetLastError());
   return LINKS_OK;
 }
 
@@ -660,6 +707,15 @@ int links_bf_load(links_ctx* c, const uint8_t* bits, uint64_t bytes, uint32_t ha
   return LINKS_OK;
 }
 
+int links_bf_covers_contigs(links_ctx* c, int yes)
+{
+  if (!c) return LINKS_E_INVAL;
+  if (!c->bf_ready) return fail(c, LINKS_E_INVAL, "links_bf_covers_contigs: no Bloom filter");
+  if (!c->contig_batches.empty()) return fail(c, LINKS_E_INVAL, "links_bf_covers_contigs: call before the first links_contigs_push");
+  c->bf_covers_contigs = yes != 0;
+  return LINKS_OK;
+}
+
 int links_bf_download(links_ctx* c, uint8_t* dst)
 {
   if (!c || !dst) return LINKS_E_INVAL;
@@ -712,13 +768,22 @@ static int contigs_push_impl(links_ctx* c, const char* seq, const uint8_t* dev_s
   c->contig_batches.push_back(b);
   c->contig_positions += positions;
   c->n_tigs_seen = std::max(c->n_tigs_seen, first_tig_id + n - 1);
-  if (c->bf_insert && b->n_tiles) {
+  if ((c->bf_insert || c->bf_covers_contigs) && b->n_tiles) {
     Span sp(c, F_BF, c->s_compute);
+    rc = ensure_member_capacity(c);  // may re-insert the earlier batches into a larger set
+    if (rc) return rc;
     ContigBatch cb{b->packed.as<uint32_t>(), b->inv.as<uint32_t>(), b->off.as<uint64_t>(), b->base0,
                    b->segs.as<uint32_t>(), b->n_seq, b->n_tiles, b->first_id};
-    contig_kernel<0><<<grid_for(c, b->n_tiles, 1, 8), kCtaThreads, k * 4 * sizeof(ulonglong2), c->s_compute>>>(
-      cb, int(k), c->kseed, c->d_tab.as<ulonglong2>(), bloom_view(c), TableView{nullptr, 0, 0}, c->d_ctr.as<Counters>());
-    c->launches++;
+    if (c->bf_insert) {
+      contig_kernel<0><<<grid_for(c, b->n_tiles, 1, 8), kCtaThreads, k * 4 * sizeof(ulonglong2), c->s_compute>>>(
+        cb, int(k), c->kseed, c->d_tab.as<ulonglong2>(), bloom_view(c), TableView{nullptr, 0, 0}, member_view(c), c->d_ctr.as<Counters>());
+      c->launches++;
+    } else if (c->member_buckets) {
+      contig_kernel<2><<<grid_for(c, b->n_tiles, 1, 8), kCtaThreads, k * 4 * sizeof(ulonglong2), c->s_compute>>>(
+        cb, int(k), c->kseed, c->d_tab.as<ulonglong2>(), bloom_view(c), TableView{nullptr, 0, 0}, member_view(c), c->d_ctr.as<Counters>());
+      c->launches++;
+    }
+    c->member_positions = c->contig_positions;
     CU(c, cudaGetLastError());
   }
   CU(c, cudaStreamSynchronize(c->s_copy)); // host buffers reusable
@@ -765,7 +830,7 @@ static int push_read_chunk(links_ctx* c, const char* seq, const uint8_t* dev_seq
       CU(c, cudaMemsetAsync(c->d_cursor.p, 0, sizeof(unsigned int), c->s_compute));
       extract_fn_for(c->hash_num)<<<grid_for(c, b.n_tiles, kWarpsPerCta, c->extract_ctas_per_sm), kCtaThreads,
                                     extract_smem_bytes(c->prm.k), c->s_compute>>>(
-        rb, dp, int(c->prm.k), c->kseed, c->d_tab2.as<ulonglong2>(), bloom_view(c),
+        rb, dp, int(c->prm.k), c->kseed, c->d_tab2.as<ulonglong2>(), bloom_view(c), member_view(c),
         pair_view(c), c->d_ctr.as<Counters>());
       c->launches++;
       c->extract_launches++;
@@ -885,7 +950,8 @@ int links_reset(links_ctx* c)
   c->contig_batches.clear();
   c->tig_len.assign(1, 0);
   c->contig_positions = 0; c->n_tigs_seen = 0;
-  c->bf_ready = false; c->bf_insert = false;
+  c->bf_ready = false; c->bf_insert = false; c->bf_covers_contigs = false;
+  c->member_buckets = 0; c->member_positions = 0; c->member_off = false;
   c->cand_total = 0; c->known_unique = 0; c->known_cand = 0;
   for (int i = 0; i < links_ctx::kSnaps; ++i) c->snap_live[i] = false;
   for (int i = 0; i < links_ctx::kSlots; ++i) c->slot_used[i] = false;
@@ -937,7 +1003,7 @@ static int build_table(links_ctx* c, cudaStream_t st)
     ContigBatch cb{b->packed.as<uint32_t>(), b->inv.as<uint32_t>(), b->off.as<uint64_t>(), b->base0,
                    b->segs.as<uint32_t>(), b->n_seq, b->n_tiles, b->first_id};
     contig_kernel<1><<<grid_for(c, b->n_tiles, 1, 8), kCtaThreads, k * 4 * sizeof(ulonglong2), st>>>(
-      cb, int(k), c->kseed, c->d_tab.as<ulonglong2>(), bloom_view(c), table_view(c), c->d_ctr.as<Counters>());
+      cb, int(k), c->kseed, c->d_tab.as<ulonglong2>(), bloom_view(c), table_view(c), MemberView{nullptr, 0}, c->d_ctr.as<Counters>());
     c->launches++;
   }
   CU(c, cudaGetLastError());
@@ -1105,6 +1171,7 @@ int links_finalize(links_ctx* c, links_row** rows_out, uint64_t* n_rows_out, lin
     memset(stats, 0, sizeof *stats);
     stats->n_candidates = h.n_candidates; stats->n_survivors = h.n_survivors; stats->n_unique_pairs = h.n_unique;
     stats->n_bf_probes = h.n_bf_probes; stats->n_contig_kmers = h.n_contig_kmers;
+    stats->n_bf_loads = h.n_bf_loads; stats->n_member_sectors = h.n_member_sectors;
     stats->ct_ok_pairs = h.ct_ok_pairs; stats->ct_problem_pairs = h.ct_problem_pairs; stats->ct_ok_contig = h.ct_ok_contig;
     stats->ct_iz_issues = h.ct_iz_issues; stats->ct_illogical = h.ct_illogical; stats->ct_gate_fail = h.ct_gate_fail;
     stats->n_rows = n_out;

@@ -87,6 +87,7 @@ def replicate_bloom(L, nbytes: int, hash_num: int, dist, device, src: int = 0, g
     dist.broadcast(buf, src=src, group=group)
     if dist.get_rank(group) != src:
         L.bf_load_dev(buf.data_ptr(), nbytes, hash_num)
+        L.bf_covers_contigs(True)  # rank `src` built these bits from the same contigs every rank pushes next
 
 
 _BIN_CODE = {-1: 0, 10: 1, 500: 2, 5000: 3, 10000: 4}  # get_distance_bin's range (src/LINKS.hpp:764-770)

@@ -234,6 +234,10 @@ class Links:
         self._check(self._lib.links_bf_load_dev(self._h, dev_bits, nbytes, hash_num))
         self.bf_bytes, self.hash_num = nbytes, hash_num
 
+    def bf_covers_contigs(self, yes: bool = True) -> None:
+        """Vouch that a loaded filter was built from the contigs about to be pushed (links_gpu.h)."""
+        self._check(self._lib.links_bf_covers_contigs(self._h, 1 if yes else 0))
+
     def set_stream(self, cuda_stream: int) -> None:
         self._check(self._lib.links_set_stream(self._h, cuda_stream))
 
