@@ -33,6 +33,9 @@ import numpy as np
 
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
+# one hardware queue per stream (copy, pack, compute, aux, import, torch's, NCCL's): a kernel waiting for a peer
+# rank must never sit in front of this rank's own work.  Read by the driver when CUDA initialises.
+os.environ.setdefault("CUDA_DEVICE_MAX_CONNECTIONS", "32")
 
 METRIC = "kmer_pairs_per_sec_extracted_probed_mapped"
 UNIT = "pairs/s"
@@ -238,6 +241,13 @@ def main_ours(args, rank: int, world: int, local_rank: int):
     L = Links(LinksOptions(k=k, distances=d, step_sizes=t, device=local_rank))
     stream = torch.cuda.current_stream()
     L.set_stream(stream.cuda_stream)
+    # N > 1: pairs travel to their owner ranks through NVLink peer memory while the reads are still being
+    # extracted (links_exchange_attach); LINKS_EXCHANGE=nccl selects the stop-and-exchange all-to-all instead
+    p2p = world > 1 and os.environ.get("LINKS_EXCHANGE", "p2p") != "nccl"
+    keep_alive = None
+    if p2p:
+        est_pairs = int(reads.off[-1]) // 12  # ~0.06 distinct pairs per read base on this workload, x1.4
+        keep_alive = multi.attach_exchange(L, dist, torch.device("cuda", local_rank), inbox_bytes=max(64 << 20, est_pairs * 24 * 2 * 2))
 
     # inputs: pinned host copies (e2e leg) and device-resident copies (value leg)
     pc_seq, nb_c = pinned_copy(lib, contigs.seq)
@@ -297,12 +307,15 @@ def main_ours(args, rank: int, world: int, local_rank: int):
         else:
             L.push_reads_raw(pr_seq, pr_off, reads.n, first_read)
         mark("reads")
-        if world > 1:
+        if p2p:
+            L.exchange_finish()
+            state["exchange"] = {"transport": "peer memory (NVLink P2P), routed per extract launch"}
+        elif world > 1:
             state["exchange"] = multi.exchange_pairs(L, dist, dev, profile=phases)
             mark("exchange")
         rows, issues, stats = L.finalize()
         mark("finalize")
-        if world > 1:
+        if world > 1 and not p2p:
             rows = multi.gather_rows(rows, dist, dev, merge=L.rows_merge)
             mark("gather_rows")
         state["rows"], state["issues"], state["stats"] = rows, issues, stats
@@ -373,7 +386,9 @@ def main_ours(args, rank: int, world: int, local_rank: int):
                        "bf_probes": stats["n_bf_probes"], "rows": n_rows, "rows_digest": digest_res,
                        "l2": "inputs (250 MB reads, GB-scale pair set and contig table) exceed the 126 MB L2; no flush",
                        "sharding": ("reads by rank (each rank its own 50x read set), Bloom filter NCCL-broadcast from rank 0, contigs replicated, "
-                                    "distinct pairs routed by one NCCL all-to-all keyed on hash(h_a,h_b), rows summed on rank 0") if world > 1 else "single GPU",
+                                    + ("distinct pairs routed to their owner rank (hash of (h_a,h_b)) through NVLink peer memory by a kernel after "
+                                       "every extract launch and imported there while extraction continues, partial link rows summed on rank 0 on the device"
+                                       if p2p else "distinct pairs routed by one NCCL all-to-all keyed on hash(h_a,h_b), rows summed on rank 0")) if world > 1 else "single GPU",
                        "exchange_rank0": state.get("exchange")},
             "e2e": {"value": cand_total / (ms_e2e * 1e-3), "unit": UNIT, "ms_per_step": ms_e2e, "h2d_bytes_per_step": int(h2d_bytes),
                     "d2h_bytes_per_step": int(d2h_bytes)},
@@ -382,7 +397,11 @@ def main_ours(args, rank: int, world: int, local_rank: int):
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": None,
                          "kernel": "extract_kernel", "launches": n_launch, "ms_per_launch": ms_launch,
                          "algorithmic_bytes_per_launch": alg_bytes_launch,
-                         "bytes_per_pair": alg_bytes_step / max(cand, 1), "peak_source": peak_src},
+                         "bytes_per_pair": alg_bytes_step / max(cand, 1), "peak_source": peak_src,
+                         # what the kernel really issued: k-mers proven present by the exact member set skip their probes
+                         "issued_sectors_per_pair": {"bloom": stats.get("n_bf_loads", 0) / max(cand, 1),
+                                                     "member_set": stats.get("n_member_sectors", 0) / max(cand, 1),
+                                                     "reference_order_bloom": stats["n_bf_probes"] / max(cand, 1)}},
             "kernel_ms_per_step": {kk: vv / args.steps for kk, vv in tm_res.items() if kk.startswith("ms_")},
             "kernel_ms_per_step_e2e": {kk: vv / args.steps for kk, vv in tm_e2e.items() if kk.startswith("ms_")},
         }
@@ -421,6 +440,8 @@ def check_sharding(args, rank: int, world: int, local_rank: int):
     _m, bf_bytes, hash_num = bf_size(file_bytes, 0.001)
     lo, hi = reads.n * rank // world, reads.n * (rank + 1) // world
     with Links(LinksOptions(k=k, distances=d, step_sizes=t, device=local_rank)) as L:
+        p2p = world > 1 and os.environ.get("LINKS_EXCHANGE", "p2p") != "nccl"
+        keep_alive = multi.attach_exchange(L, dist, dev, inbox_bytes=max(64 << 20, int(reads.off[-1]) // 12 * 24 * 4)) if p2p else None
         if rank == 0:
             L.bf_alloc(bf_bytes, hash_num)
             L.push_contigs(contigs)
@@ -429,9 +450,13 @@ def check_sharding(args, rank: int, world: int, local_rank: int):
             if rank != 0:
                 L.push_contigs(contigs)
         L.push_reads(SeqSet(reads.seq, reads.off[lo:hi + 1], []), first_read_idx=lo)
-        ex = multi.exchange_pairs(L, dist, dev) if world > 1 else {}
+        if p2p:
+            L.exchange_finish()
+            ex = {"transport": "peer memory"}
+        else:
+            ex = multi.exchange_pairs(L, dist, dev) if world > 1 else {}
         rows, issues, stats = L.finalize()
-        if world > 1:
+        if world > 1 and not p2p:
             rows = multi.gather_rows(rows, dist, dev)
     tot = torch.tensor([stats["n_candidates"], stats["n_unique_pairs"], len(issues)], dtype=torch.int64, device=dev)
     if world > 1:

@@ -185,6 +185,21 @@ uint32_t links_pair_owner(uint64_t h_a, uint64_t h_b, uint32_t n_ranks);
 int links_bf_download_dev(links_ctx* ctx, void* dev_dst);
 int links_bf_load_dev(links_ctx* ctx, const void* dev_bits, uint64_t bytes, uint32_t hash_num);
 
+/* ---- multi-GPU over peer memory (NVLink P2P / NVSwitch): the exchange above without the stop in the middle.
+ * Every rank owns an INBOX, a device buffer of inbox_bytes that all ranks of the node can address (CUDA
+ * IPC, VMM export or torch symmetric memory -- the caller's business); inbox[r] is rank r's buffer as
+ * addressable from THIS process.  Once attached (before the first job, on every rank, followed by any
+ * barrier), links_reads_push routes the pairs each extract launch found new straight into their owners'
+ * inboxes and inserts what has arrived here while the next chunk is extracted; links_exchange_finish
+ * (after the last reads_push, on every rank, does not block the host) publishes "done", and
+ * links_finalize then waits for the other ranks, classifies the pairs this rank OWNS, sends its partial
+ * link rows to rank 0 and -- on rank 0 -- returns the summed table (other ranks return 0 rows).
+ * All ranks must run the same sequence of jobs (links_reset advances a shared epoch).  A region that is
+ * too small for a job fails that job with LINKS_E_LIMIT; size it for the distinct pairs of one rank
+ * (bench.py: 24 bytes x 2 x expected pairs). */
+int links_exchange_attach(links_ctx* ctx, uint32_t rank, uint32_t n_ranks, void* const* inbox, uint64_t inbox_bytes);
+int links_exchange_finish(links_ctx* ctx);
+
 /* ---- inspection utilities (used by the parity tests; thin wrappers over the same kernels) ---- */
 /* fwd/rev ntHash2 of every k-mer start of one sequence (btllib NtHash, nthash.hpp:1265-1338);
  * valid[i] = 1 iff the k-mer at i has only ACGTU/acgtu.  Arrays hold max(len-k+1,0) entries. */

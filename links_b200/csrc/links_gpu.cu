@@ -8,6 +8,7 @@
 //                  -> reduce-by-key -> D2H rows -> mirror expansion + final ordering on the host
 // There is no CPU implementation of any of these stages in this library.
 #include "../../include/links_gpu.h"
+#include "exchange.cuh"
 #include "extract.cuh"
 #include "kernels.cuh"
 
@@ -132,6 +133,17 @@ struct links_ctx {
   DevBuf f_final;
   DevBuf f_keys[2], f_vals[2], f_issues, f_tiglen, f_hist, f_scan_tmp, f_flags, f_total, f_okeys, f_olinks, f_ogaps, f_exch, f_il, f_ig;
   uint64_t issue_cap_hint = 1ull << 16;
+
+  // peer-memory exchange (exchange.cuh); attached once, survives links_reset
+  bool x_attached = false, x_finished = false, x_settled = false;
+  InboxLayout x_lay{};
+  uint64_t x_epoch = 0;
+  DevBuf d_xdev;                                  // ExchangeDev
+  DevBuf d_owned, d_owned_list, d_owned_okeys;    // the pairs this rank owns (imports land here)
+  uint64_t owned_cap = 0;
+  cudaStream_t s_import = nullptr;
+  cudaEvent_t ev_routed = nullptr, ev_imported = nullptr;
+  DevBuf f_rowcnt;
 
   // timing
   std::vector<TimedSpan> spans;
@@ -503,6 +515,187 @@ int ensure_member_capacity(links_ctx* c)
   return LINKS_OK;
 }
 
+// ---- peer-memory exchange (exchange.cuh)
+
+// how long a rank waits for its peers before it fails the job (LINKS_EXCHANGE_TIMEOUT_MS, default 60 s)
+unsigned long long exchange_timeout_ns()
+{
+  static const unsigned long long ns = []() {
+    const char* e = getenv("LINKS_EXCHANGE_TIMEOUT_MS");
+    const unsigned long long ms = e ? strtoull(e, nullptr, 10) : 60000ull;
+    return (ms ? ms : 1ull) * 1000000ull;
+  }();
+  return ns;
+}
+
+PairView owned_view(links_ctx* c)
+{
+  return pair_view(c->d_owned.as<PairSlot>(), c->owned_cap, c->d_owned_list.as<ulonglong2>(),
+                   c->prm.n_dist > 1 ? c->d_owned_okeys.as<unsigned long long>() : nullptr);
+}
+
+int ensure_owned(links_ctx* c, uint64_t min_cap)
+{
+  const uint64_t want = std::max<uint64_t>(std::max(min_cap, c->pair_cap), 1ull << 16);
+  if (c->owned_cap >= want || (c->owned_cap && !min_cap)) return LINKS_OK;  // a live table is only replaced on request
+  const uint64_t cap = 1ull << log2_ceil(want);
+  const bool multi_d = c->prm.n_dist > 1;
+  CU(c, cudaStreamSynchronize(c->s_import));
+  c->d_owned.release(); c->d_owned_list.release(); c->d_owned_okeys.release();
+  CU(c, c->d_owned.ensure(cap * sizeof(PairSlot)));
+  CU(c, c->d_owned_list.ensure(pair_list_capacity(cap) * sizeof(ulonglong2)));
+  if (multi_d) CU(c, c->d_owned_okeys.ensure(cap * 8));
+  c->owned_cap = cap;
+  Span sp(c, F_GROW, c->s_import);
+  CU(c, cudaMemsetAsync(c->d_owned.p, 0xFF, cap * sizeof(PairSlot), c->s_import));
+  if (multi_d) CU(c, cudaMemsetAsync(c->d_owned_okeys.p, 0xFF, cap * 8, c->s_import));
+  return LINKS_OK;
+}
+
+// s_compute: route the new part of the dense pair list + publish; s_import: insert what has arrived
+int exchange_route(links_ctx* c, bool finish)
+{
+  ExchangeDev* x = c->d_xdev.as<ExchangeDev>();
+  const unsigned long long* n_unique = &c->d_ctr.as<Counters>()->n_unique;
+  {
+    Span sp(c, F_EXCHANGE, c->s_compute);
+    if (c->pair_cap) {
+      route_kernel<<<c->sm_count * 2, kCtaThreads, 0, c->s_compute>>>(pair_view(c), n_unique, x, c->x_lay, c->x_epoch, finish ? 1 : 0);
+    } else {
+      commit_kernel<<<1, kMaxP2PRanks, 0, c->s_compute>>>(x, c->x_lay, c->x_epoch, finish ? 1 : 0);
+    }
+    c->launches++;
+  }
+  CU(c, cudaGetLastError());
+  CU(c, cudaEventRecord(c->ev_routed, c->s_compute));
+  CU(c, cudaStreamWaitEvent(c->s_import, c->ev_routed, 0));
+  CU(c, cudaStreamWaitEvent(c->s_import, c->ev_cleared, 0));
+  int rc = ensure_owned(c, 0);
+  if (rc) return rc;
+  {
+    Span sp(c, F_EXCHANGE, c->s_import);
+    if (finish) { inbox_wait_kernel<<<1, kMaxP2PRanks, 0, c->s_import>>>(x, c->x_lay, c->x_epoch, exchange_timeout_ns()); c->launches++; }
+    inbox_snapshot_kernel<<<1, kMaxP2PRanks, 0, c->s_import>>>(x, c->x_lay, c->x_epoch, c->owned_cap / 10 * 7);
+    inbox_import_kernel<<<c->sm_count * 2, kCtaThreads, 0, c->s_import>>>(x, c->x_lay, c->x_epoch, owned_view(c), c->prm.n_dist > 1 ? 1 : 0);
+    c->launches += 2;
+  }
+  CU(c, cudaGetLastError());
+  return LINKS_OK;
+}
+
+// Before stage 4: everything this rank owns is in the owned set (or re-import it into a larger one), then the
+// owned set takes the place of the local one so classify and the inspection calls see it.
+int exchange_settle(links_ctx* c)
+{
+  if (c->x_settled) return LINKS_OK;
+  if (!c->x_finished) return fail(c, LINKS_E_INVAL, "links_finalize: links_exchange_finish has not been called on this rank");
+  ExchangeDev* x = c->d_xdev.as<ExchangeDev>();
+  for (int attempt = 0;; ++attempt) {
+    CU(c, cudaStreamSynchronize(c->s_compute));
+    CU(c, cudaStreamSynchronize(c->s_import));
+    ExchangeDev h;
+    CU(c, cudaMemcpy(&h, x, sizeof h, cudaMemcpyDeviceToHost));
+    if (h.timed_out) return fail(c, LINKS_E_CUDA, "pair exchange: timed out waiting for the other ranks to finish routing (LINKS_EXCHANGE_TIMEOUT_MS)");
+    if (h.route_overflow)
+      return fail(c, LINKS_E_LIMIT, "pair exchange: a peer inbox region is full (%llu records per source rank); attach a larger inbox",
+                  (unsigned long long)c->x_lay.pair_cap);
+    if (!h.owned_overflow) {
+      CU(c, cudaMemcpyAsync(&c->d_ctr.as<Counters>()->n_unique, &x->n_owned, 8, cudaMemcpyDeviceToDevice, c->s_compute));
+      break;
+    }
+    if (attempt) return fail(c, LINKS_E_CUDA, "pair exchange: owned set overflow after re-import");
+    // the inbox still holds every record of this job: start over in a table sized for all of them
+    InboxHeader hdr;
+    CU(c, cudaMemcpy(&hdr, inbox_half(h.inbox[c->x_lay.rank], c->x_lay, c->x_epoch), sizeof hdr, cudaMemcpyDeviceToHost));
+    uint64_t total = 0;
+    for (uint32_t r = 0; r < c->x_lay.n_ranks; ++r) total += hdr.committed[r] & kCountMask;
+    int rc = ensure_owned(c, total / 7 * 10 + 1024);
+    if (rc) return rc;
+    CU(c, cudaMemsetAsync(reinterpret_cast<char*>(x) + offsetof(ExchangeDev, imported), 0,
+                          offsetof(ExchangeDev, routed) - offsetof(ExchangeDev, imported), c->s_import));
+    CU(c, cudaMemsetAsync(&x->n_owned, 0, 8, c->s_import));
+    CU(c, cudaMemsetAsync(&x->owned_overflow, 0, 8, c->s_import));
+    CU(c, cudaMemsetAsync(c->d_owned.p, 0xFF, c->owned_cap * sizeof(PairSlot), c->s_import));
+    if (c->prm.n_dist > 1) CU(c, cudaMemsetAsync(c->d_owned_okeys.p, 0xFF, c->owned_cap * 8, c->s_import));
+    Span sp(c, F_EXCHANGE, c->s_import);
+    inbox_snapshot_kernel<<<1, kMaxP2PRanks, 0, c->s_import>>>(x, c->x_lay, c->x_epoch, c->owned_cap / 10 * 7);
+    inbox_import_kernel<<<c->sm_count * 2, kCtaThreads, 0, c->s_import>>>(x, c->x_lay, c->x_epoch, owned_view(c), c->prm.n_dist > 1 ? 1 : 0);
+    c->launches += 2;
+    CU(c, cudaGetLastError());
+  }
+  std::swap(c->d_pairs, c->d_owned); std::swap(c->d_pair_list, c->d_owned_list); std::swap(c->d_pair_okeys, c->d_owned_okeys);
+  std::swap(c->pair_cap, c->owned_cap);
+  c->x_settled = true;
+  return LINKS_OK;
+}
+
+// Multi-GPU: every rank's reduce-by-key output {key, links, gaps}[n] goes to rank 0's inbox; rank 0 sums
+// rows with equal keys (sort + segmented sum) into f_okeys/f_olinks/f_ogaps.  *n_out: rows now in
+// those arrays on rank 0, 0 elsewhere (the job's rows are delivered on rank 0).
+int exchange_rows(links_ctx* c, cudaStream_t s, uint32_t n, int key_bits, uint32_t* n_out)
+{
+  ExchangeDev* x = c->d_xdev.as<ExchangeDev>();
+  const InboxLayout& L = c->x_lay;
+  if (n > L.row_cap) return fail(c, LINKS_E_LIMIT, "row exchange: %u rows, inbox has room for %llu per rank", n, (unsigned long long)L.row_cap);
+  {
+    Span sp(c, F_EXCHANGE, s);
+    rows_send_kernel<<<std::max(1u, std::min<unsigned>((n + 255) / 256, 1024u)), 256, 0, s>>>(
+      c->f_okeys.as<uint64_t>(), c->f_olinks.as<unsigned long long>(), c->f_ogaps.as<unsigned long long>(), n, x, L, c->x_epoch);
+    c->launches++;
+  }
+  CU(c, cudaGetLastError());
+  *n_out = 0;
+  if (L.rank != 0) return LINKS_OK;
+  CU(c, c->f_rowcnt.ensure(size_t(kMaxP2PRanks) * 2 * 8));
+  unsigned long long* d_cnt = c->f_rowcnt.as<unsigned long long>();
+  unsigned long long* d_start = d_cnt + kMaxP2PRanks;
+  rows_wait_kernel<<<1, kMaxP2PRanks, 0, s>>>(x, L, c->x_epoch, d_cnt, exchange_timeout_ns());
+  c->launches++;
+  unsigned long long hc[kMaxP2PRanks], hs[kMaxP2PRanks];
+  CU(c, cudaMemcpyAsync(hc, d_cnt, size_t(L.n_ranks) * 8, cudaMemcpyDeviceToHost, s));
+  CU(c, cudaStreamSynchronize(s));
+  {
+    unsigned long long timed_out = 0;
+    CU(c, cudaMemcpy(&timed_out, &x->timed_out, 8, cudaMemcpyDeviceToHost));
+    if (timed_out) return fail(c, LINKS_E_CUDA, "row exchange: timed out waiting for the other ranks' link rows (LINKS_EXCHANGE_TIMEOUT_MS)");
+  }
+  unsigned long long total = 0;
+  for (uint32_t r = 0; r < L.n_ranks; ++r) { hs[r] = total; total += hc[r]; }
+  if (!total) return LINKS_OK;
+  if (total >= (1ull << 31)) return fail(c, LINKS_E_LIMIT, "row exchange: more than 2^31 partial rows");
+  CU(c, cudaMemcpy(d_start, hs, size_t(L.n_ranks) * 8, cudaMemcpyHostToDevice));
+  DevBuf (&d_keys)[2] = c->f_keys; DevBuf (&d_vals)[2] = c->f_vals;
+  CU(c, d_keys[0].ensure(total * 8)); CU(c, d_vals[0].ensure(total * 4)); CU(c, c->f_il.ensure(total * 8)); CU(c, c->f_ig.ensure(total * 8));
+  CU(c, c->f_flags.ensure(total * 4)); CU(c, c->f_total.ensure(64));
+  uint32_t n_seg = 0;
+  {
+    Span sp(c, F_SORT, s);
+    rows_gather_kernel<<<unsigned((total + 255) / 256), 256, 0, s>>>(x, L, c->x_epoch, d_start, uint32_t(total), d_keys[0].as<uint64_t>(),
+                                                                    d_vals[0].as<int32_t>(), c->f_il.as<unsigned long long>(),
+                                                                    c->f_ig.as<unsigned long long>());
+    c->launches++;
+    int cur = 0;
+    int rc = radix_sort_pairs(c, s, d_keys, d_vals, total, key_bits, cur);
+    if (rc) return rc;
+    head_flags_kernel<<<unsigned((total + 255) / 256), 256, 0, s>>>(d_keys[cur].as<uint64_t>(), total, c->f_flags.as<uint32_t>());
+    c->launches++;
+    rc = device_scan(c, s, c->f_flags.as<uint32_t>(), total, c->f_flags.as<uint32_t>(), c->f_scan_tmp, c->f_total.as<uint32_t>());
+    if (rc) return rc;
+    CU(c, cudaMemcpyAsync(&n_seg, c->f_total.p, 4, cudaMemcpyDeviceToHost, s));
+    CU(c, cudaStreamSynchronize(s));
+    CU(c, c->f_okeys.ensure(uint64_t(n_seg) * 8)); CU(c, c->f_olinks.ensure(uint64_t(n_seg) * 8)); CU(c, c->f_ogaps.ensure(uint64_t(n_seg) * 8));
+    CU(c, cudaMemsetAsync(c->f_olinks.p, 0, uint64_t(n_seg) * 8, s));
+    CU(c, cudaMemsetAsync(c->f_ogaps.p, 0, uint64_t(n_seg) * 8, s));
+    rows_segment_sum_kernel<<<unsigned((total + 255) / 256), 256, 0, s>>>(
+      d_keys[cur].as<uint64_t>(), d_vals[cur].as<int32_t>(), total, c->f_flags.as<uint32_t>(), c->f_il.as<unsigned long long>(),
+      c->f_ig.as<unsigned long long>(), c->f_okeys.as<uint64_t>(), c->f_olinks.as<unsigned long long>(), c->f_ogaps.as<unsigned long long>());
+    c->launches++;
+    CU(c, cudaGetLastError());
+  }
+  *n_out = n_seg;
+  return LINKS_OK;
+}
+
 } // namespace
 
 // ====================================================================== C ABI
@@ -595,6 +788,9 @@ int links_create(links_ctx** out, const links_params* p)
   CUC(cudaStreamCreateWithFlags(&c->s_copy, cudaStreamNonBlocking));
   CUC(cudaStreamCreateWithFlags(&c->s_aux, cudaStreamNonBlocking));
   CUC(cudaStreamCreateWithFlags(&c->s_pack, cudaStreamNonBlocking));
+  CUC(cudaStreamCreateWithFlags(&c->s_import, cudaStreamNonBlocking));
+  CUC(cudaEventCreateWithFlags(&c->ev_routed, cudaEventDisableTiming));
+  CUC(cudaEventCreateWithFlags(&c->ev_imported, cudaEventDisableTiming));
   CUC(cudaEventCreateWithFlags(&c->ev_table, cudaEventDisableTiming));
   CUC(cudaEventCreateWithFlags(&c->ev_fork, cudaEventDisableTiming));
   CUC(cudaEventCreateWithFlags(&c->ev_contig, cudaEventDisableTiming));
@@ -628,6 +824,23 @@ int links_create(links_ctx** out, const links_params* p)
       CUC(cudaFuncSetAttribute(extract_fn_for(h), cudaFuncAttributeMaxDynamicSharedMemorySize, int(extract_smem_bytes(p->k))));
       CUC(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, extract_fn_for(h), kCtaThreads, extract_smem_bytes(p->k)));
       c->extract_ctas_per_sm = std::max(occ, 1);
+    }
+    {
+      // load every kernel now: with CUDA's lazy module loading a first launch may have to wait for the
+      // device to go idle, which must not happen while a peer-wait kernel (exchange.cuh) is resident
+      cudaFuncAttributes fa;
+      const void* fns[] = {(const void*)pack_kernel, (const void*)rank_build_kernel, (const void*)table_init_kernel,
+                           (const void*)contig_kernel<0>, (const void*)contig_kernel<1>, (const void*)contig_kernel<2>,
+                           (const void*)pair_rehash_kernel, (const void*)classify_kernel, (const void*)mirror_expand_kernel,
+                           (const void*)gather_rows_kernel, (const void*)pair_bucket_count_kernel, (const void*)pair_bucket_scatter_kernel,
+                           (const void*)pair_import_kernel, (const void*)pair_export_kernel, (const void*)route_kernel,
+                           (const void*)commit_kernel, (const void*)inbox_wait_kernel, (const void*)inbox_snapshot_kernel,
+                           (const void*)inbox_import_kernel, (const void*)rows_send_kernel,
+                           (const void*)rows_wait_kernel, (const void*)rows_gather_kernel, (const void*)scan_sums_kernel,
+                           (const void*)scan_apply_kernel, (const void*)scan_small_kernel, (const void*)radix_hist_kernel,
+                           (const void*)radix_scatter_kernel, (const void*)head_flags_kernel, (const void*)reduce_by_key_kernel,
+                           (const void*)rows_segment_sum_kernel};
+      for (const void* f : fns) CUC(cudaFuncGetAttributes(&fa, f));
     }
     CUC(cudaHostAlloc(reinterpret_cast<void**>(&c->h_snap), sizeof(Counters) * links_ctx::kSnaps, cudaHostAllocDefault));
     for (int i = 0; i < links_ctx::kSnaps; ++i) CUC(cudaEventCreateWithFlags(&c->ev_snap[i], cudaEventDisableTiming));
@@ -666,6 +879,11 @@ void links_destroy(links_ctx* c)
   if (c->s_copy) cudaStreamDestroy(c->s_copy);
   if (c->s_aux) cudaStreamDestroy(c->s_aux);
   if (c->s_pack) cudaStreamDestroy(c->s_pack);
+  if (c->s_import) cudaStreamDestroy(c->s_import);
+  if (c->ev_routed) cudaEventDestroy(c->ev_routed);
+  if (c->ev_imported) cudaEventDestroy(c->ev_imported);
+  c->d_xdev.release(); c->d_owned.release(); c->d_owned_list.release(); c->d_owned_okeys.release(); c->f_rowcnt.release();
+  c->d_members.release();
   if (c->ev_table) cudaEventDestroy(c->ev_table);
   if (c->ev_fork) cudaEventDestroy(c->ev_fork);
   cudaGetLastError();
@@ -679,6 +897,7 @@ int links_sync(links_ctx* c)
   CU(c, cudaStreamSynchronize(c->s_copy));
   CU(c, cudaStreamSynchronize(c->s_aux));
   CU(c, cudaStreamSynchronize(c->s_compute));
+  CU(c, cudaStreamSynchronize(c->s_import));
   return LINKS_OK;
 }
 
@@ -838,6 +1057,10 @@ static int push_read_chunk(links_ctx* c, const char* seq, const uint8_t* dev_seq
     }
     rc = enqueue_snapshot(c);
     if (rc) return rc;
+    if (c->x_attached) {
+      rc = exchange_route(c, false);  // this launch's new pairs travel to their owners while the next chunk is extracted
+      if (rc) return rc;
+    }
   }
   CU(c, cudaEventRecord(c->ev_done[si], c->s_compute));
   c->slot_used[si] = true;
@@ -944,6 +1167,7 @@ int links_reset(links_ctx* c)
   CU(c, cudaStreamSynchronize(c->s_copy));
   CU(c, cudaStreamSynchronize(c->s_aux));
   CU(c, cudaStreamSynchronize(c->s_compute));
+  CU(c, cudaStreamSynchronize(c->s_import));
   c->table_started = false; c->table_batches_built = 0;
   poll_snapshots(c);
   for (auto* b : c->contig_batches) c->contig_pool.push_back(b);
@@ -957,11 +1181,26 @@ int links_reset(links_ctx* c)
   for (int i = 0; i < links_ctx::kSlots; ++i) c->slot_used[i] = false;
   c->next_slot = 0;  // same chunk -> slot assignment every job: slot buffers stop growing after the first one
   CU(c, cudaMemsetAsync(c->d_ctr.p, 0, sizeof(Counters), c->s_compute));
+  if (c->x_attached && c->x_settled) {  // the previous job swapped the owned set in: undo, so each buffer keeps its role (and size)
+    std::swap(c->d_pairs, c->d_owned); std::swap(c->d_pair_list, c->d_owned_list); std::swap(c->d_pair_okeys, c->d_owned_okeys);
+    std::swap(c->pair_cap, c->owned_cap);
+  }
   if (c->pair_cap) {
     // off the compute stream: the Bloom build and the first copies do not have to wait for it
     Span sp(c, F_GROW, c->s_aux);
     CU(c, cudaMemsetAsync(c->d_pairs.p, 0xFF, c->pair_cap * sizeof(PairSlot), c->s_aux));
     if (c->prm.n_dist > 1) CU(c, cudaMemsetAsync(c->d_pair_okeys.p, 0xFF, c->pair_cap * 8, c->s_aux));
+  }
+  if (c->x_attached) {
+    c->x_epoch++;
+    c->x_finished = false; c->x_settled = false;
+    CU(c, cudaMemsetAsync(reinterpret_cast<char*>(c->d_xdev.p) + offsetof(ExchangeDev, cursor), 0,
+                          sizeof(ExchangeDev) - offsetof(ExchangeDev, cursor), c->s_compute));
+    if (c->owned_cap) {
+      Span sp(c, F_GROW, c->s_aux);
+      CU(c, cudaMemsetAsync(c->d_owned.p, 0xFF, c->owned_cap * sizeof(PairSlot), c->s_aux));
+      if (c->prm.n_dist > 1) CU(c, cudaMemsetAsync(c->d_owned_okeys.p, 0xFF, c->owned_cap * 8, c->s_aux));
+    }
   }
   CU(c, cudaEventRecord(c->ev_cleared, c->s_aux));
   c->contig_pack_pending = false;
@@ -976,6 +1215,7 @@ int links_get_timing(links_ctx* c, links_timing* t, int reset)
   CU(c, cudaStreamSynchronize(c->s_copy));
   CU(c, cudaStreamSynchronize(c->s_aux));
   CU(c, cudaStreamSynchronize(c->s_compute));
+  CU(c, cudaStreamSynchronize(c->s_import));
   resolve_spans(c);
   t->ms_h2d = c->fam_ms[F_H2D]; t->ms_pack = c->fam_ms[F_PACK]; t->ms_bf_build = c->fam_ms[F_BF];
   t->ms_table_build = c->fam_ms[F_TABLE]; t->ms_extract = c->fam_ms[F_EXTRACT]; t->ms_classify = c->fam_ms[F_CLASSIFY];
@@ -1046,6 +1286,10 @@ int links_finalize(links_ctx* c, links_row** rows_out, uint64_t* n_rows_out, lin
     rc = build_table(c, s);
     if (rc) return rc;
   }
+  if (c->x_attached) {  // multi-GPU: stage 4 runs over the pairs this rank OWNS
+    rc = exchange_settle(c);
+    if (rc) return rc;
+  }
   // unique pair count sizes the row buffers
   CU(c, cudaStreamSynchronize(s));
   Counters h;
@@ -1112,6 +1356,14 @@ int links_finalize(links_ctx* c, links_row** rows_out, uint64_t* n_rows_out, lin
                                                                    d_flags.as<uint32_t>(), d_okeys.as<uint64_t>(),
                                                                    d_olinks.as<unsigned long long>(), d_ogaps.as<unsigned long long>());
     c->launches++;
+  }
+  if (c->x_attached && c->x_lay.n_ranks > 1) {  // partial link tables of all ranks are summed on rank 0, on the device
+    rc = exchange_rows(c, s, n_seg, key_bits, &n_seg);
+    if (rc) return rc;
+  }
+  if (n_seg) {
+    Span sp(c, F_SORT, s);
+    int cur = 0;
     // every canonical row stands for two tsv rows (add_to_pair_map, reference :717-761): expand, sort, gather
     n_out32 = n_seg * 2;
     CU(c, d_keys[0].ensure(uint64_t(n_out32) * 8)); CU(c, d_vals[0].ensure(uint64_t(n_out32) * 4));
@@ -1265,9 +1517,8 @@ int links_pairs_download(links_ctx* c, uint64_t* h_a, uint64_t* h_b, uint32_t* d
   if (!h_a || !h_b || !d_idx) return LINKS_OK;
   if (cap < h.n_unique) return fail(c, LINKS_E_INVAL, "links_pairs_download: cap %llu < %llu", (unsigned long long)cap, (unsigned long long)h.n_unique);
   if (!h.n_unique) return LINKS_OK;
-  DevBuf d_out;
-  struct Cleanup { DevBuf& a; ~Cleanup() { a.release(); } } cl{d_out};
-  CU(c, d_out.ensure(h.n_unique * 24));
+  DevBuf& d_out = c->f_exch;  // scratch kept by the context (no cudaFree, which would wait for every kernel on the device)
+  CU(c, d_out.ensure(std::max<uint64_t>(h.n_unique * 24, size_t(kMaxRanks) * 2 * 8)));
   pair_export_kernel<<<grid_for(c, h.n_unique, 256, 8), 256, 0, c->s_compute>>>(
     pair_view(c), h.n_unique, d_out.as<uint64_t>());
   c->launches++;
@@ -1446,6 +1697,57 @@ int links_pairs_import(links_ctx* c, const void* dev_records, uint64_t n_records
   Counters h;
   CU(c, cudaMemcpy(&h, c->d_ctr.p, sizeof h, cudaMemcpyDeviceToHost));
   c->known_unique = h.n_unique; c->known_cand = c->cand_total;
+  return LINKS_OK;
+}
+
+int links_exchange_attach(links_ctx* c, uint32_t rank, uint32_t n_ranks, void* const* inbox, uint64_t inbox_bytes)
+{
+  if (!c || !inbox) return LINKS_E_INVAL;
+  if (n_ranks == 0 || n_ranks > uint32_t(kMaxP2PRanks) || rank >= n_ranks)
+    return fail(c, LINKS_E_LIMIT, "links_exchange_attach: rank %u of %u (at most %d ranks)", rank, n_ranks, kMaxP2PRanks);
+  if (c->x_attached) return fail(c, LINKS_E_INVAL, "links_exchange_attach: already attached");
+  if (!c->contig_batches.empty() || c->cand_total) return fail(c, LINKS_E_INVAL, "links_exchange_attach: attach before the first job");
+  for (uint32_t r = 0; r < n_ranks; ++r)
+    if (!inbox[r] || (reinterpret_cast<uintptr_t>(inbox[r]) & 255)) return fail(c, LINKS_E_INVAL, "links_exchange_attach: inbox[%u] is null or not 256-byte aligned", r);
+  CU(c, cudaSetDevice(c->device));
+  InboxLayout L{};
+  L.n_ranks = n_ranks; L.rank = rank;
+  L.rec_words = c->prm.n_dist > 1 ? 3 : 2;
+  L.half_bytes = (inbox_bytes / 2) & ~uint64_t(4095);
+  L.pair_off = (sizeof(InboxHeader) + 4095) & ~uint64_t(4095);
+  if (L.half_bytes <= L.pair_off + (1ull << 16)) return fail(c, LINKS_E_INVAL, "links_exchange_attach: inbox of %llu bytes is too small", (unsigned long long)inbox_bytes);
+  const uint64_t body = L.half_bytes - L.pair_off;
+  const uint64_t row_bytes = (body / 16) & ~uint64_t(255);  // 1/16 of a half for the partial link rows
+  L.row_cap = row_bytes / n_ranks / sizeof(RowRec);
+  L.pair_cap = ((body - row_bytes) / n_ranks / (L.rec_words * 8)) & ~uint64_t(15);
+  L.row_off = L.pair_off + uint64_t(n_ranks) * L.pair_cap * L.rec_words * 8;
+  L.row_off = (L.row_off + 255) & ~uint64_t(255);
+  if (!L.pair_cap || !L.row_cap) return fail(c, LINKS_E_INVAL, "links_exchange_attach: inbox too small for %u ranks", n_ranks);
+  CU(c, c->d_xdev.ensure(sizeof(ExchangeDev)));
+  ExchangeDev h;
+  memset(&h, 0, sizeof h);
+  for (uint32_t r = 0; r < n_ranks; ++r) h.inbox[r] = static_cast<char*>(inbox[r]);
+  CU(c, cudaMemcpy(c->d_xdev.p, &h, sizeof h, cudaMemcpyHostToDevice));
+  // my own headers start at zero; peers only write them after the caller's barrier that follows the attach
+  CU(c, cudaMemset(inbox[rank], 0, sizeof(InboxHeader)));
+  CU(c, cudaMemset(static_cast<char*>(inbox[rank]) + L.half_bytes, 0, sizeof(InboxHeader)));
+  CU(c, cudaDeviceSynchronize());
+  c->x_lay = L;
+  c->x_epoch = 1;
+  c->x_attached = true; c->x_finished = false; c->x_settled = false;
+  return LINKS_OK;
+}
+
+int links_exchange_finish(links_ctx* c)
+{
+  if (!c) return LINKS_E_INVAL;
+  if (!c->x_attached) return fail(c, LINKS_E_INVAL, "links_exchange_finish: no inbox attached");
+  if (c->x_finished) return LINKS_OK;
+  CU(c, cudaSetDevice(c->device));
+  CU(c, cudaStreamWaitEvent(c->s_compute, c->ev_cleared, 0));
+  int rc = exchange_route(c, true);
+  if (rc) return rc;
+  c->x_finished = true;
   return LINKS_OK;
 }
 

@@ -86,8 +86,31 @@ def replicate_bloom(L, nbytes: int, hash_num: int, dist, device, src: int = 0, g
         L.bf_download_dev(buf.data_ptr())
     dist.broadcast(buf, src=src, group=group)
     if dist.get_rank(group) != src:
+        # the context may run on its own stream (no links_set_stream): the copy below must not overtake the broadcast
+        torch.cuda.current_stream().synchronize()
         L.bf_load_dev(buf.data_ptr(), nbytes, hash_num)
         L.bf_covers_contigs(True)  # rank `src` built these bits from the same contigs every rank pushes next
+
+
+def attach_exchange(L, dist, device, inbox_bytes: int, group=None):
+    """Peer-memory exchange (include/links_gpu.h, links_exchange_attach): allocate this rank's inbox in
+    symmetric memory, exchange the peer pointers, hand them to the context.  Returns the objects that
+    must stay alive as long as the context.  After this, a job is
+        reset -> Bloom filter -> contigs -> reads -> L.exchange_finish() -> L.finalize()
+    and rank 0's finalize returns the summed link table; there is no all-to-all and no row gather."""
+    import torch
+    import torch.distributed._symmetric_memory as symm
+    g = group if group is not None else dist.group.WORLD
+    size = torch.tensor([int(inbox_bytes)], dtype=torch.int64, device=device)
+    dist.all_reduce(size, op=dist.ReduceOp.MAX, group=g)  # one size for all ranks (the layout is shared)
+    inbox_bytes = (int(size.item()) + 4095) // 4096 * 4096
+    buf = symm.empty(int(inbox_bytes), dtype=torch.uint8, device=device)
+    hdl = symm.rendezvous(buf, g)
+    ptrs = [int(p) for p in hdl.buffer_ptrs]
+    L.exchange_attach(dist.get_rank(g), dist.get_world_size(g), ptrs, int(inbox_bytes))
+    torch.cuda.synchronize()
+    dist.barrier(group=g)  # every header is zeroed before anyone writes to a peer
+    return buf, hdl
 
 
 _BIN_CODE = {-1: 0, 10: 1, 500: 2, 5000: 3, 10000: 4}  # get_distance_bin's range (src/LINKS.hpp:764-770)

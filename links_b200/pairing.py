@@ -227,6 +227,14 @@ class Links:
             self._lib.links_free_result(out_p, None)
         return out
 
+    def exchange_attach(self, rank: int, n_ranks: int, inbox_ptrs: list[int], inbox_bytes: int) -> None:
+        """Peer-memory pair exchange (links_gpu.h): inbox_ptrs[r] = rank r's inbox as addressable here."""
+        arr = (C.c_void_p * n_ranks)(*inbox_ptrs)
+        self._check(self._lib.links_exchange_attach(self._h, rank, n_ranks, arr, inbox_bytes))
+
+    def exchange_finish(self) -> None:
+        self._check(self._lib.links_exchange_finish(self._h))
+
     def bf_download_dev(self, dev_dst: int) -> None:
         self._check(self._lib.links_bf_download_dev(self._h, dev_dst))
 

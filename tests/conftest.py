@@ -5,6 +5,12 @@ import gzip
 import hashlib
 import json
 import os
+
+# peer waits of the multi-GPU exchange give up quickly in tests: a logic error becomes a failure, not a hung GPU
+os.environ.setdefault("LINKS_EXCHANGE_TIMEOUT_MS", "8000")
+# several contexts share this process in the multi-rank emulation: give every stream its own hardware queue, so a
+# kernel that waits for a peer never sits in front of that peer's kernels (must be set before CUDA initialises)
+os.environ.setdefault("CUDA_DEVICE_MAX_CONNECTIONS", "32")
 import sys
 
 import numpy as np

@@ -148,6 +148,50 @@ def test_bf_load_path_equals_build_path(gpu_lib, oracle):
         assert sort_lines(L.format_rows(rows)) == c.expected_tsv()
 
 
+@pytest.mark.parametrize("name", ["adv_offset_k20", "adv_tandem", "c1"])
+def test_member_set_modes_agree(gpu_lib, oracle, name):
+    """The exact member set beside the filter (links_bf_covers_contigs, kernels.cuh MemberView) is a
+    shortcut, not a semantic: built with the filter (bf_alloc), built alone under a loaded filter the
+    caller vouches for, absent under a plain loaded filter, and regrown across many small contig
+    pushes -- same rows, same survivors, same reference-order probe count; only the issued loads differ."""
+    from links_b200.seqio import SeqSet
+    c = GoldenCase(name)
+    contigs, reads = c.contigs(), c.reads()
+    _m, nbytes, h = oracle.bf_size(c.meta["contigs_file_bytes"], c.opts["p"])
+    bits = oracle.bf_build(contigs.seq, contigs.off, nbytes, h, c.opts["k"])
+
+    def run(mode):
+        with _links(k=c.opts["k"], d=c.opts["d"], t=c.steps(), o=c.opts["o"], e=c.opts["e"]) as L:
+            if mode in ("build", "build_batches"):
+                L.bf_alloc(nbytes, h)
+            else:
+                L.bf_load(bits, h)
+                if mode == "load_vouched":
+                    L.bf_covers_contigs(True)
+            if mode == "build_batches":  # one contig per push: the set is re-sized and re-filled on the way
+                for i in range(contigs.n):
+                    L.push_contigs(SeqSet(contigs.seq, contigs.off[i:i + 2], []), first_tig_id=i + 1)
+            else:
+                L.push_contigs(contigs)
+            L.push_reads(reads)
+            got_bits = L.bf_bits()
+            rows, issues, stats = L.finalize()
+            return L.format_rows(rows), L.format_issues(issues), stats, got_bits
+
+    out = {m: run(m) for m in ("build", "load_plain", "load_vouched", "build_batches")}
+    for m, (tsv, iss, stats, got_bits) in out.items():
+        assert sort_lines(tsv) == c.expected_tsv(), m
+        assert sort_issue_records(iss) == c.expected_issues(), m
+        assert np.array_equal(got_bits, bits), m
+        for key in ("n_candidates", "n_survivors", "n_unique_pairs", "n_bf_probes"):
+            assert stats[key] == out["build"][2][key], (m, key)
+    assert out["load_plain"][2]["n_member_sectors"] == 0
+    assert out["load_plain"][2]["n_bf_loads"] >= out["load_plain"][2]["n_bf_probes"]
+    for m in ("build", "load_vouched", "build_batches"):
+        assert out[m][2]["n_member_sectors"] > 0, m
+        assert out[m][2]["n_bf_loads"] < out["load_plain"][2]["n_bf_loads"], m
+
+
 def test_stage_api_writes_reference_files(gpu_lib, tmp_path):
     """The four stage methods of the reference's class LINKS, file in -> file out."""
     from links_b200 import Links, LinksOptions
@@ -295,6 +339,61 @@ def test_pair_exchange_between_contexts_equals_single_context(gpu_lib, name, n_r
     finally:
         for L in ctxs:
             L.close()
+
+
+@pytest.mark.timeout(280)
+@pytest.mark.parametrize("name,n_ranks,inbox_mb", [("adv_tandem", 2, 64), ("adv_offset_k20", 3, 64), ("c1", 2, 512)])
+def test_peer_memory_exchange_equals_single_context(gpu_lib, name, n_ranks, inbox_mb):
+    """links_exchange_attach/finish as deployed: one PROCESS per rank (tests/_exchange_worker.py), here all
+    on GPU 0, inboxes shared through CUDA IPC like peer memory on an NVLink box.  Reads are sharded;
+    routing, import, the wait for the other ranks and the row merge on rank 0 all run inside the
+    library.  Two jobs back to back cover the epoch/half switch.  Rank 0's rows == the reference golden;
+    the owned pair sets partition the single-context pair set (same winning distance index)."""
+    import queue
+
+    import torch.multiprocessing as mp
+
+    from tests._exchange_worker import rank_main
+    c = GoldenCase(name)
+    _tsv1, _iss1, stats1, (pa1, pb1, pd1) = _run_gpu(c)
+    single = set(zip(pa1.tolist(), pb1.tolist(), pd1.tolist()))
+    ctx = mp.get_context("spawn")
+    queues = [ctx.Queue() for _ in range(n_ranks)]
+    results = ctx.Queue()
+    barrier = ctx.Barrier(n_ranks)
+    n_jobs = 2
+    procs = [ctx.Process(target=rank_main, args=(r, n_ranks, name, inbox_mb << 20, queues, results, barrier, n_jobs), daemon=True)
+             for r in range(n_ranks)]
+    for p in procs:
+        p.start()
+    out: dict = {}
+    try:
+        for _ in range(n_ranks):
+            r, status, payload = results.get(timeout=200)
+            assert status == "ok", f"rank {r}: {payload}"
+            out[r] = payload
+    except queue.Empty:
+        pytest.fail(f"ranks {sorted(set(range(n_ranks)) - set(out))} did not report (deadlock?)")
+    finally:
+        for p in procs:
+            p.join(timeout=20)
+        for p in procs:
+            if p.is_alive():
+                p.kill()
+    for job in range(n_jobs):
+        assert sort_lines(out[0][job]["tsv"]) == c.expected_tsv(), f"job {job}"
+        owned = []
+        for r in range(n_ranks):
+            o = out[r][job]
+            if r:
+                assert o["stats"]["n_rows"] == 0
+            owned.append(set(zip(np.frombuffer(o["pa"], np.uint64).tolist(), np.frombuffer(o["pb"], np.uint64).tolist(),
+                                 np.frombuffer(o["pd"], np.uint32).tolist())))
+        assert sum(len(o) for o in owned) == len(single)
+        assert set().union(*owned) == single
+        iss = b"".join(out[r][job]["issues"] for r in range(n_ranks))
+        assert sort_issue_records(iss) == c.expected_issues()
+        assert sum(out[r][job]["stats"]["n_candidates"] for r in range(n_ranks)) == stats1["n_candidates"]
 
 
 @pytest.mark.parametrize("name", ["c1", "adv_offset_k20", "adv_ns_lower"])
