@@ -244,6 +244,7 @@ def main_ours(args, rank: int, world: int, local_rank: int):
     # N > 1: pairs travel to their owner ranks through NVLink peer memory while the reads are still being
     # extracted (links_exchange_attach); LINKS_EXCHANGE=nccl selects the stop-and-exchange all-to-all instead
     p2p = world > 1 and os.environ.get("LINKS_EXCHANGE", "p2p") != "nccl"
+    bloom_bcast = os.environ.get("LINKS_BLOOM", "local") == "broadcast"
     keep_alive = None
     if p2p:
         est_pairs = int(reads.off[-1]) // 12  # ~0.06 distinct pairs per read base on this workload, x1.4
@@ -283,24 +284,25 @@ def main_ours(args, rank: int, world: int, local_rank: int):
     def _step(resident: bool):
         L.reset()
         mark("reset")
-        if world > 1 and rank != 0:
-            pass  # the filter arrives by broadcast below
-        else:
-            L.bf_alloc(bf_bytes, hash_num)
-        if world > 1:
-            # rank 0 builds the Bloom filter from the contigs; NCCL broadcast replicates it (north_star);
-            # the contig k-mer table is rebuilt per rank from the replicated contigs (cheaper than moving it)
+        if world > 1 and bloom_bcast:
+            # north_star's variant: rank 0 builds the Bloom filter, NCCL broadcast replicates it, the others adopt it.
+            # It serialises the ranks (everyone waits for rank 0's build) -- measured 1.7 ms of a 10 ms step at N=2.
             if rank == 0:
+                L.bf_alloc(bf_bytes, hash_num)
                 (L.push_contigs_dev(d_contigs.data_ptr(), contigs.off, 1) if resident
                  else L.push_contigs_raw(pc_seq, pc_off, contigs.n, 1))
             multi.replicate_bloom(L, bf_bytes, hash_num, dist, dev)
             if rank != 0:
                 (L.push_contigs_dev(d_contigs.data_ptr(), contigs.off, 1) if resident
                  else L.push_contigs_raw(pc_seq, pc_off, contigs.n, 1))
-        elif resident:
-            L.push_contigs_dev(d_contigs.data_ptr(), contigs.off, 1)
         else:
-            L.push_contigs_raw(pc_seq, pc_off, contigs.n, 1)
+            # default (SURVEY 8e's alternative): the contigs are replicated anyway, so every rank builds the same
+            # filter itself (0.3 ms, deterministic, bit-identical) and nobody waits
+            L.bf_alloc(bf_bytes, hash_num)
+            if resident:
+                L.push_contigs_dev(d_contigs.data_ptr(), contigs.off, 1)
+            else:
+                L.push_contigs_raw(pc_seq, pc_off, contigs.n, 1)
         mark("bloom+contigs")
         if resident:
             L.push_reads_dev(d_reads.data_ptr(), reads.off, first_read)
@@ -385,7 +387,8 @@ def main_ours(args, rank: int, world: int, local_rank: int):
                        "candidate_pairs_per_gpu": cand, "survivors": stats["n_survivors"], "unique_pairs": stats["n_unique_pairs"],
                        "bf_probes": stats["n_bf_probes"], "rows": n_rows, "rows_digest": digest_res,
                        "l2": "inputs (250 MB reads, GB-scale pair set and contig table) exceed the 126 MB L2; no flush",
-                       "sharding": ("reads by rank (each rank its own 50x read set), Bloom filter NCCL-broadcast from rank 0, contigs replicated, "
+                       "sharding": ("reads by rank (each rank its own 50x read set), contigs replicated, Bloom filter "
+                                    + ("NCCL-broadcast from rank 0, " if bloom_bcast else "built by every rank from the replicated contigs (LINKS_BLOOM=broadcast: NCCL broadcast from rank 0), ")
                                     + ("distinct pairs routed to their owner rank (hash of (h_a,h_b)) through NVLink peer memory by a kernel after "
                                        "every extract launch and imported there while extraction continues, partial link rows summed on rank 0 on the device"
                                        if p2p else "distinct pairs routed by one NCCL all-to-all keyed on hash(h_a,h_b), rows summed on rank 0")) if world > 1 else "single GPU",

@@ -62,6 +62,7 @@ struct ExchangeDev {
   unsigned long long imported[kMaxP2PRanks];    // records of src already inserted into the owned set
   unsigned long long snap[kMaxP2PRanks];        // upper bound of the import in flight
   unsigned long long routed;                    // prefix of the dense unique-pair list already routed
+  unsigned long long route_hi;                  // list length when the last extract launch ended (copied in stream order)
   unsigned long long n_owned;                   // distinct pairs in the owned set
   unsigned long long route_overflow, owned_overflow;
   unsigned int blocks_done, row_blocks_done;    // last-block-publishes counters of route_kernel / rows_send_kernel
@@ -117,12 +118,13 @@ __device__ __forceinline__ void publish_counts(ExchangeDev* x, const InboxLayout
   }
 }
 
-// pairs [x->routed, *n_unique) of the dense list -> their owners' inboxes.  Slots are handed out by
+// pairs [x->routed, x->route_hi) of the dense list -> their owners' inboxes.  Slots are handed out by
 // this rank's own cursors (only this rank writes its regions), one atomic per (warp, owner).
-__global__ void __launch_bounds__(kCtaThreads) route_kernel(PairView pv, const unsigned long long* __restrict__ n_unique,
-                                                            ExchangeDev* __restrict__ x, InboxLayout L, uint64_t epoch, int finish)
+// Runs on its own stream beside the NEXT extract launch, which keeps appending to the list: the range ends
+// at route_hi, the length recorded when the previous launch ended, not at the live counter.
+__global__ void __launch_bounds__(kCtaThreads) route_kernel(PairView pv, ExchangeDev* __restrict__ x, InboxLayout L, uint64_t epoch, int finish)
 {
-  const unsigned long long lo = x->routed, hi = *n_unique;
+  const unsigned long long lo = x->routed, hi = x->route_hi;
   const int lane = threadIdx.x & 31;
   const uint64_t stride = uint64_t(gridDim.x) * blockDim.x;
   const uint64_t n = hi - lo;

@@ -19,6 +19,7 @@
 // after the table load and no lane idles except in the <= 5 drain rounds per tile.  Within a
 // stage all probes of a k-mer are issued together (independent loads in flight).
 #pragma once
+#include "exchange.cuh"
 #include "kernels.cuh"
 
 namespace links {
@@ -65,10 +66,15 @@ __device__ __forceinline__ uint32_t warp_push_slot(bool pass, uint32_t n, uint32
 }
 
 // H = Bloom hash count known at compile time (0: runtime bf.hash_num)
-template <int H>
+// ROUTED (multi-GPU, exchange.cuh): S5 does not insert into a local pair set; it writes the surviving pair as a
+// record straight into its OWNER rank's inbox over NVLink peer memory (one cursor atomic per warp and owner), and
+// the kernel's last block publishes the new record counts after system-scope fences.  The transfer is part of
+// the extraction, tile by tile; the owner de-duplicates while this rank keeps extracting.
+template <int H, bool ROUTED>
 __global__ void __launch_bounds__(kCtaThreads, LINKS_EXTRACT_MIN_CTAS) extract_kernel(ReadBatch rb, DistParams dp, int k, uint64_t kseed,
                                                                  const ulonglong2* __restrict__ g_tab2, BloomView bf,
-                                                                 MemberView mv, PairView pv, Counters* __restrict__ ctr)
+                                                                 MemberView mv, PairView pv, Counters* __restrict__ ctr,
+                                                                 ExchangeDev* __restrict__ x, InboxLayout L, uint64_t epoch)
 {
   extern __shared__ ulonglong2 s_dyn[];
   const int n_tab = ((k + 1) >> 1) * 16;
@@ -225,7 +231,7 @@ __global__ void __launch_bounds__(kCtaThreads, LINKS_EXTRACT_MIN_CTAS) extract_k
         const uint32_t take = n4 < 32u ? n4 : 32u;
         n4 -= take;
         bool fresh = false;
-        uint64_t h_a = 0, h_b = 0;
+        uint64_t h_a = 0, h_b = 0, okey_r = 0;
         if (uint32_t(lane) < take) {
           const uint32_t q = Q.q4_i[n4 + lane];
           const uint64_t fb = Q.q4_f[n4 + lane], rbv = Q.q4_r[n4 + lane];
@@ -233,13 +239,34 @@ __global__ void __launch_bounds__(kCtaThreads, LINKS_EXTRACT_MIN_CTAS) extract_k
           uint64_t fa, ra;
           hash_kmer2(rb.packed, pos_a(n), k, s_tab, fa, ra);
           if (fa < rbv) { h_a = rbv; h_b = ra; } else { h_a = fa; h_b = fb; }
-          fresh = pair_insert(pv, h_a, h_b, make_okey(rb.first_read_idx + r, di, n), multi_d);
+          if (!ROUTED) fresh = pair_insert(pv, h_a, h_b, make_okey(rb.first_read_idx + r, di, n), multi_d);
+          else okey_r = make_okey(rb.first_read_idx + r, di, n);
         }
         if (lane == 0) n_surv += take;
         __syncwarp();
-        uint32_t slot;
-        n5 = warp_push_slot(fresh, n5, slot);
-        if (fresh) { Q.q5_a[slot] = h_a; Q.q5_b[slot] = h_b; }
+        if (ROUTED) {
+          const bool live = uint32_t(lane) < take;
+          const uint32_t dst = live ? dest_rank(h_a, h_b, L.n_ranks) : 0xFFFFFFFFu;
+          const uint32_t peers = __match_any_sync(0xffffffffu, dst);
+          const int leader = __ffs(peers) - 1;
+          unsigned long long base = 0;
+          if (live && lane == leader) base = atomicAdd(&x->cursor[dst], (unsigned long long)__popc(peers));
+          base = __shfl_sync(0xffffffffu, base, leader);
+          if (live) {
+            const unsigned long long slot = base + __popc(peers & ((1u << lane) - 1u));
+            if (slot < L.pair_cap) {
+              uint64_t* rec = inbox_pair_region(x->inbox[dst], L, epoch, L.rank) + slot * L.rec_words;
+              if (L.rec_words == 2) *reinterpret_cast<ulonglong2*>(rec) = make_ulonglong2(h_a, h_b);
+              else { rec[0] = h_a; rec[1] = h_b; rec[2] = okey_r; }
+            } else {
+              x->route_overflow = 1;
+            }
+          }
+        } else {
+          uint32_t slot;
+          n5 = warp_push_slot(fresh, n5, slot);
+          if (fresh) { Q.q5_a[slot] = h_a; Q.q5_b[slot] = h_b; }
+        }
       } else {  // ---- append fresh pairs to the dense unique-pair list: one global atomic per 32 pairs
         const uint32_t take = n5 < 32u ? n5 : 32u;
         n5 -= take;
@@ -262,6 +289,9 @@ __global__ void __launch_bounds__(kCtaThreads, LINKS_EXTRACT_MIN_CTAS) extract_k
     if (n_probe_acc) atomicAdd(&ctr->n_bf_probes, n_probe_acc);
     if (n_load_acc) atomicAdd(&ctr->n_bf_loads, n_load_acc);
     if (n_msec_acc) atomicAdd(&ctr->n_member_sectors, n_msec_acc);
+  }
+  if (ROUTED) {  // every record of this launch is visible to its owner before the count that announces it
+    if (last_block_after_fence(&x->blocks_done)) publish_counts(x, L, epoch, 0);
   }
 }
 

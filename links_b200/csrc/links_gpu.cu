@@ -62,6 +62,7 @@ struct TimedSpan { int fam; cudaEvent_t a, b; };
 struct links_ctx {
   int device = 0;
   int sm_count = 148;
+  size_t dev_total_mem = 0;
   links_params prm{};
   std::vector<uint32_t> dist;
   std::vector<uint32_t> step;
@@ -136,14 +137,19 @@ struct links_ctx {
 
   // peer-memory exchange (exchange.cuh); attached once, survives links_reset
   bool x_attached = false, x_finished = false, x_settled = false;
+  bool x_fused = true;          // pairs leave for their owner from inside extract_kernel (no local pair set); false: local de-duplication first, route_kernel after every launch (LINKS_EXCHANGE_DEDUP=local)
+  bool x_job_started = false;   // something of this job may already sit in the owned set
+  uint64_t x_cand_hint = 0;     // candidates of the largest reads_push seen: sizes the owned set before a job's first import
   InboxLayout x_lay{};
   uint64_t x_epoch = 0;
   DevBuf d_xdev;                                  // ExchangeDev
   DevBuf d_owned, d_owned_list, d_owned_okeys;    // the pairs this rank owns (imports land here)
   uint64_t owned_cap = 0;
-  cudaStream_t s_import = nullptr;
-  cudaEvent_t ev_routed = nullptr, ev_imported = nullptr;
+  cudaStream_t s_import = nullptr, s_route = nullptr;
+  cudaEvent_t ev_routed = nullptr, ev_imported = nullptr, ev_extracted = nullptr;
   DevBuf f_rowcnt;
+  FinalRow* h_rows = nullptr;  // pinned staging for the rows' D2H
+  size_t h_rows_cap = 0;
 
   // timing
   std::vector<TimedSpan> spans;
@@ -208,9 +214,9 @@ void resolve_spans(links_ctx* c)
       cudaEventSynchronize(sp.b);
       cudaEventElapsedTime(&a, t0, sp.a);
       cudaEventElapsedTime(&b, t0, sp.b);
-      fprintf(stderr, "[links timeline] %-8s %8.3f -> %8.3f ms\n", names[sp.fam], a, b);
+      fprintf(stderr, "[links timeline dev%d] %-8s %8.3f -> %8.3f ms\n", c->device, names[sp.fam], a, b);
     }
-    fprintf(stderr, "[links timeline] ----\n");
+    fprintf(stderr, "[links timeline dev%d] ----\n", c->device);
   }
   for (auto& sp : c->spans) {
     float ms = 0;
@@ -276,18 +282,24 @@ BloomView bloom_view(links_ctx* c)
 
 // extract_kernel is instantiated for the Bloom hash counts LINKS produces in practice
 // (hash_num = floor(-log2(fpr)): 9 for the default -p 0.001) and once with a runtime count.
-using ExtractFn = void (*)(ReadBatch, DistParams, int, uint64_t, const ulonglong2*, BloomView, MemberView, PairView, Counters*);
-ExtractFn extract_fn_for(uint32_t hash_num)
+using ExtractFn = void (*)(ReadBatch, DistParams, int, uint64_t, const ulonglong2*, BloomView, MemberView, PairView, Counters*,
+                           ExchangeDev*, InboxLayout, uint64_t);
+template <bool ROUTED>
+ExtractFn extract_fn_sel(uint32_t hash_num)
 {
   switch (hash_num) {
-  case 6: return extract_kernel<6>;
-  case 7: return extract_kernel<7>;
-  case 8: return extract_kernel<8>;
-  case 9: return extract_kernel<9>;
-  case 10: return extract_kernel<10>;
-  case 13: return extract_kernel<13>;
-  default: return extract_kernel<0>;
+  case 6: return extract_kernel<6, ROUTED>;
+  case 7: return extract_kernel<7, ROUTED>;
+  case 8: return extract_kernel<8, ROUTED>;
+  case 9: return extract_kernel<9, ROUTED>;
+  case 10: return extract_kernel<10, ROUTED>;
+  case 13: return extract_kernel<13, ROUTED>;
+  default: return extract_kernel<0, ROUTED>;
   }
+}
+ExtractFn extract_fn_for(uint32_t hash_num, bool routed = false)
+{
+  return routed ? extract_fn_sel<true>(hash_num) : extract_fn_sel<false>(hash_num);
 }
 const uint32_t kExtractVariants[] = {0, 6, 7, 8, 9, 10, 13};
 
@@ -476,6 +488,7 @@ int ensure_pair_capacity(links_ctx* c, uint64_t incoming, uint64_t later)
     }
   }
   CU(c, cudaStreamSynchronize(c->s_compute));
+  CU(c, cudaStreamSynchronize(c->s_route));  // a routing kernel may still read the old list
   c->d_pairs.release(); c->d_pair_list.release(); c->d_pair_okeys.release();
   c->d_pairs = nb; c->d_pair_list = nl; c->d_pair_okeys = nk;
   c->pair_cap = cap;
@@ -493,8 +506,7 @@ int ensure_member_capacity(links_ctx* c)
   const uint64_t need_buckets = c->contig_positions / 2 + 1;  // 4 slots per bucket, load 0.5
   if (c->member_buckets >= need_buckets) return LINKS_OK;
   const uint64_t estimate = c->member_buckets ? need_buckets + need_buckets / 2 : std::max(need_buckets, c->bf_bytes * 9 / 32);
-  size_t free_b = 0, total_b = 0;
-  CU(c, cudaMemGetInfo(&free_b, &total_b));
+  const size_t total_b = c->dev_total_mem;  // (cudaMemGetInfo is a slow driver call; the total does not change)
   if (estimate * sizeof(MemberBucket) > total_b / 8 && estimate * sizeof(MemberBucket) > c->d_members.cap) {
     c->member_buckets = 0; c->member_off = true;  // large assemblies: every k-mer takes the probe path
     return LINKS_OK;
@@ -536,11 +548,18 @@ PairView owned_view(links_ctx* c)
 
 int ensure_owned(links_ctx* c, uint64_t min_cap)
 {
-  const uint64_t want = std::max<uint64_t>(std::max(min_cap, c->pair_cap), 1ull << 16);
-  if (c->owned_cap >= want || (c->owned_cap && !min_cap)) return LINKS_OK;  // a live table is only replaced on request
+  // before a job's first import the table may be replaced by a larger one; later only exchange_settle's
+  // re-import (min_cap != 0 there) does that
+  uint64_t want = std::max<uint64_t>(std::max(min_cap, c->pair_cap), 1ull << 16);
+  if (!c->x_job_started) want = std::max<uint64_t>(want, c->x_cand_hint / 2);  // ~35 % of the candidates survive at most, load 0.7
+  const bool may_replace = min_cap != 0 || !c->x_job_started;
+  c->x_job_started = true;
+  if (c->owned_cap >= want || (c->owned_cap && !may_replace)) return LINKS_OK;
   const uint64_t cap = 1ull << log2_ceil(want);
   const bool multi_d = c->prm.n_dist > 1;
+  CU(c, cudaStreamSynchronize(c->s_route));
   CU(c, cudaStreamSynchronize(c->s_import));
+  CU(c, cudaStreamSynchronize(c->s_aux));  // links_reset may still be clearing the old table
   c->d_owned.release(); c->d_owned_list.release(); c->d_owned_okeys.release();
   CU(c, c->d_owned.ensure(cap * sizeof(PairSlot)));
   CU(c, c->d_owned_list.ensure(pair_list_capacity(cap) * sizeof(ulonglong2)));
@@ -552,22 +571,10 @@ int ensure_owned(links_ctx* c, uint64_t min_cap)
   return LINKS_OK;
 }
 
-// s_compute: route the new part of the dense pair list + publish; s_import: insert what has arrived
-int exchange_route(links_ctx* c, bool finish)
+// s_import, after ev_routed: insert what has arrived (with `finish`: wait for every rank's "done" first)
+int exchange_import_round(links_ctx* c, bool finish)
 {
   ExchangeDev* x = c->d_xdev.as<ExchangeDev>();
-  const unsigned long long* n_unique = &c->d_ctr.as<Counters>()->n_unique;
-  {
-    Span sp(c, F_EXCHANGE, c->s_compute);
-    if (c->pair_cap) {
-      route_kernel<<<c->sm_count * 2, kCtaThreads, 0, c->s_compute>>>(pair_view(c), n_unique, x, c->x_lay, c->x_epoch, finish ? 1 : 0);
-    } else {
-      commit_kernel<<<1, kMaxP2PRanks, 0, c->s_compute>>>(x, c->x_lay, c->x_epoch, finish ? 1 : 0);
-    }
-    c->launches++;
-  }
-  CU(c, cudaGetLastError());
-  CU(c, cudaEventRecord(c->ev_routed, c->s_compute));
   CU(c, cudaStreamWaitEvent(c->s_import, c->ev_routed, 0));
   CU(c, cudaStreamWaitEvent(c->s_import, c->ev_cleared, 0));
   int rc = ensure_owned(c, 0);
@@ -583,6 +590,43 @@ int exchange_route(links_ctx* c, bool finish)
   return LINKS_OK;
 }
 
+// s_compute: route the new part of the dense pair list + publish; s_import: insert what has arrived
+int exchange_route(links_ctx* c, bool finish)
+{
+  ExchangeDev* x = c->d_xdev.as<ExchangeDev>();
+  // the list length as of now (stream order: after the extract launch just enqueued); the routing itself runs on
+  // s_route beside the next extract launch
+  CU(c, cudaMemcpyAsync(&x->route_hi, &c->d_ctr.as<Counters>()->n_unique, 8, cudaMemcpyDeviceToDevice, c->s_compute));
+  CU(c, cudaEventRecord(c->ev_extracted, c->s_compute));
+  CU(c, cudaStreamWaitEvent(c->s_route, c->ev_extracted, 0));
+  {
+    Span sp(c, F_EXCHANGE, c->s_route);
+    if (c->pair_cap) {
+      route_kernel<<<c->sm_count * 2, kCtaThreads, 0, c->s_route>>>(pair_view(c), x, c->x_lay, c->x_epoch, finish ? 1 : 0);
+    } else {
+      commit_kernel<<<1, kMaxP2PRanks, 0, c->s_route>>>(x, c->x_lay, c->x_epoch, finish ? 1 : 0);
+    }
+    c->launches++;
+  }
+  CU(c, cudaGetLastError());
+  CU(c, cudaEventRecord(c->ev_routed, c->s_route));
+  return exchange_import_round(c, finish);
+}
+
+// fused mode: extract_kernel<.., true> has written its survivors into the owners' inboxes and published the counts
+int exchange_after_routed_extract(links_ctx* c, bool finish)
+{
+  ExchangeDev* x = c->d_xdev.as<ExchangeDev>();
+  if (finish) {
+    Span sp(c, F_EXCHANGE, c->s_compute);
+    commit_kernel<<<1, kMaxP2PRanks, 0, c->s_compute>>>(x, c->x_lay, c->x_epoch, 1);
+    c->launches++;
+    CU(c, cudaGetLastError());
+  }
+  CU(c, cudaEventRecord(c->ev_routed, c->s_compute));
+  return exchange_import_round(c, finish);
+}
+
 // Before stage 4: everything this rank owns is in the owned set (or re-import it into a larger one), then the
 // owned set takes the place of the local one so classify and the inspection calls see it.
 int exchange_settle(links_ctx* c)
@@ -592,13 +636,15 @@ int exchange_settle(links_ctx* c)
   ExchangeDev* x = c->d_xdev.as<ExchangeDev>();
   for (int attempt = 0;; ++attempt) {
     CU(c, cudaStreamSynchronize(c->s_compute));
-    CU(c, cudaStreamSynchronize(c->s_import));
+    CU(c, cudaStreamSynchronize(c->s_route));
+  CU(c, cudaStreamSynchronize(c->s_import));
     ExchangeDev h;
     CU(c, cudaMemcpy(&h, x, sizeof h, cudaMemcpyDeviceToHost));
     if (h.timed_out) return fail(c, LINKS_E_CUDA, "pair exchange: timed out waiting for the other ranks to finish routing (LINKS_EXCHANGE_TIMEOUT_MS)");
     if (h.route_overflow)
-      return fail(c, LINKS_E_LIMIT, "pair exchange: a peer inbox region is full (%llu records per source rank); attach a larger inbox",
-                  (unsigned long long)c->x_lay.pair_cap);
+      return fail(c, LINKS_E_LIMIT, "pair exchange: a peer inbox region is full (%llu records per source rank); attach a larger inbox%s",
+                  (unsigned long long)c->x_lay.pair_cap,
+                  c->x_fused ? " or, for reads that repeat the same k-mer pairs many times, set LINKS_EXCHANGE_DEDUP=local (de-duplicate before sending)" : "");
     if (!h.owned_overflow) {
       CU(c, cudaMemcpyAsync(&c->d_ctr.as<Counters>()->n_unique, &x->n_owned, 8, cudaMemcpyDeviceToDevice, c->s_compute));
       break;
@@ -784,11 +830,14 @@ int links_create(links_ctx** out, const links_params* p)
   cudaDeviceProp prop;
   CUC(cudaGetDeviceProperties(&prop, c->device));
   c->sm_count = prop.multiProcessorCount;
+  c->dev_total_mem = prop.totalGlobalMem;
   CUC(cudaStreamCreateWithFlags(&c->s_compute, cudaStreamNonBlocking));
   CUC(cudaStreamCreateWithFlags(&c->s_copy, cudaStreamNonBlocking));
   CUC(cudaStreamCreateWithFlags(&c->s_aux, cudaStreamNonBlocking));
   CUC(cudaStreamCreateWithFlags(&c->s_pack, cudaStreamNonBlocking));
   CUC(cudaStreamCreateWithFlags(&c->s_import, cudaStreamNonBlocking));
+  CUC(cudaStreamCreateWithFlags(&c->s_route, cudaStreamNonBlocking));
+  CUC(cudaEventCreateWithFlags(&c->ev_extracted, cudaEventDisableTiming));
   CUC(cudaEventCreateWithFlags(&c->ev_routed, cudaEventDisableTiming));
   CUC(cudaEventCreateWithFlags(&c->ev_imported, cudaEventDisableTiming));
   CUC(cudaEventCreateWithFlags(&c->ev_table, cudaEventDisableTiming));
@@ -820,11 +869,12 @@ int links_create(links_ctx** out, const links_params* p)
     CUC(cudaMemcpy(c->d_tab2.p, tab2.data(), tab2.size() * sizeof(ulonglong2), cudaMemcpyHostToDevice));
     CUC(c->d_cursor.ensure(64));
     int occ = 0;
-    for (uint32_t h : kExtractVariants) {
-      CUC(cudaFuncSetAttribute(extract_fn_for(h), cudaFuncAttributeMaxDynamicSharedMemorySize, int(extract_smem_bytes(p->k))));
-      CUC(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, extract_fn_for(h), kCtaThreads, extract_smem_bytes(p->k)));
-      c->extract_ctas_per_sm = std::max(occ, 1);
-    }
+    for (uint32_t h : kExtractVariants)
+      for (int routed = 0; routed < 2; ++routed) {
+        CUC(cudaFuncSetAttribute(extract_fn_for(h, routed), cudaFuncAttributeMaxDynamicSharedMemorySize, int(extract_smem_bytes(p->k))));
+        CUC(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, extract_fn_for(h, routed), kCtaThreads, extract_smem_bytes(p->k)));
+        c->extract_ctas_per_sm = std::max(occ, 1);
+      }
     {
       // load every kernel now: with CUDA's lazy module loading a first launch may have to wait for the
       // device to go idle, which must not happen while a peer-wait kernel (exchange.cuh) is resident
@@ -871,6 +921,7 @@ void links_destroy(links_ctx* c)
   c->contig_ascii.release();
   for (int i = 0; i < links_ctx::kSnaps; ++i) if (c->ev_snap[i]) cudaEventDestroy(c->ev_snap[i]);
   if (c->h_snap) cudaFreeHost(c->h_snap);
+  if (c->h_rows) cudaFreeHost(c->h_rows);
   for (DevBuf* b : {&c->f_keys[0], &c->f_keys[1], &c->f_vals[0], &c->f_vals[1], &c->f_issues, &c->f_tiglen, &c->f_hist,
                     &c->f_scan_tmp, &c->f_flags, &c->f_total, &c->f_okeys, &c->f_olinks, &c->f_ogaps, &c->f_final, &c->f_exch, &c->f_il, &c->f_ig}) b->release();
   c->d_tab.release(); c->d_tab2.release(); c->d_cursor.release(); c->d_dist.release(); c->d_step.release(); c->d_minallowed.release();
@@ -880,6 +931,8 @@ void links_destroy(links_ctx* c)
   if (c->s_aux) cudaStreamDestroy(c->s_aux);
   if (c->s_pack) cudaStreamDestroy(c->s_pack);
   if (c->s_import) cudaStreamDestroy(c->s_import);
+  if (c->s_route) cudaStreamDestroy(c->s_route);
+  if (c->ev_extracted) cudaEventDestroy(c->ev_extracted);
   if (c->ev_routed) cudaEventDestroy(c->ev_routed);
   if (c->ev_imported) cudaEventDestroy(c->ev_imported);
   c->d_xdev.release(); c->d_owned.release(); c->d_owned_list.release(); c->d_owned_okeys.release(); c->f_rowcnt.release();
@@ -897,6 +950,7 @@ int links_sync(links_ctx* c)
   CU(c, cudaStreamSynchronize(c->s_copy));
   CU(c, cudaStreamSynchronize(c->s_aux));
   CU(c, cudaStreamSynchronize(c->s_compute));
+  CU(c, cudaStreamSynchronize(c->s_route));
   CU(c, cudaStreamSynchronize(c->s_import));
   return LINKS_OK;
 }
@@ -1029,7 +1083,8 @@ static int push_read_chunk(links_ctx* c, const char* seq, const uint8_t* dev_seq
     CU(c, cudaEventSynchronize(c->ev_done[si]));
   }
   CU(c, cudaStreamWaitEvent(c->s_compute, c->ev_cleared, 0));  // links_reset clears the pair set on s_aux
-  int rc = ensure_pair_capacity(c, cand, later);
+  const bool fused = c->x_attached && c->x_fused;  // no local pair set: survivors go straight to their owners
+  int rc = fused ? LINKS_OK : ensure_pair_capacity(c, cand, later);
   if (rc) return rc;
   SeqBatchDev& b = c->slot[si];
   b.first_read_idx = first_read_idx;
@@ -1047,10 +1102,10 @@ static int push_read_chunk(links_ctx* c, const char* seq, const uint8_t* dev_seq
                    first_read_idx, c->d_cursor.as<unsigned int>()};
       DistParams dp{c->d_dist.as<uint32_t>(), c->d_step.as<uint32_t>(), c->prm.n_dist, c->prm.offset};
       CU(c, cudaMemsetAsync(c->d_cursor.p, 0, sizeof(unsigned int), c->s_compute));
-      extract_fn_for(c->hash_num)<<<grid_for(c, b.n_tiles, kWarpsPerCta, c->extract_ctas_per_sm), kCtaThreads,
-                                    extract_smem_bytes(c->prm.k), c->s_compute>>>(
+      extract_fn_for(c->hash_num, fused)<<<grid_for(c, b.n_tiles, kWarpsPerCta, c->extract_ctas_per_sm), kCtaThreads,
+                                           extract_smem_bytes(c->prm.k), c->s_compute>>>(
         rb, dp, int(c->prm.k), c->kseed, c->d_tab2.as<ulonglong2>(), bloom_view(c), member_view(c),
-        pair_view(c), c->d_ctr.as<Counters>());
+        pair_view(c), c->d_ctr.as<Counters>(), c->d_xdev.as<ExchangeDev>(), c->x_lay, c->x_epoch);
       c->launches++;
       c->extract_launches++;
       CU(c, cudaGetLastError());
@@ -1058,7 +1113,8 @@ static int push_read_chunk(links_ctx* c, const char* seq, const uint8_t* dev_seq
     rc = enqueue_snapshot(c);
     if (rc) return rc;
     if (c->x_attached) {
-      rc = exchange_route(c, false);  // this launch's new pairs travel to their owners while the next chunk is extracted
+      // the owners insert this launch's pairs while the next chunk is extracted
+      rc = fused ? exchange_after_routed_extract(c, false) : exchange_route(c, false);
       if (rc) return rc;
     }
   }
@@ -1107,6 +1163,7 @@ static int reads_push_impl(links_ctx* c, const char* seq, const uint8_t* dev_seq
     if (len >= (1ull << 28)) return fail(c, LINKS_E_LIMIT, "links_reads_push: read longer than 2^28-1");
     for (uint32_t di = 0; di < nd; ++di) total_cand += seg_count(len, di);
   }
+  c->x_cand_hint = std::max(c->x_cand_hint, total_cand);
   uint32_t i0 = 0;
   uint64_t done_cand = 0;
   std::vector<uint32_t> segs;
@@ -1167,6 +1224,7 @@ int links_reset(links_ctx* c)
   CU(c, cudaStreamSynchronize(c->s_copy));
   CU(c, cudaStreamSynchronize(c->s_aux));
   CU(c, cudaStreamSynchronize(c->s_compute));
+  CU(c, cudaStreamSynchronize(c->s_route));
   CU(c, cudaStreamSynchronize(c->s_import));
   c->table_started = false; c->table_batches_built = 0;
   poll_snapshots(c);
@@ -1193,7 +1251,7 @@ int links_reset(links_ctx* c)
   }
   if (c->x_attached) {
     c->x_epoch++;
-    c->x_finished = false; c->x_settled = false;
+    c->x_finished = false; c->x_settled = false; c->x_job_started = false;
     CU(c, cudaMemsetAsync(reinterpret_cast<char*>(c->d_xdev.p) + offsetof(ExchangeDev, cursor), 0,
                           sizeof(ExchangeDev) - offsetof(ExchangeDev, cursor), c->s_compute));
     if (c->owned_cap) {
@@ -1215,6 +1273,7 @@ int links_get_timing(links_ctx* c, links_timing* t, int reset)
   CU(c, cudaStreamSynchronize(c->s_copy));
   CU(c, cudaStreamSynchronize(c->s_aux));
   CU(c, cudaStreamSynchronize(c->s_compute));
+  CU(c, cudaStreamSynchronize(c->s_route));
   CU(c, cudaStreamSynchronize(c->s_import));
   resolve_spans(c);
   t->ms_h2d = c->fam_ms[F_H2D]; t->ms_pack = c->fam_ms[F_PACK]; t->ms_bf_build = c->fam_ms[F_BF];
@@ -1333,7 +1392,7 @@ int links_finalize(links_ctx* c, links_row** rows_out, uint64_t* n_rows_out, lin
   if (n_rows_raw > row_cap) return fail(c, LINKS_E_CUDA, "links_finalize: internal row overflow");
 
   // ---- K5b: sort + reduce-by-key on the packed row key, then mirror expansion + a final small sort
-  std::vector<FinalRow> hrows;
+  FinalRow* hrows = nullptr;
   uint32_t n_seg = 0, n_out32 = 0;
   const int key_bits = 3 + 2 * tb;
   if (n_rows_raw) {
@@ -1378,12 +1437,19 @@ int links_finalize(links_ctx* c, links_row** rows_out, uint64_t* n_rows_out, lin
                                                            c->f_final.as<FinalRow>());
     c->launches++;
     CU(c, cudaGetLastError());
-    hrows.resize(n_out32);
+    if (c->h_rows_cap < n_out32) {
+      if (c->h_rows) cudaFreeHost(c->h_rows);
+      c->h_rows = nullptr; c->h_rows_cap = 0;
+      const size_t want = size_t(n_out32) + n_out32 / 4 + 1024;
+      CU(c, cudaHostAlloc(reinterpret_cast<void**>(&c->h_rows), want * sizeof(FinalRow), cudaHostAllocDefault));
+      c->h_rows_cap = want;
+    }
+    hrows = c->h_rows;
   }
   std::vector<IssueRec> hi(h.n_issues);
   {
     Span sp(c, F_D2H, s);
-    if (n_out32) CU(c, cudaMemcpyAsync(hrows.data(), c->f_final.p, uint64_t(n_out32) * sizeof(FinalRow), cudaMemcpyDeviceToHost, s));
+    if (n_out32) CU(c, cudaMemcpyAsync(hrows, c->f_final.p, uint64_t(n_out32) * sizeof(FinalRow), cudaMemcpyDeviceToHost, s));
     if (h.n_issues) CU(c, cudaMemcpyAsync(hi.data(), d_issues.p, h.n_issues * sizeof(IssueRec), cudaMemcpyDeviceToHost, s));
   }
   CU(c, cudaStreamSynchronize(s));
@@ -1734,7 +1800,11 @@ int links_exchange_attach(links_ctx* c, uint32_t rank, uint32_t n_ranks, void* c
   CU(c, cudaDeviceSynchronize());
   c->x_lay = L;
   c->x_epoch = 1;
-  c->x_attached = true; c->x_finished = false; c->x_settled = false;
+  c->x_attached = true; c->x_finished = false; c->x_settled = false; c->x_job_started = false;
+  {
+    const char* e = getenv("LINKS_EXCHANGE_DEDUP");
+    c->x_fused = !(e && strcmp(e, "local") == 0);
+  }
   return LINKS_OK;
 }
 
@@ -1745,7 +1815,7 @@ int links_exchange_finish(links_ctx* c)
   if (c->x_finished) return LINKS_OK;
   CU(c, cudaSetDevice(c->device));
   CU(c, cudaStreamWaitEvent(c->s_compute, c->ev_cleared, 0));
-  int rc = exchange_route(c, true);
+  int rc = c->x_fused ? exchange_after_routed_extract(c, true) : exchange_route(c, true);
   if (rc) return rc;
   c->x_finished = true;
   return LINKS_OK;

@@ -10,8 +10,9 @@ import sys
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 
 
-def rank_main(r: int, n_ranks: int, name: str, inbox_bytes: int, queues, results, barrier, n_jobs: int) -> None:
+def rank_main(r: int, n_ranks: int, name: str, inbox_bytes: int, queues, results, barrier, n_jobs: int, dedup: str = "owner") -> None:
     os.environ.setdefault("LINKS_EXCHANGE_TIMEOUT_MS", "20000")
+    os.environ["LINKS_EXCHANGE_DEDUP"] = dedup  # owner: pairs leave from inside extract_kernel; local: local set + route_kernel
     if ROOT not in sys.path:
         sys.path.insert(0, ROOT)
     try:

@@ -342,13 +342,17 @@ def test_pair_exchange_between_contexts_equals_single_context(gpu_lib, name, n_r
 
 
 @pytest.mark.timeout(280)
-@pytest.mark.parametrize("name,n_ranks,inbox_mb", [("adv_tandem", 2, 64), ("adv_offset_k20", 3, 64), ("c1", 2, 512)])
-def test_peer_memory_exchange_equals_single_context(gpu_lib, name, n_ranks, inbox_mb):
+@pytest.mark.parametrize("name,n_ranks,inbox_mb,dedup", [("adv_tandem", 2, 1024, "owner"), ("adv_tandem", 2, 64, "local"),
+                                                         ("adv_offset_k20", 3, 1024, "owner"), ("c1", 2, 1024, "owner"),
+                                                         ("c1", 2, 512, "local")])
+def test_peer_memory_exchange_equals_single_context(gpu_lib, name, n_ranks, inbox_mb, dedup):
     """links_exchange_attach/finish as deployed: one PROCESS per rank (tests/_exchange_worker.py), here all
     on GPU 0, inboxes shared through CUDA IPC like peer memory on an NVLink box.  Reads are sharded;
     routing, import, the wait for the other ranks and the row merge on rank 0 all run inside the
     library.  Two jobs back to back cover the epoch/half switch.  Rank 0's rows == the reference golden;
-    the owned pair sets partition the single-context pair set (same winning distance index)."""
+    the owned pair sets partition the single-context pair set (same winning distance index).  Both
+    exchange modes: de-duplication at the owner only (records leave from inside extract_kernel) and local
+    de-duplication first (route_kernel after every extract launch)."""
     import queue
 
     import torch.multiprocessing as mp
@@ -362,7 +366,7 @@ def test_peer_memory_exchange_equals_single_context(gpu_lib, name, n_ranks, inbo
     results = ctx.Queue()
     barrier = ctx.Barrier(n_ranks)
     n_jobs = 2
-    procs = [ctx.Process(target=rank_main, args=(r, n_ranks, name, inbox_mb << 20, queues, results, barrier, n_jobs), daemon=True)
+    procs = [ctx.Process(target=rank_main, args=(r, n_ranks, name, inbox_mb << 20, queues, results, barrier, n_jobs, dedup), daemon=True)
              for r in range(n_ranks)]
     for p in procs:
         p.start()
