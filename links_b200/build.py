@@ -52,6 +52,7 @@ def build_lib(force: bool = False, verbose: bool = False) -> str:
     if not force and _newer(LIB, srcs):
         return LIB
     cmd = [_nvcc(), *NVCC_FLAGS, "-shared", "-o", LIB, os.path.join(CSRC, "links_gpu.cu")]
+    cmd[1:1] = os.environ.get("LINKS_NVCC_DEFS", "").split()  # kernel-variant experiments: -DLINKS_EXTRACT_TILE=256 ...
     if verbose:
         cmd[1:1] = ["-Xptxas", "-v"]
         print(" ".join(cmd))

@@ -27,6 +27,9 @@ namespace links {
 #ifndef LINKS_EXTRACT_TILE
 #define LINKS_EXTRACT_TILE 512
 #endif
+#ifndef LINKS_PROBE_WITH_SET
+#define LINKS_PROBE_WITH_SET 0
+#endif
 #ifndef LINKS_EXTRACT_MIN_CTAS
 #define LINKS_EXTRACT_MIN_CTAS 4
 #endif
@@ -102,7 +105,7 @@ __global__ void __launch_bounds__(kCtaThreads, LINKS_EXTRACT_MIN_CTAS) extract_k
     if (tile >= rb.n_tiles) break;
 
     // ---- tile header (warp-uniform; every lane computes the same values)
-    const uint32_t s = find_segment(rb.seg_tile_start, n_seg, tile);
+    const uint32_t s = find_segment_warp(rb.seg_tile_start, n_seg, tile);
     const uint32_t r = s / dp.n_dist, di = s - r * dp.n_dist;
     const uint64_t g0 = rb.off[r] - rb.base0;
     const uint64_t len = rb.off[r + 1] - rb.off[r];
@@ -156,12 +159,22 @@ __global__ void __launch_bounds__(kCtaThreads, LINKS_EXTRACT_MIN_CTAS) extract_k
           uint64_t f, rr;
           hash_kmer2(rb.packed, pos_a(rank_n(q)), k, s_tab, f, rr);
           h0 = rr < f ? rr : f;
+#if LINKS_PROBE_WITH_SET
+          // set bucket and the first probes are independent loads: issue them together (one latency, not two);
+          // a proven member's probe result is simply not used
+          uint32_t np = 0;
+          pass = H ? bloom_probe_fixed<kFirst>(bf, h0, kseed, 0, np) : bloom_probe_loop(bf, h0, kseed, 0, h_first, np);
+          n_load += h_first;
+          if (has_set) member = member_contains(mv, h0, n_msec);
+          if (member) { n_probe += hn; pass = false; } else n_probe += np;
+#else
           if (has_set) member = member_contains(mv, h0, n_msec);
           if (member) n_probe += hn;  // the filter holds every set key: all hash_num bits are set, no need to look
           else {
             pass = H ? bloom_probe_fixed<kFirst>(bf, h0, kseed, 0, n_probe) : bloom_probe_loop(bf, h0, kseed, 0, h_first, n_probe);
             n_load += h_first;
           }
+#endif
         }
         next_q += 32;
         uint32_t slot;
@@ -196,12 +209,20 @@ __global__ void __launch_bounds__(kCtaThreads, LINKS_EXTRACT_MIN_CTAS) extract_k
           q = Q.q2_i[n2 + lane];
           hash_kmer2(rb.packed, pos_b(rank_n(q)), k, s_tab, f, rr);
           const uint64_t h0 = rr < f ? rr : f;
+#if LINKS_PROBE_WITH_SET
+          uint32_t np = 0;
+          pass = H ? bloom_probe_fixed<kFirst>(bf, h0, kseed, 0, np) : bloom_probe_loop(bf, h0, kseed, 0, h_first, np);
+          n_load += h_first;
+          if (has_set) member = member_contains(mv, h0, n_msec);
+          if (member) { n_probe += hn; pass = false; } else n_probe += np;
+#else
           if (has_set) member = member_contains(mv, h0, n_msec);
           if (member) n_probe += hn;
           else {
             pass = H ? bloom_probe_fixed<kFirst>(bf, h0, kseed, 0, n_probe) : bloom_probe_loop(bf, h0, kseed, 0, h_first, n_probe);
             n_load += h_first;
           }
+#endif
         }
         __syncwarp();
         uint32_t slot;

@@ -271,6 +271,26 @@ __device__ __forceinline__ uint32_t find_segment(const uint32_t* __restrict__ se
   return lo;
 }
 
+// same answer, found by the whole warp: 32 partition points per round instead of one (3 dependent loads for
+// 25k segments instead of 15).  All lanes must call it; the result is warp-uniform.
+__device__ __forceinline__ uint32_t find_segment_warp(const uint32_t* __restrict__ seg_tile_start, uint32_t n_seg, uint32_t tile)
+{
+  const uint32_t lane = threadIdx.x & 31;
+  uint32_t lo = 0, hi = n_seg;  // invariant: seg[lo] <= tile, (hi == n_seg or seg[hi] > tile)
+  while (hi - lo > 1) {
+    const uint32_t span = hi - lo;
+    const uint32_t stride = (span + 32) / 33;            // 32 probes cut [lo,hi) into <= 33 pieces
+    const uint32_t idx = lo + (lane + 1) * stride;
+    const bool le = idx < hi && __ldg(seg_tile_start + idx) <= tile;
+    const uint32_t c = __popc(__ballot_sync(0xffffffffu, le));  // probes are monotone: the first c are true
+    const uint32_t nlo = lo + c * stride;
+    const uint32_t nhi = lo + (c + 1) * stride;
+    lo = nlo;
+    if (nhi < hi) hi = nhi;
+  }
+  return lo;
+}
+
 // ------------------------------------------------------------------ contigs: Bloom build + table build
 
 struct ContigBatch {
