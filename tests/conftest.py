@@ -21,7 +21,7 @@ if ROOT not in sys.path:
     sys.path.insert(0, ROOT)
 
 GOLDEN = os.path.join(ROOT, "tests", "golden")
-GOLDEN_CASES = sorted(d for d in os.listdir(GOLDEN) if os.path.exists(os.path.join(GOLDEN, d, "case.json")))
+GOLDEN_CASES = sorted(d for d in os.listdir(GOLDEN) if not d.startswith("cfg_") and os.path.exists(os.path.join(GOLDEN, d, "case.json")))
 
 
 def pytest_configure(config):
@@ -92,6 +92,43 @@ def sort_issue_records(text: bytes) -> bytes:
 @pytest.fixture(params=GOLDEN_CASES)
 def golden_case(request) -> GoldenCase:
     return GoldenCase(request.param)
+
+
+class ConfigCase:
+    """A BASELINE.json configuration at reference-runnable size (tools/make_config_golden.py): inputs are
+    regenerated from links_b200.synth (seeded), expected outputs come from the unmodified reference."""
+
+    def __init__(self, name: str):
+        self.name = name
+        self.dir = os.path.join(GOLDEN, "cfg_" + name)
+        self.meta = json.load(open(os.path.join(self.dir, "case.json")))
+        self.opts = self.meta["opts"]
+
+    def inputs(self):
+        from links_b200 import synth
+        g, nc, cov, rl, _k, _d, _t = self.meta["synth"]
+        genome = synth.make_genome(g, seed=11)
+        contigs = synth.make_contigs(genome, nc, seed=13)
+        reads = synth.make_reads(genome, cov, rl, seed=12)
+        h = hashlib.sha256()
+        for a in (contigs.seq, contigs.off, reads.seq, reads.off):
+            h.update(a.tobytes())
+        assert h.hexdigest() == self.meta["inputs_sha256"], "links_b200.synth no longer reproduces the golden inputs"
+        return contigs, reads
+
+    def expected_tsv(self) -> bytes:
+        return open(os.path.join(self.dir, "expected.tigpair_checkpoint.tsv"), "rb").read()
+
+    def expected_issues(self) -> bytes:
+        return open(os.path.join(self.dir, "expected.pairing_issues"), "rb").read()
+
+
+CONFIG_CASES = sorted(d[4:] for d in os.listdir(GOLDEN) if d.startswith("cfg_"))
+
+
+@pytest.fixture(params=CONFIG_CASES)
+def config_case(request) -> ConfigCase:
+    return ConfigCase(request.param)
 
 
 @pytest.fixture(scope="session")

@@ -104,6 +104,28 @@ def test_whole_path_matches_reference_goldens(gpu_lib, golden_case):
     assert stats["n_rows"] == golden_case.meta["n_rows"]
 
 
+def test_baseline_configs_match_reference(gpu_lib, config_case):
+    """BASELINE.json configs[2..4] (multi-distance with per-distance steps; k 20 d 5000 t 5; the step sweep
+    t = 1 ... 100 at d 10000) at a size the unmodified reference ran here: .bloom, tsv and issues bit-exact."""
+    from links_b200 import bf_size
+    c = config_case
+    contigs, reads = c.inputs()
+    o = c.opts
+    _m, nbytes, h = bf_size(c.meta["contigs_file_bytes"], o["p"])
+    with _links(k=o["k"], d=o["d"], t=o["t"], o=o["o"], e=o["e"]) as L:
+        L.bf_alloc(nbytes, h)
+        L.push_contigs(contigs)
+        L.push_reads(reads)
+        bits = L.bf_bits()
+        rows, issues, stats = L.finalize()
+        tsv, iss = L.format_rows(rows), L.format_issues(issues)
+    assert sort_lines(tsv) == c.expected_tsv()
+    assert sort_issue_records(iss) == c.expected_issues()
+    assert stats["n_rows"] == c.meta["n_rows"]
+    from links_b200 import bf_header
+    assert sha256(bf_header(o["k"], h, nbytes) + bits.tobytes()) == c.meta["bloom_sha256"]
+
+
 def test_intermediates_match_oracle(gpu_lib, oracle, golden_case):
     """Candidate / survivor counts, the distinct pair set with its first-wins distance index, and the
     stage-4 counters, against the oracle on the same inputs."""
