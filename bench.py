@@ -378,6 +378,12 @@ def main_ours(args, rank: int, world: int, local_rank: int):
             peak, peak_src = float(mp["hbm_gbs"]), "MEASURED_PEAKS.json hbm_gbs (burst copy)"
         except Exception:
             pass
+        traffic = None  # DRAM bytes per launch of the dominant kernel, from the committed ncu capture (per candidate x candidates per launch)
+        try:
+            tr = json.load(open(os.path.join(ROOT, "profiles", "extract_traffic.json")))
+            traffic = float(tr["dram_bytes_per_candidate"]) * cand * steps_l / n_launch
+        except Exception:
+            pass
         out = {
             "metric": METRIC, "value": cand_total / (ms_res * 1e-3), "unit": UNIT, "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": ms_res, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
@@ -397,7 +403,8 @@ def main_ours(args, rank: int, world: int, local_rank: int):
                     "d2h_bytes_per_step": int(d2h_bytes)},
             "gpu_launches": int(tm_res["launches"]),
             "clocks": clk,
-            "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": None,
+            "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": traffic,
+                         "traffic_source": "profiles/extract_traffic.json (ncu dram__bytes_read+write per candidate pair, c2 workload) x candidates per launch",
                          "kernel": "extract_kernel", "launches": n_launch, "ms_per_launch": ms_launch,
                          "algorithmic_bytes_per_launch": alg_bytes_launch,
                          "bytes_per_pair": alg_bytes_step / max(cand, 1), "peak_source": peak_src,
