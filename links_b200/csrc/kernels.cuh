@@ -490,9 +490,15 @@ __device__ __forceinline__ KInfo decode_kinfo(uint64_t v, int k)
   return ki;
 }
 
+// `range` != nullptr: classify list entries [range[0], range[1]) (bounds live on the device: the host
+// launches this beside the extraction without knowing how many pairs exist yet); else [0, n_pairs).
 __global__ void __launch_bounds__(kCtaThreads) classify_kernel(PairView pv, uint64_t n_pairs, TableView tv, ClassifyParams cp,
-                                                               int k, Counters* __restrict__ ctr)
+                                                               int k, Counters* __restrict__ ctr,
+                                                               const unsigned long long* __restrict__ range)
 {
+  uint64_t first = 0;
+  if (range) { first = range[0]; n_pairs = range[1] > range[0] ? range[1] - range[0] : 0; }
+  pv.list += first;
   __shared__ uint32_t sm_scan[9];
   __shared__ unsigned long long s_base;
   unsigned long long c_ok = 0, c_prob = 0, c_okc = 0, c_iz = 0, c_ill = 0, c_gate = 0;
@@ -604,6 +610,8 @@ __global__ void mirror_expand_kernel(const uint64_t* __restrict__ keys, uint32_t
   out_idx[2 * i] = int32_t(i);
   out_idx[2 * i + 1] = int32_t(i);
 }
+
+__global__ void range_advance_kernel(unsigned long long* range) { range[0] = range[1]; }
 
 struct FinalRow { uint64_t key; unsigned long long links; long long gaps; };
 __global__ void gather_rows_kernel(const uint64_t* __restrict__ keys, const int32_t* __restrict__ idx, uint32_t n,

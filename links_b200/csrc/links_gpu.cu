@@ -151,6 +151,14 @@ struct links_ctx {
   FinalRow* h_rows = nullptr;  // pinned staging for the rows' D2H
   size_t h_rows_cap = 0;
 
+  // stage 4 runs along with the extraction (single GPU): after every extract launch the pairs that launch added to
+  // the dense list are classified on s_cls, so only the last launch's share is left for links_finalize
+  bool cls_on = true, cls_valid = false, cls_started = false;
+  cudaStream_t s_cls = nullptr;
+  cudaEvent_t ev_cls_in = nullptr, ev_cls_done = nullptr;
+  DevBuf d_cls;               // {classified prefix, list length at the last launch}
+  uint64_t cls_row_cap = 0, cls_pair_cap = 0, cls_issue_cap = 0, max_read_end = 0;
+
   // timing
   std::vector<TimedSpan> spans;
   std::vector<cudaEvent_t> ev_pool;
@@ -489,6 +497,8 @@ int ensure_pair_capacity(links_ctx* c, uint64_t incoming, uint64_t later)
   }
   CU(c, cudaStreamSynchronize(c->s_compute));
   CU(c, cudaStreamSynchronize(c->s_route));  // a routing kernel may still read the old list
+  CU(c, cudaStreamSynchronize(c->s_cls));    // and so may an incremental classify; its row buffers were sized for the old table
+  c->cls_valid = false;
   c->d_pairs.release(); c->d_pair_list.release(); c->d_pair_okeys.release();
   c->d_pairs = nb; c->d_pair_list = nl; c->d_pair_okeys = nk;
   c->pair_cap = cap;
@@ -558,6 +568,7 @@ int ensure_owned(links_ctx* c, uint64_t min_cap)
   const uint64_t cap = 1ull << log2_ceil(want);
   const bool multi_d = c->prm.n_dist > 1;
   CU(c, cudaStreamSynchronize(c->s_route));
+  CU(c, cudaStreamSynchronize(c->s_cls));
   CU(c, cudaStreamSynchronize(c->s_import));
   CU(c, cudaStreamSynchronize(c->s_aux));  // links_reset may still be clearing the old table
   c->d_owned.release(); c->d_owned_list.release(); c->d_owned_okeys.release();
@@ -596,6 +607,7 @@ int exchange_route(links_ctx* c, bool finish)
   ExchangeDev* x = c->d_xdev.as<ExchangeDev>();
   // the list length as of now (stream order: after the extract launch just enqueued); the routing itself runs on
   // s_route beside the next extract launch
+  CU(c, cudaStreamWaitEvent(c->s_compute, c->ev_routed, 0));  // the previous routing round still reads route_hi
   CU(c, cudaMemcpyAsync(&x->route_hi, &c->d_ctr.as<Counters>()->n_unique, 8, cudaMemcpyDeviceToDevice, c->s_compute));
   CU(c, cudaEventRecord(c->ev_extracted, c->s_compute));
   CU(c, cudaStreamWaitEvent(c->s_route, c->ev_extracted, 0));
@@ -637,6 +649,7 @@ int exchange_settle(links_ctx* c)
   for (int attempt = 0;; ++attempt) {
     CU(c, cudaStreamSynchronize(c->s_compute));
     CU(c, cudaStreamSynchronize(c->s_route));
+  CU(c, cudaStreamSynchronize(c->s_cls));
   CU(c, cudaStreamSynchronize(c->s_import));
     ExchangeDev h;
     CU(c, cudaMemcpy(&h, x, sizeof h, cudaMemcpyDeviceToHost));
@@ -742,6 +755,47 @@ int exchange_rows(links_ctx* c, cudaStream_t s, uint32_t n, int key_bits, uint32
   return LINKS_OK;
 }
 
+// ---- stage 4 alongside the extraction (single GPU).  Valid while: the contig table is complete and being built or
+// built (no contigs after the first reads), the pair table has not been re-allocated, reads arrive in increasing
+// global ordinal when there are several distances (so a classified pair's winning distance cannot change later),
+// and the issue buffer does not overflow.  Otherwise links_finalize classifies everything from scratch as before.
+int classify_increment(links_ctx* c)
+{
+  if (!c->cls_valid || c->x_attached || !c->pair_cap) return LINKS_OK;
+  if (!(c->table_started && c->table_batches_built == c->contig_batches.size())) return LINKS_OK;
+  if (!c->cls_started) {
+    c->cls_row_cap = pair_list_capacity(c->pair_cap);
+    c->cls_pair_cap = c->pair_cap;
+    c->cls_issue_cap = c->issue_cap_hint;
+    CU(c, c->f_keys[0].ensure(c->cls_row_cap * 8)); CU(c, c->f_vals[0].ensure(c->cls_row_cap * 4));
+    CU(c, c->f_issues.ensure(c->cls_issue_cap * sizeof(IssueRec)));
+    CU(c, c->f_tiglen.ensure(c->tig_len.size() * 4));
+    CU(c, cudaMemcpyAsync(c->f_tiglen.p, c->tig_len.data(), c->tig_len.size() * 4, cudaMemcpyHostToDevice, c->s_cls));
+    c->cls_started = true;
+  }
+  if (c->pair_cap != c->cls_pair_cap) { c->cls_valid = false; return LINKS_OK; }
+  unsigned long long* range = c->d_cls.as<unsigned long long>();
+  // the previous round (beside the launch that just ended) must be through before its upper bound moves
+  CU(c, cudaStreamWaitEvent(c->s_compute, c->ev_cls_done, 0));
+  CU(c, cudaMemcpyAsync(range + 1, &c->d_ctr.as<Counters>()->n_unique, 8, cudaMemcpyDeviceToDevice, c->s_compute));
+  CU(c, cudaEventRecord(c->ev_cls_in, c->s_compute));
+  CU(c, cudaStreamWaitEvent(c->s_cls, c->ev_cls_in, 0));
+  CU(c, cudaStreamWaitEvent(c->s_cls, c->ev_table, 0));
+  {
+    Span sp(c, F_CLASSIFY, c->s_cls);
+    const int tb = log2_ceil(uint64_t(c->n_tigs_seen) * 2 + 2);
+    ClassifyParams cp{c->d_dist.as<uint32_t>(), c->d_minallowed.as<int32_t>(), c->prm.n_dist, c->f_tiglen.as<uint32_t>(), tb,
+                      c->f_keys[0].as<uint64_t>(), c->f_vals[0].as<int32_t>(), c->cls_row_cap, c->f_issues.as<IssueRec>(), c->cls_issue_cap};
+    classify_kernel<<<c->sm_count * 4, kCtaThreads, 0, c->s_cls>>>(pair_view(c), 0, table_view(c), cp, int(c->prm.k),
+                                                                   c->d_ctr.as<Counters>(), range);
+    range_advance_kernel<<<1, 1, 0, c->s_cls>>>(range);
+    c->launches += 2;
+  }
+  CU(c, cudaGetLastError());
+  CU(c, cudaEventRecord(c->ev_cls_done, c->s_cls));
+  return LINKS_OK;
+}
+
 } // namespace
 
 // ====================================================================== C ABI
@@ -837,6 +891,12 @@ int links_create(links_ctx** out, const links_params* p)
   CUC(cudaStreamCreateWithFlags(&c->s_pack, cudaStreamNonBlocking));
   CUC(cudaStreamCreateWithFlags(&c->s_import, cudaStreamNonBlocking));
   CUC(cudaStreamCreateWithFlags(&c->s_route, cudaStreamNonBlocking));
+  CUC(cudaStreamCreateWithFlags(&c->s_cls, cudaStreamNonBlocking));
+  CUC(cudaEventCreateWithFlags(&c->ev_cls_in, cudaEventDisableTiming));
+  CUC(cudaEventCreateWithFlags(&c->ev_cls_done, cudaEventDisableTiming));
+  CUC(c->d_cls.ensure(64));
+  CUC(cudaMemset(c->d_cls.p, 0, 64));
+  { const char* e = getenv("LINKS_INCREMENTAL_CLASSIFY"); c->cls_on = !(e && e[0] == '0'); c->cls_valid = c->cls_on; }
   CUC(cudaEventCreateWithFlags(&c->ev_extracted, cudaEventDisableTiming));
   CUC(cudaEventCreateWithFlags(&c->ev_routed, cudaEventDisableTiming));
   CUC(cudaEventCreateWithFlags(&c->ev_imported, cudaEventDisableTiming));
@@ -932,6 +992,10 @@ void links_destroy(links_ctx* c)
   if (c->s_pack) cudaStreamDestroy(c->s_pack);
   if (c->s_import) cudaStreamDestroy(c->s_import);
   if (c->s_route) cudaStreamDestroy(c->s_route);
+  if (c->s_cls) cudaStreamDestroy(c->s_cls);
+  if (c->ev_cls_in) cudaEventDestroy(c->ev_cls_in);
+  if (c->ev_cls_done) cudaEventDestroy(c->ev_cls_done);
+  c->d_cls.release();
   if (c->ev_extracted) cudaEventDestroy(c->ev_extracted);
   if (c->ev_routed) cudaEventDestroy(c->ev_routed);
   if (c->ev_imported) cudaEventDestroy(c->ev_imported);
@@ -951,6 +1015,7 @@ int links_sync(links_ctx* c)
   CU(c, cudaStreamSynchronize(c->s_aux));
   CU(c, cudaStreamSynchronize(c->s_compute));
   CU(c, cudaStreamSynchronize(c->s_route));
+  CU(c, cudaStreamSynchronize(c->s_cls));
   CU(c, cudaStreamSynchronize(c->s_import));
   return LINKS_OK;
 }
@@ -1011,6 +1076,7 @@ static int contigs_push_impl(links_ctx* c, const char* seq, const uint8_t* dev_s
   const uint32_t k = c->prm.k;
   std::vector<uint32_t> segs(size_t(n) + 1);
   uint64_t tiles = 0, positions = 0;
+  if (c->cls_started) { CU(c, cudaStreamSynchronize(c->s_cls)); c->cls_valid = false; }  // contigs after the first reads: stage 4 starts over at finalize
   if (c->tig_len.size() < size_t(first_tig_id) + n) c->tig_len.resize(size_t(first_tig_id) + n, 0);
   for (uint32_t i = 0; i < n; ++i) {
     if (off[i + 1] < off[i]) return fail(c, LINKS_E_INVAL, "links_contigs_push: offsets not monotone");
@@ -1112,6 +1178,8 @@ static int push_read_chunk(links_ctx* c, const char* seq, const uint8_t* dev_seq
     }
     rc = enqueue_snapshot(c);
     if (rc) return rc;
+    rc = classify_increment(c);
+    if (rc) return rc;
     if (c->x_attached) {
       // the owners insert this launch's pairs while the next chunk is extracted
       rc = fused ? exchange_after_routed_extract(c, false) : exchange_route(c, false);
@@ -1164,6 +1232,8 @@ static int reads_push_impl(links_ctx* c, const char* seq, const uint8_t* dev_seq
     for (uint32_t di = 0; di < nd; ++di) total_cand += seg_count(len, di);
   }
   c->x_cand_hint = std::max(c->x_cand_hint, total_cand);
+  if (nd > 1 && first_read_idx < c->max_read_end) c->cls_valid = false;  // an earlier ordinal may still take a classified pair's distance
+  c->max_read_end = std::max<uint64_t>(c->max_read_end, first_read_idx + n);
   uint32_t i0 = 0;
   uint64_t done_cand = 0;
   std::vector<uint32_t> segs;
@@ -1225,6 +1295,7 @@ int links_reset(links_ctx* c)
   CU(c, cudaStreamSynchronize(c->s_aux));
   CU(c, cudaStreamSynchronize(c->s_compute));
   CU(c, cudaStreamSynchronize(c->s_route));
+  CU(c, cudaStreamSynchronize(c->s_cls));
   CU(c, cudaStreamSynchronize(c->s_import));
   c->table_started = false; c->table_batches_built = 0;
   poll_snapshots(c);
@@ -1239,6 +1310,8 @@ int links_reset(links_ctx* c)
   for (int i = 0; i < links_ctx::kSlots; ++i) c->slot_used[i] = false;
   c->next_slot = 0;  // same chunk -> slot assignment every job: slot buffers stop growing after the first one
   CU(c, cudaMemsetAsync(c->d_ctr.p, 0, sizeof(Counters), c->s_compute));
+  CU(c, cudaMemsetAsync(c->d_cls.p, 0, 64, c->s_compute));
+  c->cls_valid = c->cls_on; c->cls_started = false; c->max_read_end = 0;
   if (c->x_attached && c->x_settled) {  // the previous job swapped the owned set in: undo, so each buffer keeps its role (and size)
     std::swap(c->d_pairs, c->d_owned); std::swap(c->d_pair_list, c->d_owned_list); std::swap(c->d_pair_okeys, c->d_owned_okeys);
     std::swap(c->pair_cap, c->owned_cap);
@@ -1274,6 +1347,7 @@ int links_get_timing(links_ctx* c, links_timing* t, int reset)
   CU(c, cudaStreamSynchronize(c->s_aux));
   CU(c, cudaStreamSynchronize(c->s_compute));
   CU(c, cudaStreamSynchronize(c->s_route));
+  CU(c, cudaStreamSynchronize(c->s_cls));
   CU(c, cudaStreamSynchronize(c->s_import));
   resolve_spans(c);
   t->ms_h2d = c->fam_ms[F_H2D]; t->ms_pack = c->fam_ms[F_PACK]; t->ms_bf_build = c->fam_ms[F_BF];
@@ -1349,6 +1423,10 @@ int links_finalize(links_ctx* c, links_row** rows_out, uint64_t* n_rows_out, lin
     rc = exchange_settle(c);
     if (rc) return rc;
   }
+  if (c->cls_started) {  // incremental stage 4 in flight on s_cls
+    CU(c, cudaEventRecord(c->ev_cls_done, c->s_cls));
+    CU(c, cudaStreamWaitEvent(s, c->ev_cls_done, 0));
+  }
   // unique pair count sizes the row buffers
   CU(c, cudaStreamSynchronize(s));
   Counters h;
@@ -1360,8 +1438,9 @@ int links_finalize(links_ctx* c, links_row** rows_out, uint64_t* n_rows_out, lin
   DevBuf (&d_keys)[2] = c->f_keys; DevBuf (&d_vals)[2] = c->f_vals;
   DevBuf &d_issues = c->f_issues, &d_tiglen = c->f_tiglen, &d_scan_tmp = c->f_scan_tmp, &d_flags = c->f_flags,
          &d_total = c->f_total, &d_okeys = c->f_okeys, &d_olinks = c->f_olinks, &d_ogaps = c->f_ogaps;
-  const uint64_t row_cap = std::max<uint64_t>(n_unique, 1);
-  uint64_t issue_cap = c->issue_cap_hint;
+  const bool incremental = c->cls_valid && c->cls_started && !c->x_attached && c->pair_cap == c->cls_pair_cap;
+  const uint64_t row_cap = incremental ? c->cls_row_cap : std::max<uint64_t>(n_unique, 1);
+  uint64_t issue_cap = incremental ? c->cls_issue_cap : c->issue_cap_hint;
   CU(c, d_keys[0].ensure(row_cap * 8)); CU(c, d_vals[0].ensure(row_cap * 4));
   CU(c, d_tiglen.ensure(c->tig_len.size() * 4));
   CU(c, cudaMemcpyAsync(d_tiglen.p, c->tig_len.data(), c->tig_len.size() * 4, cudaMemcpyHostToDevice, s));
@@ -1369,16 +1448,22 @@ int links_finalize(links_ctx* c, links_row** rows_out, uint64_t* n_rows_out, lin
 
   for (int attempt = 0; attempt < 2; ++attempt) {
     CU(c, d_issues.ensure(issue_cap * sizeof(IssueRec)));
-    // reset the stage-4 counters (keeps the stage-2/3 ones)
-    CU(c, cudaMemsetAsync(reinterpret_cast<char*>(c->d_ctr.p) + offsetof(Counters, ct_ok_pairs), 0,
-                          sizeof(Counters) - offsetof(Counters, ct_ok_pairs), s));
+    const bool rest_only = incremental && attempt == 0;  // pairs up to the last extract launch but one are already classified
+    unsigned long long* range = c->d_cls.as<unsigned long long>();
+    if (rest_only) {
+      CU(c, cudaMemcpyAsync(range + 1, &c->d_ctr.as<Counters>()->n_unique, 8, cudaMemcpyDeviceToDevice, s));
+    } else {
+      // reset the stage-4 counters (keeps the stage-2/3 ones)
+      CU(c, cudaMemsetAsync(reinterpret_cast<char*>(c->d_ctr.p) + offsetof(Counters, ct_ok_pairs), 0,
+                            sizeof(Counters) - offsetof(Counters, ct_ok_pairs), s));
+    }
     if (c->pair_cap && n_unique) {
       Span sp(c, F_CLASSIFY, s);
       ClassifyParams cp{c->d_dist.as<uint32_t>(), c->d_minallowed.as<int32_t>(), c->prm.n_dist, d_tiglen.as<uint32_t>(), tb,
                         d_keys[0].as<uint64_t>(), d_vals[0].as<int32_t>(), row_cap, d_issues.as<IssueRec>(), issue_cap};
-      classify_kernel<<<grid_for(c, n_unique, kCtaThreads, 8), kCtaThreads, 0, s>>>(
+      classify_kernel<<<rest_only ? c->sm_count * 4 : grid_for(c, n_unique, kCtaThreads, 8), kCtaThreads, 0, s>>>(
         pair_view(c), n_unique, table_view(c), cp,
-        int(c->prm.k), c->d_ctr.as<Counters>());
+        int(c->prm.k), c->d_ctr.as<Counters>(), rest_only ? range : nullptr);
       c->launches++;
       CU(c, cudaGetLastError());
     }
@@ -1731,6 +1816,8 @@ int links_pairs_clear(links_ctx* c)
   CU(c, cudaSetDevice(c->device));
   CU(c, cudaStreamSynchronize(c->s_copy));
   CU(c, cudaStreamSynchronize(c->s_compute));
+  CU(c, cudaStreamSynchronize(c->s_cls));
+  c->cls_valid = false;  // the set is re-filled by imports: stage 4 runs once, at finalize
   poll_snapshots(c);
   for (int i = 0; i < links_ctx::kSnaps; ++i) c->snap_live[i] = false;
   c->known_unique = 0; c->known_cand = c->cand_total;
@@ -1748,6 +1835,8 @@ int links_pairs_import(links_ctx* c, const void* dev_records, uint64_t n_records
   if (!n_records) return LINKS_OK;
   CU(c, cudaSetDevice(c->device));
   CU(c, cudaStreamWaitEvent(c->s_compute, c->ev_cleared, 0));
+  CU(c, cudaStreamSynchronize(c->s_cls));
+  c->cls_valid = false;
   int rc = ensure_pair_capacity(c, n_records, 0);
   if (rc) return rc;
   {
