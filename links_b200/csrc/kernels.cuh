@@ -613,15 +613,21 @@ __global__ void mirror_expand_kernel(const uint64_t* __restrict__ keys, uint32_t
 
 __global__ void range_advance_kernel(unsigned long long* range) { range[0] = range[1]; }
 
-struct FinalRow { uint64_t key; unsigned long long links; long long gaps; };
-__global__ void gather_rows_kernel(const uint64_t* __restrict__ keys, const int32_t* __restrict__ idx, uint32_t n,
+// same layout as links_row (include/links_gpu.h): the rows leave the device ready for the caller
+struct FinalRow { int32_t bin; uint32_t tig_a, tig_b; uint8_t rev_a, rev_b, pad_[2]; unsigned long long links; long long gaps; };
+__global__ void gather_rows_kernel(const uint64_t* __restrict__ keys, const int32_t* __restrict__ idx, uint32_t n, int tb,
                                    const unsigned long long* __restrict__ links, const unsigned long long* __restrict__ gaps,
                                    FinalRow* __restrict__ out)
 {
   const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n) return;
+  const uint64_t key = keys[i];
+  const uint64_t tmask = (1ull << tb) - 1;
+  const uint32_t B = uint32_t(key & tmask), A = uint32_t((key >> tb) & tmask), bc = uint32_t(key >> (2 * tb));
   FinalRow r;
-  r.key = keys[i]; r.links = links[idx[i]]; r.gaps = (long long)gaps[idx[i]];
+  r.bin = bc == 0 ? -1 : bc == 1 ? 10 : bc == 2 ? 500 : bc == 3 ? 5000 : 10000;  // get_distance_bin's values, ref :764-770
+  r.tig_a = A >> 1; r.rev_a = A & 1u; r.tig_b = B >> 1; r.rev_b = B & 1u; r.pad_[0] = r.pad_[1] = 0;
+  r.links = links[idx[i]]; r.gaps = (long long)gaps[idx[i]];
   out[i] = r;
 }
 

@@ -18,6 +18,8 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <mutex>
+#include <ctime>
 #include <string>
 #include <vector>
 
@@ -169,6 +171,63 @@ struct links_ctx {
 };
 
 namespace {
+
+// Result arrays handed to the caller (released with links_free_result).  A job returns the same megabyte-sized
+// arrays over and over; going back to the C library each time means fresh pages and ~1 us of page fault per 4 KB
+// (0.4 ms per job measured).  The last few released blocks are kept and reused when large enough.
+struct ResultHeader { uint64_t magic, cap; uint64_t pad_[2]; };
+constexpr uint64_t kResultMagic = 0x4c494e4b53524f57ull;
+std::mutex g_result_mu;
+ResultHeader* g_result_cache[4] = {nullptr, nullptr, nullptr, nullptr};
+
+void* result_alloc(size_t bytes)
+{
+  {
+    std::lock_guard<std::mutex> lk(g_result_mu);
+    int best = -1;
+    for (int i = 0; i < 4; ++i)
+      if (g_result_cache[i] && g_result_cache[i]->cap >= bytes && (best < 0 || g_result_cache[i]->cap < g_result_cache[best]->cap)) best = i;
+    if (best >= 0 && g_result_cache[best]->cap <= 4 * bytes + (1u << 16)) {
+      ResultHeader* h = g_result_cache[best];
+      g_result_cache[best] = nullptr;
+      return h + 1;
+    }
+  }
+  ResultHeader* h = static_cast<ResultHeader*>(malloc(sizeof(ResultHeader) + bytes));
+  if (!h) return nullptr;
+  h->magic = kResultMagic; h->cap = bytes;
+  return h + 1;
+}
+
+void result_free(void* p)
+{
+  if (!p) return;
+  ResultHeader* h = static_cast<ResultHeader*>(p) - 1;
+  if (h->magic != kResultMagic) return;  // not ours: leave it alone rather than corrupt the heap
+  {
+    std::lock_guard<std::mutex> lk(g_result_mu);
+    int slot = -1;
+    for (int i = 0; i < 4; ++i) if (!g_result_cache[i]) { slot = i; break; }
+    if (slot < 0) {  // cache full: replace the smallest block if this one is larger
+      int sm = 0;
+      for (int i = 1; i < 4; ++i) if (g_result_cache[i]->cap < g_result_cache[sm]->cap) sm = i;
+      if (g_result_cache[sm]->cap < h->cap) { ResultHeader* old = g_result_cache[sm]; g_result_cache[sm] = h; h = old; }
+    } else { g_result_cache[slot] = h; h = nullptr; }
+  }
+  if (h) { h->magic = 0; free(h); }
+}
+
+// LINKS_DEBUG_HOST=1: host wall-clock marks (us since the first mark) at the milestones of a job
+void host_mark(links_ctx* c, const char* what)
+{
+  static const bool on = getenv("LINKS_DEBUG_HOST") != nullptr;
+  if (!on) return;
+  static timespec t0{};
+  timespec t;
+  clock_gettime(CLOCK_MONOTONIC, &t);
+  if (!t0.tv_sec) t0 = t;
+  fprintf(stderr, "[links host dev%d] %10.1f us  %s\n", c ? c->device : -1, (t.tv_sec - t0.tv_sec) * 1e6 + (t.tv_nsec - t0.tv_nsec) * 1e-3, what);
+}
 
 int fail(links_ctx* c, int code, const char* fmt, ...)
 {
@@ -1291,12 +1350,14 @@ int links_reset(links_ctx* c)
 {
   if (!c) return LINKS_E_INVAL;
   CU(c, cudaSetDevice(c->device));
+  host_mark(c, "reset: enter");
   CU(c, cudaStreamSynchronize(c->s_copy));
   CU(c, cudaStreamSynchronize(c->s_aux));
   CU(c, cudaStreamSynchronize(c->s_compute));
   CU(c, cudaStreamSynchronize(c->s_route));
   CU(c, cudaStreamSynchronize(c->s_cls));
   CU(c, cudaStreamSynchronize(c->s_import));
+  host_mark(c, "reset: streams idle");
   c->table_started = false; c->table_batches_built = 0;
   poll_snapshots(c);
   for (auto* b : c->contig_batches) c->contig_pool.push_back(b);
@@ -1336,6 +1397,7 @@ int links_reset(links_ctx* c)
   CU(c, cudaEventRecord(c->ev_cleared, c->s_aux));
   c->contig_pack_pending = false;
   c->finalized = false;
+  host_mark(c, "reset: return");
   return LINKS_OK;
 }
 
@@ -1408,6 +1470,7 @@ int links_finalize(links_ctx* c, links_row** rows_out, uint64_t* n_rows_out, lin
   if (issues_out) *issues_out = nullptr;
   if (n_issues_out) *n_issues_out = 0;
   CU(c, cudaSetDevice(c->device));
+  host_mark(c, "finalize: enter");
   cudaStream_t s = c->s_compute;
   CU(c, cudaStreamSynchronize(c->s_copy));
   CU(c, cudaStreamWaitEvent(s, c->ev_cleared, 0));
@@ -1427,8 +1490,10 @@ int links_finalize(links_ctx* c, links_row** rows_out, uint64_t* n_rows_out, lin
     CU(c, cudaEventRecord(c->ev_cls_done, c->s_cls));
     CU(c, cudaStreamWaitEvent(s, c->ev_cls_done, 0));
   }
+  host_mark(c, "finalize: settled");
   // unique pair count sizes the row buffers
   CU(c, cudaStreamSynchronize(s));
+  host_mark(c, "finalize: extraction drained");
   Counters h;
   CU(c, cudaMemcpy(&h, c->d_ctr.p, sizeof h, cudaMemcpyDeviceToHost));
   const uint64_t n_unique = h.n_unique;
@@ -1473,6 +1538,7 @@ int links_finalize(links_ctx* c, links_row** rows_out, uint64_t* n_rows_out, lin
     issue_cap = h.n_issues; // rerun with an exact-size buffer
     c->issue_cap_hint = issue_cap;
   }
+  host_mark(c, "finalize: classified");
   const uint64_t n_rows_raw = h.n_rows;
   if (n_rows_raw > row_cap) return fail(c, LINKS_E_CUDA, "links_finalize: internal row overflow");
 
@@ -1517,7 +1583,7 @@ int links_finalize(links_ctx* c, links_row** rows_out, uint64_t* n_rows_out, lin
     rc = radix_sort_pairs(c, s, d_keys, d_vals, n_out32, key_bits, cur);
     if (rc) return rc;
     CU(c, c->f_final.ensure(uint64_t(n_out32) * sizeof(FinalRow)));
-    gather_rows_kernel<<<(n_out32 + 255) / 256, 256, 0, s>>>(d_keys[cur].as<uint64_t>(), d_vals[cur].as<int32_t>(), n_out32,
+    gather_rows_kernel<<<(n_out32 + 255) / 256, 256, 0, s>>>(d_keys[cur].as<uint64_t>(), d_vals[cur].as<int32_t>(), n_out32, tb,
                                                            d_olinks.as<unsigned long long>(), d_ogaps.as<unsigned long long>(),
                                                            c->f_final.as<FinalRow>());
     c->launches++;
@@ -1538,26 +1604,19 @@ int links_finalize(links_ctx* c, links_row** rows_out, uint64_t* n_rows_out, lin
     if (h.n_issues) CU(c, cudaMemcpyAsync(hi.data(), d_issues.p, h.n_issues * sizeof(IssueRec), cudaMemcpyDeviceToHost, s));
   }
   CU(c, cudaStreamSynchronize(s));
+  host_mark(c, "finalize: rows on host");
 
-  // ---- host: unpack (rows arrive in (bin, tig_a, rev_a, tig_b, rev_b) order: the packed key is monotone in it)
-  static const int32_t bin_of_code[5] = {-1, 10, 500, 5000, 10000};
+  // ---- host: the rows arrive as links_row records in (bin, tig_a, rev_a, tig_b, rev_b) order (the packed key is monotone in it)
+  static_assert(sizeof(FinalRow) == sizeof(links_row), "row record layout");
   const uint64_t n_out = n_out32;
-  links_row* rows = static_cast<links_row*>(malloc(std::max<uint64_t>(n_out, 1) * sizeof(links_row)));
+  links_row* rows = static_cast<links_row*>(result_alloc(std::max<uint64_t>(n_out, 1) * sizeof(links_row)));
   if (!rows) return fail(c, LINKS_E_NOMEM, "links_finalize: out of host memory");
-  const uint64_t tmask = (1ull << tb) - 1;
-  for (uint64_t i = 0; i < n_out; ++i) {
-    const uint64_t key = hrows[i].key;
-    const uint32_t B = uint32_t(key & tmask), A = uint32_t((key >> tb) & tmask), bc = uint32_t(key >> (2 * tb));
-    links_row r;
-    memset(&r, 0, sizeof r);
-    r.bin = bin_of_code[bc]; r.links = hrows[i].links; r.gaps = hrows[i].gaps;
-    r.tig_a = A >> 1; r.rev_a = A & 1; r.tig_b = B >> 1; r.rev_b = B & 1;
-    rows[i] = r;
-  }
+  if (n_out) memcpy(rows, hrows, n_out * sizeof(links_row));
+  host_mark(c, "finalize: rows unpacked");
   links_issue* issues = nullptr;
   if (issues_out) {
-    issues = static_cast<links_issue*>(malloc(std::max<uint64_t>(hi.size(), 1) * sizeof(links_issue)));
-    if (!issues) { free(rows); return fail(c, LINKS_E_NOMEM, "links_finalize: out of host memory"); }
+    issues = static_cast<links_issue*>(result_alloc(std::max<uint64_t>(hi.size(), 1) * sizeof(links_issue)));
+    if (!issues) { result_free(rows); return fail(c, LINKS_E_NOMEM, "links_finalize: out of host memory"); }
     static_assert(sizeof(links_issue) == sizeof(IssueRec), "issue record layout");
     if (!hi.empty()) memcpy(issues, hi.data(), hi.size() * sizeof(links_issue));
     std::sort(issues, issues + hi.size(), [](const links_issue& a, const links_issue& b) {
@@ -1580,10 +1639,11 @@ int links_finalize(links_ctx* c, links_row** rows_out, uint64_t* n_rows_out, lin
     stats->n_rows = n_out;
   }
   c->finalized = true;
+  host_mark(c, "finalize: return");
   return LINKS_OK;
 }
 
-void links_free_result(links_row* rows, links_issue* issues) { free(rows); free(issues); }
+void links_free_result(links_row* rows, links_issue* issues) { result_free(rows); result_free(issues); }
 
 int links_format_row(const links_row* r, char* dst, size_t cap)
 {
@@ -1693,7 +1753,7 @@ int links_rows_merge(links_ctx* c, const links_row* rows, uint64_t n, links_row*
   if (!c || !out || !n_out || (!rows && n)) return LINKS_E_INVAL;
   *out = nullptr; *n_out = 0;
   if (n >= (1ull << 31)) return fail(c, LINKS_E_LIMIT, "links_rows_merge: more than 2^31 rows");
-  links_row* res = static_cast<links_row*>(malloc(std::max<uint64_t>(n, 1) * sizeof(links_row)));
+  links_row* res = static_cast<links_row*>(result_alloc(std::max<uint64_t>(n, 1) * sizeof(links_row)));
   if (!res) return fail(c, LINKS_E_NOMEM, "links_rows_merge: out of host memory");
   *out = res;
   if (!n) return LINKS_OK;
