@@ -570,11 +570,20 @@ int ensure_pair_capacity(links_ctx* c, uint64_t incoming, uint64_t later)
 // ~1.8 bytes per base, src/LINKS.hpp:297-302) so that a multi-batch push rarely regrows.
 int ensure_member_capacity(links_ctx* c)
 {
-  static const bool env_off = []() { const char* e = getenv("LINKS_MEMBER_SET"); return e && e[0] == '0'; }();
-  if (env_off || c->member_off) { c->member_buckets = 0; c->member_off = true; return LINKS_OK; }
+  // LINKS_MEMBER_SET=0 / 1 forces the set off / on; unset = the measured rule below
+  static const int env_mode = []() { const char* e = getenv("LINKS_MEMBER_SET"); return !e ? -1 : e[0] == '0' ? 0 : 1; }();
+  if (env_mode == 0 || c->member_off) { c->member_buckets = 0; c->member_off = true; return LINKS_OK; }
   const uint64_t need_buckets = c->contig_positions / 2 + 1;  // 4 slots per bucket, load 0.5
   if (c->member_buckets >= need_buckets) return LINKS_OK;
   const uint64_t estimate = c->member_buckets ? need_buckets + need_buckets / 2 : std::max(need_buckets, c->bf_bytes * 9 / 32);
+  if (env_mode < 0 && !c->member_buckets) {
+    // A set lookup is one sector that replaces hash_num filter sectors for a true member -- a win when those
+    // sectors come from DRAM (filter larger than L2: 80 Mbp assembly, extract 131 -> 98 ms), a loss when the filter
+    // sits in L2 but the 9x larger set does not (20 Mbp: 14.4 -> 18.0 ms), neutral when both nearly fit (5 Mbp).
+    const bool filter_in_l2 = c->bf_bytes < (64ull << 20);
+    const bool set_near_l2 = estimate * sizeof(MemberBucket) <= (96ull << 20);
+    if (filter_in_l2 && !set_near_l2) { c->member_buckets = 0; c->member_off = true; return LINKS_OK; }
+  }
   const size_t total_b = c->dev_total_mem;  // (cudaMemGetInfo is a slow driver call; the total does not change)
   if (estimate * sizeof(MemberBucket) > total_b / 8 && estimate * sizeof(MemberBucket) > c->d_members.cap) {
     c->member_buckets = 0; c->member_off = true;  // large assemblies: every k-mer takes the probe path
