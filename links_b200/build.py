@@ -17,6 +17,7 @@ ROOT = os.path.dirname(HERE)
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "liblinks_gpu.so")
 HOST_BIN = os.path.join(HERE, "bin", "LINKS_CPP")
+LAYOUT_BIN = os.path.join(HERE, "bin", "LINKS_layout")  # the Perl stage (bin/LINKS.pl) in C++; also installed as bin/LINKS.pl
 
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a",
@@ -74,9 +75,23 @@ def build_host(force: bool = False) -> str | None:
     return HOST_BIN
 
 
+def build_layout(force: bool = False) -> str:
+    """CPU only (no CUDA): usable on any machine, also by the `-m "not gpu"` tests."""
+    src = os.path.join(CSRC, "host", "links_layout_main.cpp")
+    srcs = [src, os.path.join(CSRC, "host", "links_layout.hpp")]
+    if force or not _newer(LAYOUT_BIN, srcs):
+        os.makedirs(os.path.dirname(LAYOUT_BIN), exist_ok=True)
+        subprocess.run(["g++", "-std=c++17", "-O2", "-Wall", src, "-o", LAYOUT_BIN], check=True)
+    alias = os.path.join(os.path.dirname(LAYOUT_BIN), "LINKS.pl")  # what the unmodified LINKS-make calls (bin/LINKS-make:124)
+    if force or not _newer(alias, [LAYOUT_BIN]):
+        shutil.copy2(LAYOUT_BIN, alias)
+    return LAYOUT_BIN
+
+
 def build_all(force: bool = False, verbose: bool = False) -> None:
     build_lib(force, verbose)
     build_host(force)
+    build_layout(force)
 
 
 if __name__ == "__main__":

@@ -7,6 +7,7 @@ import os
 import numpy as np
 import pytest
 
+from .conftest import GOLDEN as GOLDEN_DIR
 from .conftest import GoldenCase, sha256, sort_issue_records, sort_lines
 
 pytestmark = pytest.mark.gpu
@@ -450,3 +451,17 @@ def test_links_cpp_binary_writes_reference_files(gpu_lib, tmp_path, name):
     assert r.returncode == 0, r.stderr
     assert sort_lines(open(base + "2.tigpair_checkpoint.tsv", "rb").read()) == c.expected_tsv()
     assert not os.path.exists(base + "2.bloom")
+    # the whole pipeline as LINKS-make chains it (bin/LINKS-make:121-125): LINKS_CPP on the GPU, then the layout stage
+    # (our bin/LINKS.pl = links_layout) -> scaffolds identical to the reference's
+    lay = os.path.join(GOLDEN_DIR, name, "layout")
+    if os.path.exists(os.path.join(lay, "layout.json")):
+        import hashlib
+        import json
+        meta = json.load(open(os.path.join(lay, "layout.json")))
+        build.build_layout()
+        open(str(tmp_path / "empty.fof"), "w").close()
+        r = subprocess.run([os.path.join(os.path.dirname(build.LAYOUT_BIN), "LINKS.pl"), "-f", cpath, "-s", str(tmp_path / "empty.fof"), "-b", base,
+                            "-l", str(meta["opts"]["l"]), "-a", str(meta["opts"]["a"]), "-z", str(meta["opts"]["z"])], capture_output=True, text=True)
+        assert r.returncode == 0, r.stderr
+        assert open(base + ".scaffolds", "rb").read() == open(os.path.join(lay, "expected.scaffolds"), "rb").read()
+        assert hashlib.sha256(open(base + ".scaffolds.fa", "rb").read()).hexdigest() == meta["scaffolds_fa_sha256"]

@@ -1,0 +1,87 @@
+"""The layout stage (links_b200/csrc/host/links_layout.hpp = the reference's bin/LINKS.pl in C++) against the
+reference's own outputs: the installation test's shipped files, and the unmodified Perl run on the other golden
+cases (tools/make_layout_golden.py).  CPU only."""
+from __future__ import annotations
+
+import gzip
+import hashlib
+import json
+import os
+import shutil
+import subprocess
+
+import pytest
+
+from .conftest import GOLDEN, ConfigCase
+
+CASES = sorted(d for d in os.listdir(GOLDEN) if os.path.exists(os.path.join(GOLDEN, d, "layout", "layout.json")))
+
+
+@pytest.fixture(scope="module")
+def layout_bin():
+    from links_b200 import build
+    return build.build_layout()
+
+
+def _below_label(gv: bytes) -> bytes:
+    return b"\n".join(gv.split(b"\n")[2:])
+
+
+def _run(layout_bin, wd, contigs_name, opts, exe_name=None):
+    exe = layout_bin
+    if exe_name:  # called under another name, as LINKS-make calls "LINKS.pl"
+        exe = os.path.join(wd, exe_name)
+        shutil.copy2(layout_bin, exe)
+    open(os.path.join(wd, "empty.fof"), "w").close()
+    subprocess.run([exe, "-f", contigs_name, "-s", "empty.fof", "-b", "out", "-l", str(opts["l"]), "-a", str(opts["a"]), "-z", str(opts["z"]),
+                    "-e", "0.1", "-p", "0.001", "-v", "0"], cwd=wd, check=True, stdout=subprocess.DEVNULL)
+    rd = lambda s: open(os.path.join(wd, "out." + s), "rb").read()  # noqa: E731
+    return rd("scaffolds"), rd("scaffolds.fa"), rd("gv"), rd("assembly_correspondence.tsv")
+
+
+@pytest.mark.parametrize("case", CASES)
+def test_layout_matches_reference_perl(layout_bin, tmp_path, case):
+    d = os.path.join(GOLDEN, case, "layout")
+    meta = json.load(open(os.path.join(d, "layout.json")))
+    wd = str(tmp_path)
+    if case.startswith("cfg_"):
+        from links_b200.seqio import write_fasta
+        contigs, _reads = ConfigCase(case[4:]).inputs()
+        contigs.names = [str(i + 1) for i in range(contigs.n)]
+        write_fasta(os.path.join(wd, "contigs.fa"), contigs)
+        name = "contigs.fa"
+    elif case == "c1":  # read through the gunzip pipe, as LINKS.pl does for *.gz (bin/LINKS.pl:1253)
+        shutil.copy(os.path.join(GOLDEN, case, "contigs.fa.gz"), os.path.join(wd, "contigs.fa.gz"))
+        name = "contigs.fa.gz"
+    else:
+        open(os.path.join(wd, "contigs.fa"), "wb").write(gzip.open(os.path.join(GOLDEN, case, "contigs.fa.gz"), "rb").read())
+        name = "contigs.fa"
+    tsv = os.path.join(d, "input.tigpair_checkpoint.tsv")  # c1: the rows in the order the reference shipped them
+    if not os.path.exists(tsv):
+        tsv = os.path.join(GOLDEN, case, "expected.tigpair_checkpoint.tsv")
+    shutil.copy(tsv, os.path.join(wd, "out.tigpair_checkpoint.tsv"))
+    sc, fa, gv, corr = _run(layout_bin, wd, name, meta["opts"], exe_name="LINKS.pl" if case == "c1" else None)
+    assert sc == open(os.path.join(d, "expected.scaffolds"), "rb").read()
+    assert hashlib.sha256(fa).hexdigest() == meta["scaffolds_fa_sha256"] and len(fa) == meta["scaffolds_fa_bytes"]
+    assert _below_label(gv) == open(os.path.join(d, "expected.gv_body"), "rb").read()
+    assert corr.split(b"\n", 1)[1] == open(os.path.join(d, "expected.assembly_correspondence_body.tsv"), "rb").read()
+    assert sc.count(b"\n") == meta["n_scaffolds"]
+
+
+def test_layout_option_and_input_quirks(layout_bin, tmp_path):
+    """`-l 0`, `-a 0`, `-z 0` leave the defaults (Perl: `$min_links = $opt_l if($opt_l)`, bin/LINKS.pl:52-55); a missing
+    checkpoint is not an error (:121-124); rows naming an unknown or empty contig id are skipped (:1166-1168)."""
+    wd = str(tmp_path)
+    open(os.path.join(wd, "c.fa"), "w").write(">a\n" + "ACGT" * 200 + "\n>b\n" + "TTGCA" * 200 + "\n>c\nACG\n")
+    open(os.path.join(wd, "empty.fof"), "w").close()
+    r = subprocess.run([layout_bin, "-f", "c.fa", "-b", "out"], cwd=wd, capture_output=True, text=True)
+    assert r.returncode == 0 and "No checkpoint provided" in r.stdout and not os.path.exists(os.path.join(wd, "out.scaffolds"))
+    rows = ["500\tf1\tf2\t7\t700", "500\tr2\tr1\t7\t700", "500\tf1\tf\t9\t90", "500\tf1\tf3\t50\t50", "500\tf1\tf99\t50\t50"]
+    open(os.path.join(wd, "out.tigpair_checkpoint.tsv"), "w").write("\n".join(rows) + "\n")
+    subprocess.run([layout_bin, "-f", "c.fa", "-s", "empty.fof", "-b", "out", "-l", "0", "-a", "0", "-z", "0"], cwd=wd, check=True,
+                   stdout=subprocess.DEVNULL)
+    sc = open(os.path.join(wd, "out.scaffolds")).read().splitlines()
+    # b (1000 bp) seeds first, a (800 bp) joins on its left with 7 >= 5 links, mean gap 100; c (3 bp < 500) stays alone
+    assert sc == ["scaffold1,1800,f1z800k7a0m100_f2Z1000", "scaffold2,3,f3Z3"]
+    fa = open(os.path.join(wd, "out.scaffolds.fa")).read().splitlines()
+    assert fa[1] == "ACGT" * 200 + "N" * 100 + "TTGCA" * 200
