@@ -106,6 +106,21 @@ def make_reads(genome: np.ndarray, coverage: float, mean_len: int, seed: int = 2
     return SeqSet(seq, off, [f"r{i}" for i in range(len(lens))])
 
 
+def unique_lengths(contigs: SeqSet) -> SeqSet:
+    """Trim bases off the end of later contigs until no two contigs have the same length.  The reference's layout stage
+    seeds scaffolds longest contig first and breaks ties in Perl hash order (bin/LINKS.pl:673), which changes from run to
+    run, so an input meant to pin its output must not contain ties."""
+    seen: set[int] = set()
+    recs = []
+    for i in range(contigs.n):
+        r = contigs.record(i)
+        while len(r) in seen and len(r) > 1:
+            r = r[:-1]
+        seen.add(len(r))
+        recs.append(r)
+    return SeqSet.from_records(recs, list(contigs.names))
+
+
 def candidate_pairs(read_off: np.ndarray, k: int, dist: list[int], step: list[int], offset: int = 0) -> int:
     """Analytic count of (A,B) k-mer pairs visited for N-free reads:
     sum_reads sum_d floor((len-k+1-o-d)/t)  (reference src/LINKS.hpp:525-543)."""

@@ -44,19 +44,30 @@ def test_layout_matches_reference_perl(layout_bin, tmp_path, case):
     d = os.path.join(GOLDEN, case, "layout")
     meta = json.load(open(os.path.join(d, "layout.json")))
     wd = str(tmp_path)
+    d_in = d
     if case.startswith("cfg_"):
         from links_b200.seqio import write_fasta
         contigs, _reads = ConfigCase(case[4:]).inputs()
         contigs.names = [str(i + 1) for i in range(contigs.n)]
         write_fasta(os.path.join(wd, "contigs.fa"), contigs)
         name = "contigs.fa"
+    elif "stress" in meta:  # seeded synthetic contigs of distinct lengths (tools/make_layout_golden.py: stress_contigs)
+        from links_b200 import synth
+        from links_b200.seqio import write_fasta
+        st = meta["stress"]
+        contigs = synth.make_contigs(synth.make_genome(st["genome"], seed=st["seeds"][0]), st["contigs"], seed=st["seeds"][1])
+        contigs.names = [str(i + 1) for i in range(contigs.n)]
+        write_fasta(os.path.join(wd, "contigs.fa"), synth.unique_lengths(contigs))
+        name = "contigs.fa"
+        if "input_from" in meta:
+            d_in = os.path.join(GOLDEN, meta["input_from"], "layout")
     elif case == "c1":  # read through the gunzip pipe, as LINKS.pl does for *.gz (bin/LINKS.pl:1253)
         shutil.copy(os.path.join(GOLDEN, case, "contigs.fa.gz"), os.path.join(wd, "contigs.fa.gz"))
         name = "contigs.fa.gz"
     else:
         open(os.path.join(wd, "contigs.fa"), "wb").write(gzip.open(os.path.join(GOLDEN, case, "contigs.fa.gz"), "rb").read())
         name = "contigs.fa"
-    tsv = os.path.join(d, "input.tigpair_checkpoint.tsv")  # c1: the rows in the order the reference shipped them
+    tsv = os.path.join(d_in, "input.tigpair_checkpoint.tsv")  # c1: the rows in the order the reference shipped them
     if not os.path.exists(tsv):
         tsv = os.path.join(GOLDEN, case, "expected.tigpair_checkpoint.tsv")
     shutil.copy(tsv, os.path.join(wd, "out.tigpair_checkpoint.tsv"))

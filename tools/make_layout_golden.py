@@ -8,8 +8,11 @@
  cfg_<name>    the unmodified bin/LINKS.pl run on the reference's tigpair_checkpoint.tsv of the BASELINE-config
                cases (tests/golden/cfg_*/expected.tigpair_checkpoint.tsv) with the synthetic contigs, options
                -l 5 -a 0.3 -z 500.  Perl's hash order is random per process and decides ties, so LINKS.pl runs
-               under three different PERL_HASH_SEEDs; a case whose outputs differ between them is reported and
+               under five different PERL_HASH_SEEDs; a case whose outputs differ between them is reported and
                NOT stored (there is no single right answer to pin).
+ lay_stress_*  300 synthetic contigs of distinct lengths (links_b200.synth, seeded; ties would make the Perl's own
+               output vary), links from the unmodified LINKS_CPP at three distances, laid out under three -l/-a/-z
+               settings: tens of scaffolds, chains extended on both sides, reverse-strand joins, overlaps (m < 0).
 Stored under tests/golden/<case>/layout/.
 """
 from __future__ import annotations
@@ -27,6 +30,8 @@ sys.path.insert(0, ROOT)
 sys.path.insert(0, os.path.join(ROOT, "tools"))
 REF = "/root/reference"
 GOLD = os.path.join(ROOT, "tests", "golden")
+# hex digits; picked so that `keys` of a small hash really comes out in different orders (1 / 12345 / 987654321 do not)
+SEEDS = ("1", "777", "424242", "deadbeef", "0badc0de")
 
 
 def below_label(gv: bytes) -> bytes:
@@ -78,14 +83,14 @@ def main() -> None:
         with tempfile.TemporaryDirectory() as wd:
             fa = os.path.join(wd, "contigs.fa")
             open(fa, "wb").write(fasta_bytes(contigs))
-            runs = [run_perl(fa, tsv, opts, seed) for seed in ("1", "12345", "987654321")]
+            runs = [run_perl(fa, tsv, opts, seed) for seed in SEEDS]
         same = all(r["scaffolds"] == runs[0]["scaffolds"] and r["fa"] == runs[0]["fa"] and r["corr"] == runs[0]["corr"]
                    and below_label(r["gv"]) == below_label(runs[0]["gv"]) for r in runs)
         if not same:
             print(f"cfg_{name}: LINKS.pl's own output depends on its hash seed (ties) -- not stored")
             continue
         store("cfg_" + name, runs[0], "perl /root/reference/bin/LINKS.pl (unmodified) on expected.tigpair_checkpoint.tsv, identical "
-              "under three PERL_HASH_SEEDs, tools/make_layout_golden.py", opts)
+              "under five PERL_HASH_SEEDs, tools/make_layout_golden.py", opts)
     # the adversarial cases (Ns, lower case, tandem repeats, short contigs) with non-default -l -a -z
     import gzip
     for name in ("adv_k40", "adv_ns_lower", "adv_offset_k20", "adv_tandem"):
@@ -94,14 +99,61 @@ def main() -> None:
         with tempfile.TemporaryDirectory() as wd:
             fa = os.path.join(wd, "contigs.fa")
             open(fa, "wb").write(gzip.open(os.path.join(GOLD, name, "contigs.fa.gz"), "rb").read())
-            runs = [run_perl(fa, tsv, opts, seed) for seed in ("1", "12345", "987654321")]
+            runs = [run_perl(fa, tsv, opts, seed) for seed in SEEDS]
         same = all(r["scaffolds"] == runs[0]["scaffolds"] and r["fa"] == runs[0]["fa"] and r["corr"] == runs[0]["corr"]
                    and below_label(r["gv"]) == below_label(runs[0]["gv"]) for r in runs)
         if not same:
             print(f"{name}: LINKS.pl's own output depends on its hash seed (ties) -- not stored")
             continue
-        store(name, runs[0], "perl /root/reference/bin/LINKS.pl (unmodified), -l 2 -a 0.5 -z 200, identical under three PERL_HASH_SEEDs, "
+        store(name, runs[0], "perl /root/reference/bin/LINKS.pl (unmodified), -l 2 -a 0.5 -z 200, identical under five PERL_HASH_SEEDs, "
               "tools/make_layout_golden.py", opts)
+    stress()
+
+
+STRESS = {"genome": 3_000_000, "contigs": 300, "seeds": [21, 23, 22], "coverage": 8.0, "read_len": 15_000,
+          "links_opts": {"k": 15, "d": [2000, 5000, 10000], "t": [10, 10, 10], "o": 0, "e": 0.1, "p": 0.001}}
+STRESS_LAYOUTS = {"lay_stress_default": {"l": 5, "a": 0.3, "z": 500}, "lay_stress_loose": {"l": 2, "a": 0.7, "z": 200},
+                  "lay_stress_strict": {"l": 10, "a": 0.1, "z": 1000}}
+
+
+def stress_contigs():
+    from links_b200 import synth
+    genome = synth.make_genome(STRESS["genome"], seed=STRESS["seeds"][0])
+    contigs = synth.make_contigs(genome, STRESS["contigs"], seed=STRESS["seeds"][1])
+    contigs.names = [str(i + 1) for i in range(contigs.n)]
+    return genome, synth.unique_lengths(contigs)
+
+
+def stress() -> None:
+    from links_b200 import synth
+    from make_golden import fasta_bytes, run_ref
+    genome, contigs = stress_contigs()
+    reads = synth.make_reads(genome, STRESS["coverage"], STRESS["read_len"], seed=STRESS["seeds"][2])
+    reads.names = [f"r{i}" for i in range(reads.n)]
+    with tempfile.TemporaryDirectory() as wd:
+        fa = os.path.join(wd, "contigs.fa")
+        open(fa, "wb").write(fasta_bytes(contigs))
+        open(os.path.join(wd, "reads.fa"), "wb").write(fasta_bytes(reads))
+        tsv = run_ref(wd, fa, [os.path.join(wd, "reads.fa")], STRESS["links_opts"])["tsv"]
+        first = None
+        for case, opts in STRESS_LAYOUTS.items():
+            runs = [run_perl(fa, tsv, opts, seed) for seed in SEEDS]
+            same = all(r["scaffolds"] == runs[0]["scaffolds"] and r["fa"] == runs[0]["fa"] and r["corr"] == runs[0]["corr"]
+                       and below_label(r["gv"]) == below_label(runs[0]["gv"]) for r in runs)
+            if not same:
+                print(f"{case}: LINKS.pl's own output depends on its hash seed (ties) -- not stored")
+                continue
+            store(case, runs[0], "perl /root/reference/bin/LINKS.pl (unmodified) on the unmodified LINKS_CPP's checkpoint for 300 "
+                  "synthetic contigs of distinct lengths, identical under five PERL_HASH_SEEDs, tools/make_layout_golden.py", opts)
+            d = os.path.join(GOLD, case, "layout")
+            meta = json.load(open(os.path.join(d, "layout.json")))
+            meta["stress"] = STRESS
+            if first is None:
+                first = case
+                open(os.path.join(d, "input.tigpair_checkpoint.tsv"), "wb").write(tsv)
+            else:
+                meta["input_from"] = first  # one copy of the 85 KB checkpoint
+            json.dump(meta, open(os.path.join(d, "layout.json"), "w"), indent=1, sort_keys=True)
 
 
 if __name__ == "__main__":
