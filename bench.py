@@ -42,6 +42,10 @@ UNIT = "pairs/s"
 WORKLOADS = {
     # BASELINE.json configs[1]: synthetic 5 Mbp bacterial genome, 500 contigs, 50x ONT-like 10 kb reads, -k 15 -d 4000 -t 2
     "c2_bacterial_5mbp": "c2_bacterial_5mbp",
+    # configs[2]: 100 Mbp draft, 30x 15 kb reads, -d 1000,2500,5000 -t 20,10,5 (not the headline line; run with --workload)
+    "c3_celegans_100mbp": "c3_celegans_100mbp",
+    # configs[4], densest point of the sweep: 100 Mbp, -d 10000 -t 1 (5x reads so that it stays a bench, not a soak)
+    "c5_step_sweep_100mbp": "c5_step_sweep_100mbp",
     "tiny": "tiny",
 }
 
@@ -140,6 +144,25 @@ def rows_digest(rows: np.ndarray) -> str:
     return hashlib.sha256(keep.tobytes()).hexdigest()[:16]
 
 
+def job_properties(rows, issues, stats, reads, k, d, t) -> dict:
+    """Checks that hold at any size (tests/test_gpu_parity.py::test_full_size_properties has the same list)."""
+    from links_b200 import synth
+
+    def table(mirrored: bool):
+        ta, ra, tb, rb = (rows[n].astype(np.int64) for n in ("tig_a", "rev_a", "tig_b", "rev_b"))
+        if mirrored:
+            ta, ra, tb, rb = tb, 1 - rb, ta, 1 - ra
+        m = np.stack([rows["bin"].astype(np.int64), ta, ra, tb, rb, rows["links"].astype(np.int64), rows["gaps"].astype(np.int64)], axis=1)
+        return m[np.lexsort(m.T[::-1])]
+    classes = sum(stats[n] for n in ("ct_ok_pairs", "ct_problem_pairs", "ct_ok_contig", "ct_iz_issues", "ct_illogical", "ct_gate_fail"))
+    closed = synth.candidate_pairs(reads.off, k, list(d), list(t))  # exact for reads without an invalid base (0.1 % have an N)
+    return {"candidates_within_0.1pct_below_closed_form": closed - closed // 1000 <= stats["n_candidates"] <= closed,
+            "classes_sum_to_unique_pairs": classes == stats["n_unique_pairs"],
+            "issue_records_equal_counter": len(issues) == stats["ct_iz_issues"],
+            "links_sum_twice_ok_pairs": int(rows["links"].sum()) == 2 * stats["ct_ok_pairs"],
+            "rows_closed_under_mirror": bool(len(rows) % 2 == 0 and np.array_equal(table(False), table(True)))}
+
+
 # ---------------------------------------------------------------------------------------------- reference arm
 
 def reference_sample(contigs, reads, k, d, t, target_cand: int):
@@ -233,6 +256,7 @@ def main_ours(args, rank: int, world: int, local_rank: int):
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
     lib = _abi.load()
+    from links_b200.synth import CONFIGS as synth_configs
 
     contigs, reads, k, d, t = load_workload(args.workload, args.scale, seed_shift=rank)
     file_bytes = int(contigs.off[-1]) + contigs.n * (2 + len(str(contigs.n)))  # what the FASTA would weigh on disk
@@ -388,7 +412,7 @@ def main_ours(args, rank: int, world: int, local_rank: int):
             "metric": METRIC, "value": cand_total / (ms_res * 1e-3), "unit": UNIT, "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": ms_res, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": "u64", "data": "synthetic",
-            "config": {"workload": args.workload, "scale": args.scale, "k": k, "d": d, "t": t, "genome_bp": int(5_000_000 * args.scale),
+            "config": {"workload": args.workload, "scale": args.scale, "k": k, "d": d, "t": t, "genome_bp": int(synth_configs[args.workload][0] * args.scale),
                        "contigs": contigs.n, "reads_per_gpu": reads.n, "read_bases_per_gpu": int(reads.off[-1]),
                        "candidate_pairs_per_gpu": cand, "survivors": stats["n_survivors"], "unique_pairs": stats["n_unique_pairs"],
                        "bf_probes": stats["n_bf_probes"], "rows": n_rows, "rows_digest": digest_res,
@@ -415,6 +439,8 @@ def main_ours(args, rank: int, world: int, local_rank: int):
             "kernel_ms_per_step": {kk: vv / args.steps for kk, vv in tm_res.items() if kk.startswith("ms_")},
             "kernel_ms_per_step_e2e": {kk: vv / args.steps for kk, vv in tm_e2e.items() if kk.startswith("ms_")},
         }
+        if args.properties:
+            out["config"]["properties"] = job_properties(state["rows"], state["issues"], stats, reads, k, d, t) if world == 1 else "N=1 only"
         if world == 1 and not args.no_cpu_baseline:
             r = cpu_reference(contigs, reads, k, d, t, args.ref_candidates, runs=1, warm=0)
             if r is not None:
@@ -500,6 +526,7 @@ def main():
     ap.add_argument("--scale", type=float, default=1.0)
     ap.add_argument("--ref-candidates", type=int, default=4_000_000, help="size of the bounded CPU sample (candidate pairs)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--properties", action="store_true", help="size-independent checks of the last job's result (counts balance, mirror closure)")
     ap.add_argument("--check-sharding", action="store_true", help="parity of the N-rank path against one GPU (same reads split over ranks)")
     args = ap.parse_args()
     rank, world, local_rank = env_int("RANK", 0), env_int("WORLD_SIZE", 1), env_int("LOCAL_RANK", 0)

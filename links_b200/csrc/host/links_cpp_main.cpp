@@ -9,6 +9,7 @@
 // IO and formatting.  There is no CPU fallback: without a CUDA device links_create fails and the
 // program exits non-zero.
 #include "../../../include/links_gpu.h"
+#include "fasta_ingest.hpp"
 #include "seq_stream.hpp"
 
 #include <chrono>
@@ -20,6 +21,7 @@
 #include <sstream>
 #include <string>
 #include <sys/stat.h>
+#include <thread>
 #include <vector>
 
 namespace {
@@ -58,7 +60,7 @@ void usage()
                "  -d  distance between k-mer pairs, comma separated (default -d 4000)\n"
                "  -k  k-mer value (default -k 15)\n"
                "  -t  step of sliding window when extracting k-mer pairs, comma separated (default -t 2)\n"
-               "  -j  threads (accepted for compatibility; the GPU path does not use CPU workers)\n"
+               "  -j  threads: lower bound for the host's FASTA ingest threads (LINKS_HOST_THREADS overrides; no CPU compute workers)\n"
                "  -o  offset position for extracting k-mer pairs (default -o 0)\n"
                "  -e  error (%) allowed on -d distance, e.g. -e 0.1 == distance +/- 10% (default -e 0.1)\n"
                "  -l  minimum number of links to compute scaffold (default -l 5; used by LINKS.pl and the base name)\n"
@@ -244,13 +246,45 @@ int main(int argc, char** argv)
     if (rc != LINKS_OK) die(nullptr, "links_create", rc);
   }
 
-  // one pinned staging buffer shared by the contig and read streams
+  // two pinned staging buffers shared by the contig and read streams: while one is on its way to the device
+  // the ingest threads fill the other.  No larger than the largest input needs (pinning memory is not free).
   size_t stage_mb = 256;
   if (const char* e = getenv("LINKS_STAGE_MB")) stage_mb = std::max<size_t>(size_t(atoll(e)), 1);
+  size_t stage_cap = stage_mb << 20;
+  {
+    uint64_t need = 0;
+    bool known = true;
+    std::vector<std::string> inputs = o.read_files;
+    inputs.push_back(o.assembly_file);
+    for (const std::string& p : inputs) {
+      struct stat st;
+      if (stat(p.c_str(), &st) != 0 || !S_ISREG(st.st_mode)) { known = false; break; }
+      for (const char* suf : {".gz", ".bz2", ".xz", ".zst", ".zip", ".lrz", ".7z"})
+        if (links_host::ends_with(p, suf)) known = false;
+      need = std::max<uint64_t>(need, uint64_t(st.st_size));
+    }
+    if (known) stage_cap = std::min<size_t>(stage_cap, size_t(((need + 1) + (1u << 20) - 1) >> 20 << 20));
+  }
+  unsigned host_threads = std::max(o.thread, std::min(std::thread::hardware_concurrency(), 16u));
+  if (const char* e = getenv("LINKS_HOST_THREADS")) host_threads = unsigned(std::max(atoi(e), 1));
+  char* stage[2] = {static_cast<char*>(links_host_alloc(stage_cap)), static_cast<char*>(links_host_alloc(stage_cap))};
+  if (!stage[0] || !stage[1]) { std::cerr << "LINKS_CPP: cannot allocate 2 x " << (stage_cap >> 20) << " MB of pinned host memory\n"; return 1; }
   links_host::SeqBatch batch;
-  batch.cap = stage_mb << 20;
-  batch.seq = static_cast<char*>(links_host_alloc(batch.cap));
-  if (!batch.seq) { std::cerr << "LINKS_CPP: cannot allocate " << stage_mb << " MB of pinned host memory\n"; return 1; }
+  batch.cap = stage_cap;
+  batch.seq = stage[0];
+  // One input file -> batches for push(seq, off, n, first_ordinal); returns the records read.  Plain FASTA goes
+  // through the multi-threaded reader; FASTQ, compressed inputs and pipes through the serial
+  // one, exactly as before.  A batch never spans two files.
+  auto ingest = [&](const std::string& path, size_t max_records, uint64_t first_ordinal,
+                    const std::function<void(const char*, const uint64_t*, size_t, uint64_t)>& push) -> uint64_t {
+    if (host_threads > 1) {
+      links_host::ParallelFastaIngest par(path, host_threads);
+      if (par.usable()) return par.run(stage, stage_cap, max_records, first_ordinal, push);
+    }
+    batch.clear(first_ordinal);
+    return links_host::stream_file(path, batch, max_records, true,
+                                   [&](links_host::SeqBatch& b) { push(b.seq, b.off.data(), b.n(), b.first_ordinal); });
+  };
 
   // ---- stage 1: init_bloom_filter (reference src/LINKS.hpp:284-352)
   uint64_t bf_bytes = 0;
@@ -273,10 +307,9 @@ int main(int argc, char** argv)
     }
     // every record of the assembly, no -z filter (:318-324); the packed contigs stay on the
     // device for the k-mer table of stage 3, so the file is read once
-    batch.clear(0);
     try {
-      n_contigs = links_host::stream_file(o.assembly_file, batch, size_t(1) << 22, true, [&](links_host::SeqBatch& b) {
-        LK(ctx, links_contigs_push(ctx, b.seq, b.off.data(), uint32_t(b.n()), uint32_t(b.first_ordinal + 1)));
+      n_contigs = ingest(o.assembly_file, size_t(1) << 22, 0, [&](const char* seq, const uint64_t* off, size_t n, uint64_t first) {
+        LK(ctx, links_contigs_push(ctx, seq, off, uint32_t(n), uint32_t(first + 1)));
       });
     } catch (const std::exception& e) { std::cerr << "LINKS_CPP: " << e.what() << "\n"; return 1; }
     if (o.bf_file.empty()) {
@@ -298,15 +331,13 @@ int main(int argc, char** argv)
   {
     Stage st("STAGE: Reading sequence reads");
     uint64_t n_reads = 0;
-    batch.clear(0);
     try {
       for (const std::string& path : o.read_files) {
-        n_reads += links_host::stream_file(path, batch, size_t(1) << 24, false, [&](links_host::SeqBatch& b) {
-          LK(ctx, links_reads_push(ctx, b.seq, b.off.data(), uint32_t(b.n()), b.first_ordinal));
-          if (o.verbose) std::cout << "Processed " << b.first_ordinal + b.n() << " reads\n";
+        n_reads += ingest(path, size_t(1) << 24, n_reads, [&](const char* seq, const uint64_t* off, size_t n, uint64_t first) {
+          LK(ctx, links_reads_push(ctx, seq, off, uint32_t(n), first));
+          if (o.verbose) std::cout << "Processed " << first + n << " reads\n";
         });
       }
-      if (batch.n()) LK(ctx, links_reads_push(ctx, batch.seq, batch.off.data(), uint32_t(batch.n()), batch.first_ordinal));
     } catch (const std::exception& e) { std::cerr << "LINKS_CPP: " << e.what() << "\n"; return 1; }
     LK(ctx, links_sync(ctx));
     std::cout << "Reads processed: " << n_reads << "\n";
@@ -357,7 +388,8 @@ int main(int argc, char** argv)
     st.done("Pair contig stage completed in: ");
   }
 
-  links_host_free(batch.seq);
+  links_host_free(stage[0]);
+  links_host_free(stage[1]);
   links_destroy(ctx);
   return 0;
 }

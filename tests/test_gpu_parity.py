@@ -423,8 +423,9 @@ def test_peer_memory_exchange_equals_single_context(gpu_lib, name, n_ranks, inbo
         assert sum(out[r][job]["stats"]["n_candidates"] for r in range(n_ranks)) == stats1["n_candidates"]
 
 
-@pytest.mark.parametrize("name", ["c1", "adv_offset_k20", "adv_ns_lower"])
-def test_links_cpp_binary_writes_reference_files(gpu_lib, tmp_path, name):
+@pytest.mark.parametrize("name,host_threads", [("c1", None), ("adv_offset_k20", None), ("adv_ns_lower", None), ("adv_ns_lower", "1"),
+                                               ("adv_tandem", "5")])
+def test_links_cpp_binary_writes_reference_files(gpu_lib, tmp_path, name, host_threads):
     """The C++ host LINKS_CPP, run as the reference binary is run (bin/LINKS-make:121-122): same
     options in, byte-identical .bloom, and .tigpair_checkpoint.tsv / .pairing_issues equal to the
     unmodified reference's after the sort the reference's CI applies."""
@@ -438,6 +439,8 @@ def test_links_cpp_binary_writes_reference_files(gpu_lib, tmp_path, name):
     env = dict(os.environ, LINKS_STAGE_MB="2")  # small staging buffer: several pushes per file
     if name == "c1":
         env["LINKS_STAGE_MB"] = "8"  # its single 1 Mbp read must fit
+    if host_threads:  # "1": the serial reader (seq_stream.hpp); default: the multi-threaded FASTA ingest (fasta_ingest.hpp)
+        env["LINKS_HOST_THREADS"] = host_threads
     r = subprocess.run(cmd, capture_output=True, text=True, env=env)
     assert r.returncode == 0, r.stderr
     for banner in ("STAGE: Bloom filter construction/read", "STAGE: Reading sequence reads", "STAGE: Reading contigs",
@@ -465,3 +468,76 @@ def test_links_cpp_binary_writes_reference_files(gpu_lib, tmp_path, name):
         assert r.returncode == 0, r.stderr
         assert open(base + ".scaffolds", "rb").read() == open(os.path.join(lay, "expected.scaffolds"), "rb").read()
         assert hashlib.sha256(open(base + ".scaffolds.fa", "rb").read()).hexdigest() == meta["scaffolds_fa_sha256"]
+
+
+def _rows_table(rows, mirrored=False):
+    """Rows as a lexicographically sorted int64 table; mirrored: every row replaced by its reverse-strand twin
+    (B', A') -- the reference stores both under the same counts (src/LINKS.hpp:699-762)."""
+    ta, ra, tb, rb = (rows[n].astype(np.int64) for n in ("tig_a", "rev_a", "tig_b", "rev_b"))
+    if mirrored:
+        ta, ra, tb, rb = tb, 1 - rb, ta, 1 - ra
+    m = np.stack([rows["bin"].astype(np.int64), ta, ra, tb, rb, rows["links"].astype(np.int64), rows["gaps"].astype(np.int64)], axis=1)
+    return m[np.lexsort(m.T[::-1])]
+
+
+def _check_job_properties(rows, issues, stats, reads, k, d, t):
+    from links_b200 import synth
+    # every (A,B) position the reference visits is counted once; an invalid base removes the k-mers over it
+    closed_form = synth.candidate_pairs(reads.off, k, list(d), list(t))
+    assert closed_form - closed_form // 1000 <= stats["n_candidates"] <= closed_form  # equal but for the 0.1 % of reads with an N
+    assert stats["n_unique_pairs"] <= stats["n_survivors"] <= stats["n_candidates"]
+    # each distinct pair lands in exactly one class of pair_contigs (src/LINKS.hpp:824-968)
+    assert (stats["ct_ok_pairs"] + stats["ct_problem_pairs"] + stats["ct_ok_contig"] + stats["ct_iz_issues"]
+            + stats["ct_illogical"] + stats["ct_gate_fail"]) == stats["n_unique_pairs"]
+    assert len(issues) == stats["ct_iz_issues"]
+    # every accepted pair is added to [A][B] and to its mirror: the link column sums to twice the accepted pairs
+    assert int(rows["links"].sum()) == 2 * stats["ct_ok_pairs"]
+    assert len(rows) % 2 == 0 and np.array_equal(_rows_table(rows), _rows_table(rows, mirrored=True))
+    assert (rows["tig_a"] != rows["tig_b"]).all() and (rows["links"] > 0).all()
+
+
+@pytest.mark.parametrize("name,scale,sample_reads", [("c2_bacterial_5mbp", 1.0, 2000), ("c3_celegans_100mbp", 0.1, 500)])
+def test_full_size_properties(gpu_lib, oracle, name, scale, sample_reads):
+    """BASELINE.json configs[1] at its full size (5 Mbp, 500 contigs, 50x 10 kb reads, 75 M candidate pairs) and configs[2]
+    at a tenth (multi-distance): beyond what the oracle runs in seconds, so checked through properties that hold at any
+    size -- counts that must balance, mirror closure, the same rows from one push, from many pushes, and from a second job
+    on the recycled context -- plus the oracle bit for bit on the full-size contigs with the first reads only."""
+    from links_b200 import bf_size, synth
+    from links_b200.seqio import SeqSet
+    _g, contigs, reads, k, d, t = synth.make_config(name, scale)
+    _m, nbytes, h = bf_size(len(contigs.seq) + 10 * contigs.n, 0.001)
+    with _links(k=k, d=d, t=t) as L:
+        L.bf_alloc(nbytes, h)
+        L.push_contigs(contigs)
+        L.push_reads(reads)
+        bits = L.bf_bits().copy()
+        rows, issues, stats = L.finalize()
+        rows, issues = rows.copy(), issues.copy()
+        _check_job_properties(rows, issues, stats, reads, k, d, t)
+        assert len(rows) > 0 and stats["ct_ok_pairs"] > 0
+        # second job on the same context, reads arriving in 7 uneven pushes
+        L.reset()
+        L.bf_alloc(nbytes, h)
+        L.push_contigs(contigs)
+        cuts = sorted({0, reads.n, *(reads.n * f // 100 for f in (3, 11, 40, 41, 77, 99))})
+        for lo, hi in zip(cuts[:-1], cuts[1:]):
+            base = int(reads.off[lo])
+            L.push_reads(SeqSet(reads.seq[base:int(reads.off[hi])], reads.off[lo:hi + 1] - np.uint64(base), []), first_read_idx=lo)
+        rows2, issues2, stats2 = L.finalize()
+        assert np.array_equal(_rows_table(rows2), _rows_table(rows)) and len(issues2) == len(issues)
+        assert {n: stats2[n] for n in stats if n.startswith(("n_c", "n_s", "n_u", "ct_"))} == \
+               {n: stats[n] for n in stats if n.startswith(("n_c", "n_s", "n_u", "ct_"))}
+        # full-size filter and contig table, bounded read sample: the oracle, bit for bit
+        L.reset()
+        L.bf_alloc(nbytes, h)
+        L.push_contigs(contigs)
+        sub = SeqSet(reads.seq[:int(reads.off[sample_reads])], reads.off[:sample_reads + 1], [])
+        L.push_reads(sub)
+        rows3, issues3, stats3 = L.finalize()
+        tsv3, iss3 = L.format_rows(rows3), L.format_issues(issues3)
+    assert np.array_equal(bits, oracle.bf_build(contigs.seq, contigs.off, nbytes, h, k))
+    orows, oiss, ostats, _ = oracle.run(k, d, t, 0, 0.1, bits, h, contigs.seq, contigs.off, sub.seq, sub.off)
+    assert tsv3 == oracle.format_rows(orows) and iss3 == oracle.format_issues(oiss)
+    for key in ("n_candidates", "n_survivors", "n_unique_pairs", "ct_ok_pairs", "ct_problem_pairs", "ct_ok_contig",
+                "ct_iz_issues", "ct_illogical", "ct_gate_fail"):
+        assert stats3[key] == ostats[key], key

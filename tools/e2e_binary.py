@@ -1,0 +1,84 @@
+#!/usr/bin/env python
+"""End-to-end seconds of the command-line pipeline on a synthetic BASELINE workload ("LINKS_CPP start ->
+tsv closed"): FASTA files on disk -> links_b200/bin/LINKS_CPP (GPU) -> .tigpair_checkpoint.tsv -> links_b200/bin/LINKS.pl
+(the C++ layout stage) -> .scaffolds.fa.  Process wall time, CUDA context creation and file IO included; the stage
+seconds are the ones the binary prints in the reference's own banners.
+
+    python tools/e2e_binary.py [--workload c2_bacterial_5mbp] [--scale 1.0] [--runs 3]
+
+Prints one JSON line.  Needs a GPU (LINKS_CPP has no CPU path)."""
+from __future__ import annotations
+
+import argparse
+import hashlib
+import json
+import os
+import re
+import shutil
+import subprocess
+import sys
+import tempfile
+import time
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+
+
+def run_links_cpp(wd: str, k, d, t, env_extra: dict) -> dict:
+    for f in os.listdir(wd):
+        if f.startswith("out."):
+            os.remove(os.path.join(wd, f))
+    env = dict(os.environ, **env_extra)
+    cmd = [os.path.join(ROOT, "links_b200", "bin", "LINKS_CPP"), "-f", "contigs.fa", "-s", "reads.fof", "-b", "out", "-k", str(k),
+           "-d", ",".join(map(str, d)), "-t", ",".join(map(str, t))]
+    t0 = time.perf_counter()
+    r = subprocess.run(cmd, cwd=wd, env=env, capture_output=True, text=True)
+    wall = time.perf_counter() - t0
+    if r.returncode != 0:
+        raise SystemExit(f"LINKS_CPP failed ({r.returncode}): {r.stdout[-500:]} {r.stderr[-500:]}")
+    stages = dict(re.findall(r"^(Bloom filter generated or loaded|Read fasta stage completed|Read contig stage completed|"
+                             r"Pair contig stage completed) in: (.*)$", r.stdout, re.M))
+    cand = int(re.search(r"Candidate k-mer pairs visited: (\d+)", r.stdout).group(1))
+    tsv = open(os.path.join(wd, "out.tigpair_checkpoint.tsv"), "rb").read()
+    return {"wall_s": wall, "stages": stages, "candidates": cand, "tsv_sha256": hashlib.sha256(tsv).hexdigest()[:16], "tsv_rows": tsv.count(b"\n")}
+
+
+def main() -> None:
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--workload", default="c2_bacterial_5mbp")
+    ap.add_argument("--scale", type=float, default=1.0)
+    ap.add_argument("--runs", type=int, default=3)
+    a = ap.parse_args()
+    from links_b200 import build, synth
+    from links_b200.seqio import write_fasta
+    build.build_all()
+    _g, contigs, reads, k, d, t = synth.make_config(a.workload, a.scale)
+    contigs.names = [str(i + 1) for i in range(contigs.n)]
+    reads.names = [f"r{i}" for i in range(reads.n)]
+    wd = tempfile.mkdtemp(prefix="links_e2e_")
+    try:
+        write_fasta(os.path.join(wd, "contigs.fa"), contigs)
+        write_fasta(os.path.join(wd, "reads.fa"), reads)
+        open(os.path.join(wd, "reads.fof"), "w").write("reads.fa\n")
+        in_bytes = os.path.getsize(os.path.join(wd, "contigs.fa")) + os.path.getsize(os.path.join(wd, "reads.fa"))
+        out = {"workload": a.workload, "scale": a.scale, "k": k, "d": d, "t": t, "input_fasta_bytes": in_bytes, "host_cores": os.cpu_count()}
+        for label, env in (("parallel_ingest", {}), ("serial_ingest", {"LINKS_HOST_THREADS": "1"})):
+            runs = [run_links_cpp(wd, k, d, t, env) for _ in range(a.runs)]
+            best = min(runs, key=lambda r: r["wall_s"])
+            out[label] = {"wall_s_runs": [round(r["wall_s"], 3) for r in runs], "wall_s": round(best["wall_s"], 3), "stages": best["stages"],
+                          "pairs_per_s_process": best["candidates"] / best["wall_s"], "candidates": best["candidates"],
+                          "tsv_sha256": best["tsv_sha256"], "tsv_rows": best["tsv_rows"]}
+        assert out["parallel_ingest"]["tsv_sha256"] == out["serial_ingest"]["tsv_sha256"], "ingest paths disagree"
+        t0 = time.perf_counter()
+        open(os.path.join(wd, "empty.fof"), "w").close()
+        subprocess.run([os.path.join(ROOT, "links_b200", "bin", "LINKS.pl"), "-f", "contigs.fa", "-s", "empty.fof", "-b", "out"], cwd=wd,
+                       check=True, stdout=subprocess.DEVNULL)
+        out["layout"] = {"wall_s": round(time.perf_counter() - t0, 3), "scaffolds": open(os.path.join(wd, "out.scaffolds")).read().count("\n"),
+                         "scaffolds_fa_bytes": os.path.getsize(os.path.join(wd, "out.scaffolds.fa"))}
+        print(json.dumps(out))
+    finally:
+        shutil.rmtree(wd, ignore_errors=True)
+
+
+if __name__ == "__main__":
+    main()
