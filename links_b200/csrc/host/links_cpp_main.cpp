@@ -223,10 +223,19 @@ struct Stage {
   }
 };
 
+// LINKS_CPP_TIMING=1: milliseconds since main() at the host's milestones, on stderr (where the wall time of a short job goes)
+void milestone(const char* what)
+{
+  static const bool on = getenv("LINKS_CPP_TIMING") != nullptr;
+  static const auto t0 = std::chrono::steady_clock::now();
+  if (on) std::cerr << "[LINKS_CPP] " << std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count() << " ms  " << what << "\n";
+}
+
 }  // namespace
 
 int main(int argc, char** argv)
 {
+  milestone("main");
   Options o = parse(argc, argv);
   if (!o.ok) return -1;
   print_opts(o);
@@ -245,10 +254,11 @@ int main(int argc, char** argv)
     const int rc = links_create(&ctx, &prm);
     if (rc != LINKS_OK) die(nullptr, "links_create", rc);
   }
+  milestone("links_create done (CUDA context, streams, tables, kernels loaded)");
 
   // two pinned staging buffers shared by the contig and read streams: while one is on its way to the device
   // the ingest threads fill the other.  No larger than the largest input needs (pinning memory is not free).
-  size_t stage_mb = 256;
+  size_t stage_mb = 64;  // x2; pinning costs ~0.35 ms per MB, and 64 MB batches already keep the device busy (profiles/r01zb_e2e_binary_c2.json)
   if (const char* e = getenv("LINKS_STAGE_MB")) stage_mb = std::max<size_t>(size_t(atoll(e)), 1);
   size_t stage_cap = stage_mb << 20;
   {
@@ -269,6 +279,7 @@ int main(int argc, char** argv)
   if (const char* e = getenv("LINKS_HOST_THREADS")) host_threads = unsigned(std::max(atoi(e), 1));
   char* stage[2] = {static_cast<char*>(links_host_alloc(stage_cap)), static_cast<char*>(links_host_alloc(stage_cap))};
   if (!stage[0] || !stage[1]) { std::cerr << "LINKS_CPP: cannot allocate 2 x " << (stage_cap >> 20) << " MB of pinned host memory\n"; return 1; }
+  milestone("pinned staging buffers allocated");
   links_host::SeqBatch batch;
   batch.cap = stage_cap;
   batch.seq = stage[0];
@@ -324,6 +335,7 @@ int main(int argc, char** argv)
       if (!out) { std::cerr << "LINKS_CPP: cannot write " << o.base_name << ".bloom\n"; return 1; }
     }
     st.done("Bloom filter generated or loaded in: ");
+    milestone("stage 1 done");
   }
 
   // ---- stage 2: start_read_fasta (:470-486): every file of the .fof in order; read ordinals run
@@ -342,6 +354,7 @@ int main(int argc, char** argv)
     LK(ctx, links_sync(ctx));
     std::cout << "Reads processed: " << n_reads << "\n";
     st.done("Read fasta stage completed in: ");
+    milestone("stage 2 done");
   }
 
   // ---- stage 3: start_read_contig (:487-513).  The contigs were packed and kept resident by
@@ -386,10 +399,13 @@ int main(int argc, char** argv)
     }
     links_free_result(rows, issues);
     st.done("Pair contig stage completed in: ");
+    milestone("stage 4 done");
   }
 
   links_host_free(stage[0]);
   links_host_free(stage[1]);
+  milestone("staging freed");
   links_destroy(ctx);
+  milestone("links_destroy done");
   return 0;
 }

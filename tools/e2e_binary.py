@@ -28,7 +28,7 @@ def run_links_cpp(wd: str, k, d, t, env_extra: dict) -> dict:
     for f in os.listdir(wd):
         if f.startswith("out."):
             os.remove(os.path.join(wd, f))
-    env = dict(os.environ, **env_extra)
+    env = dict(os.environ, LINKS_CPP_TIMING="1", **env_extra)
     cmd = [os.path.join(ROOT, "links_b200", "bin", "LINKS_CPP"), "-f", "contigs.fa", "-s", "reads.fof", "-b", "out", "-k", str(k),
            "-d", ",".join(map(str, d)), "-t", ",".join(map(str, t))]
     t0 = time.perf_counter()
@@ -40,7 +40,8 @@ def run_links_cpp(wd: str, k, d, t, env_extra: dict) -> dict:
                              r"Pair contig stage completed) in: (.*)$", r.stdout, re.M))
     cand = int(re.search(r"Candidate k-mer pairs visited: (\d+)", r.stdout).group(1))
     tsv = open(os.path.join(wd, "out.tigpair_checkpoint.tsv"), "rb").read()
-    return {"wall_s": wall, "stages": stages, "candidates": cand, "tsv_sha256": hashlib.sha256(tsv).hexdigest()[:16], "tsv_rows": tsv.count(b"\n")}
+    marks = {m.group(2).split(" (")[0]: round(float(m.group(1)), 1) for m in re.finditer(r"^\[LINKS_CPP\] ([0-9.e+-]+) ms  (.*)$", r.stderr, re.M)}
+    return {"wall_s": wall, "stages": stages, "ms_since_main": marks, "candidates": cand, "tsv_sha256": hashlib.sha256(tsv).hexdigest()[:16], "tsv_rows": tsv.count(b"\n")}
 
 
 def main() -> None:
@@ -62,10 +63,10 @@ def main() -> None:
         open(os.path.join(wd, "reads.fof"), "w").write("reads.fa\n")
         in_bytes = os.path.getsize(os.path.join(wd, "contigs.fa")) + os.path.getsize(os.path.join(wd, "reads.fa"))
         out = {"workload": a.workload, "scale": a.scale, "k": k, "d": d, "t": t, "input_fasta_bytes": in_bytes, "host_cores": os.cpu_count()}
-        for label, env in (("parallel_ingest", {}), ("serial_ingest", {"LINKS_HOST_THREADS": "1"})):
+        for label, env in (("parallel_ingest", {}), ("serial_ingest", {"LINKS_HOST_THREADS": "1"}), ("parallel_ingest_stage64", {"LINKS_STAGE_MB": "64"})):
             runs = [run_links_cpp(wd, k, d, t, env) for _ in range(a.runs)]
             best = min(runs, key=lambda r: r["wall_s"])
-            out[label] = {"wall_s_runs": [round(r["wall_s"], 3) for r in runs], "wall_s": round(best["wall_s"], 3), "stages": best["stages"],
+            out[label] = {"wall_s_runs": [round(r["wall_s"], 3) for r in runs], "wall_s": round(best["wall_s"], 3), "stages": best["stages"], "ms_since_main": best["ms_since_main"],
                           "pairs_per_s_process": best["candidates"] / best["wall_s"], "candidates": best["candidates"],
                           "tsv_sha256": best["tsv_sha256"], "tsv_rows": best["tsv_rows"]}
         assert out["parallel_ingest"]["tsv_sha256"] == out["serial_ingest"]["tsv_sha256"], "ingest paths disagree"
