@@ -34,6 +34,9 @@ namespace links {
 #define LINKS_EXTRACT_MIN_CTAS 4
 #endif
 constexpr int kExtractTile = LINKS_EXTRACT_TILE;  // candidates of one (read, distance) per warp tile
+#ifndef LINKS_HASH_SPLIT
+#define LINKS_HASH_SPLIT 1
+#endif
 constexpr int kQueueCap = 64;
 constexpr int kWarpsPerCta = kCtaThreads / 32;
 
@@ -73,7 +76,8 @@ __device__ __forceinline__ uint32_t warp_push_slot(bool pass, uint32_t n, uint32
 // record straight into its OWNER rank's inbox over NVLink peer memory (one cursor atomic per warp and owner), and
 // the kernel's last block publishes the new record counts after system-scope fences.  The transfer is part of
 // the extraction, tile by tile; the owner de-duplicates while this rank keeps extracting.
-template <int H, bool ROUTED>
+// SMALL: the filter has fewer than 2^31 bits (bf.bits32 set): 32-bit remainder in bloom_mod
+template <int H, bool ROUTED, bool SMALL>
 __global__ void __launch_bounds__(kCtaThreads, LINKS_EXTRACT_MIN_CTAS) extract_kernel(ReadBatch rb, DistParams dp, int k, uint64_t kseed,
                                                                  const ulonglong2* __restrict__ g_tab2, BloomView bf,
                                                                  MemberView mv, PairView pv, Counters* __restrict__ ctr,
@@ -81,9 +85,17 @@ __global__ void __launch_bounds__(kCtaThreads, LINKS_EXTRACT_MIN_CTAS) extract_k
 {
   extern __shared__ ulonglong2 s_dyn[];
   const int n_tab = ((k + 1) >> 1) * 16;
-  ulonglong2* s_tab = s_dyn;
   WarpQueues& Q = reinterpret_cast<WarpQueues*>(s_dyn + n_tab)[threadIdx.x >> 5];
+#if LINKS_HASH_SPLIT
+  uint64_t* s_tf = reinterpret_cast<uint64_t*>(s_dyn);  // forward halves, then reverse halves (hash_kmer2_split)
+  uint64_t* s_tr = s_tf + n_tab;
+  for (int i = threadIdx.x; i < n_tab; i += blockDim.x) { const ulonglong2 e = g_tab2[i]; s_tf[i] = e.x; s_tr[i] = e.y; }
+#define LINKS_HASH(pos, f, r) hash_kmer2_split(rb.packed, pos, k, s_tf, s_tr, f, r)
+#else
+  ulonglong2* s_tab = s_dyn;
   for (int i = threadIdx.x; i < n_tab; i += blockDim.x) s_tab[i] = g_tab2[i];
+#define LINKS_HASH(pos, f, r) hash_kmer2(rb.packed, pos, k, s_tab, f, r)
+#endif
   __syncthreads();
 
   const int lane = threadIdx.x & 31;
@@ -157,13 +169,13 @@ __global__ void __launch_bounds__(kCtaThreads, LINKS_EXTRACT_MIN_CTAS) extract_k
         uint64_t h0 = 0;
         if (q < n_tile) {
           uint64_t f, rr;
-          hash_kmer2(rb.packed, pos_a(rank_n(q)), k, s_tab, f, rr);
+          LINKS_HASH(pos_a(rank_n(q)), f, rr);
           h0 = rr < f ? rr : f;
 #if LINKS_PROBE_WITH_SET
           // set bucket and the first probes are independent loads: issue them together (one latency, not two);
           // a proven member's probe result is simply not used
           uint32_t np = 0;
-          pass = H ? bloom_probe_fixed<kFirst>(bf, h0, kseed, 0, np) : bloom_probe_loop(bf, h0, kseed, 0, h_first, np);
+          pass = H ? bloom_probe_fixed<kFirst, SMALL>(bf, h0, kseed, 0, np) : bloom_probe_loop<SMALL>(bf, h0, kseed, 0, h_first, np);
           n_load += h_first;
           if (has_set) member = member_contains(mv, h0, n_msec);
           if (member) { n_probe += hn; pass = false; } else n_probe += np;
@@ -171,10 +183,9 @@ __global__ void __launch_bounds__(kCtaThreads, LINKS_EXTRACT_MIN_CTAS) extract_k
           if (has_set) member = member_contains(mv, h0, n_msec);
           if (member) n_probe += hn;  // the filter holds every set key: all hash_num bits are set, no need to look
           else {
-            pass = H ? bloom_probe_fixed<kFirst>(bf, h0, kseed, 0, n_probe) : bloom_probe_loop(bf, h0, kseed, 0, h_first, n_probe);
+            pass = H ? bloom_probe_fixed<kFirst, SMALL>(bf, h0, kseed, 0, n_probe) : bloom_probe_loop<SMALL>(bf, h0, kseed, 0, h_first, n_probe);
             n_load += h_first;
           }
-#endif
         }
         next_q += 32;
         uint32_t slot;
@@ -184,6 +195,7 @@ __global__ void __launch_bounds__(kCtaThreads, LINKS_EXTRACT_MIN_CTAS) extract_k
           n2 = warp_push_slot(member, n2, slot);
           if (member) Q.q2_i[slot] = uint16_t(q);
         }
+#endif
       } else if (stage == 2) {  // ---- S2: remaining probes of A
         const uint32_t take = n1 < 32u ? n1 : 32u;
         n1 -= take;
@@ -192,7 +204,7 @@ __global__ void __launch_bounds__(kCtaThreads, LINKS_EXTRACT_MIN_CTAS) extract_k
         if (uint32_t(lane) < take) {
           q = Q.q1_i[n1 + lane];
           const uint64_t h0 = Q.q1_h[n1 + lane];
-          pass = H ? bloom_probe_fixed<kRest>(bf, h0, kseed, kFirst, n_probe) : bloom_probe_loop(bf, h0, kseed, h_first, hn, n_probe);
+          pass = H ? bloom_probe_fixed<kRest, SMALL>(bf, h0, kseed, kFirst, n_probe) : bloom_probe_loop<SMALL>(bf, h0, kseed, h_first, hn, n_probe);
           n_load += hn - h_first;
         }
         __syncwarp();
@@ -207,11 +219,11 @@ __global__ void __launch_bounds__(kCtaThreads, LINKS_EXTRACT_MIN_CTAS) extract_k
         uint64_t f = 0, rr = 0;
         if (uint32_t(lane) < take) {
           q = Q.q2_i[n2 + lane];
-          hash_kmer2(rb.packed, pos_b(rank_n(q)), k, s_tab, f, rr);
+          LINKS_HASH(pos_b(rank_n(q)), f, rr);
           const uint64_t h0 = rr < f ? rr : f;
 #if LINKS_PROBE_WITH_SET
           uint32_t np = 0;
-          pass = H ? bloom_probe_fixed<kFirst>(bf, h0, kseed, 0, np) : bloom_probe_loop(bf, h0, kseed, 0, h_first, np);
+          pass = H ? bloom_probe_fixed<kFirst, SMALL>(bf, h0, kseed, 0, np) : bloom_probe_loop<SMALL>(bf, h0, kseed, 0, h_first, np);
           n_load += h_first;
           if (has_set) member = member_contains(mv, h0, n_msec);
           if (member) { n_probe += hn; pass = false; } else n_probe += np;
@@ -219,7 +231,7 @@ __global__ void __launch_bounds__(kCtaThreads, LINKS_EXTRACT_MIN_CTAS) extract_k
           if (has_set) member = member_contains(mv, h0, n_msec);
           if (member) n_probe += hn;
           else {
-            pass = H ? bloom_probe_fixed<kFirst>(bf, h0, kseed, 0, n_probe) : bloom_probe_loop(bf, h0, kseed, 0, h_first, n_probe);
+            pass = H ? bloom_probe_fixed<kFirst, SMALL>(bf, h0, kseed, 0, n_probe) : bloom_probe_loop<SMALL>(bf, h0, kseed, 0, h_first, n_probe);
             n_load += h_first;
           }
 #endif
@@ -241,7 +253,7 @@ __global__ void __launch_bounds__(kCtaThreads, LINKS_EXTRACT_MIN_CTAS) extract_k
         if (uint32_t(lane) < take) {
           q = Q.q3_i[n3 + lane]; f = Q.q3_f[n3 + lane]; rr = Q.q3_r[n3 + lane];
           const uint64_t h0 = rr < f ? rr : f;
-          pass = H ? bloom_probe_fixed<kRest>(bf, h0, kseed, kFirst, n_probe) : bloom_probe_loop(bf, h0, kseed, h_first, hn, n_probe);
+          pass = H ? bloom_probe_fixed<kRest, SMALL>(bf, h0, kseed, kFirst, n_probe) : bloom_probe_loop<SMALL>(bf, h0, kseed, h_first, hn, n_probe);
           n_load += hn - h_first;
         }
         __syncwarp();
@@ -258,7 +270,7 @@ __global__ void __launch_bounds__(kCtaThreads, LINKS_EXTRACT_MIN_CTAS) extract_k
           const uint64_t fb = Q.q4_f[n4 + lane], rbv = Q.q4_r[n4 + lane];
           const uint64_t n = rank_n(q);
           uint64_t fa, ra;
-          hash_kmer2(rb.packed, pos_a(n), k, s_tab, fa, ra);
+          LINKS_HASH(pos_a(n), fa, ra);
           if (fa < rbv) { h_a = rbv; h_b = ra; } else { h_a = fa; h_b = fb; }
           if (!ROUTED) fresh = pair_insert(pv, h_a, h_b, make_okey(rb.first_read_idx + r, di, n), multi_d);
           else okey_r = make_okey(rb.first_read_idx + r, di, n);
@@ -315,5 +327,7 @@ __global__ void __launch_bounds__(kCtaThreads, LINKS_EXTRACT_MIN_CTAS) extract_k
     if (last_block_after_fence(&x->blocks_done)) publish_counts(x, L, epoch, 0);
   }
 }
+
+#undef LINKS_HASH
 
 }  // namespace links

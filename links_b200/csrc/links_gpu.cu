@@ -344,6 +344,7 @@ BloomView bloom_view(links_ctx* c)
   bf.array_bits = c->bf_bytes * 8;
   bf.magic = bf.array_bits ? uint64_t((((unsigned __int128)1) << 64) / bf.array_bits) : 0;
   bf.hash_num = c->hash_num;
+  bf.bits32 = bf.array_bits < (1ull << 31) ? uint32_t(bf.array_bits) : 0u;
   return bf;
 }
 
@@ -351,22 +352,24 @@ BloomView bloom_view(links_ctx* c)
 // (hash_num = floor(-log2(fpr)): 9 for the default -p 0.001) and once with a runtime count.
 using ExtractFn = void (*)(ReadBatch, DistParams, int, uint64_t, const ulonglong2*, BloomView, MemberView, PairView, Counters*,
                            ExchangeDev*, InboxLayout, uint64_t);
-template <bool ROUTED>
+template <bool ROUTED, bool SMALL>
 ExtractFn extract_fn_sel(uint32_t hash_num)
 {
   switch (hash_num) {
-  case 6: return extract_kernel<6, ROUTED>;
-  case 7: return extract_kernel<7, ROUTED>;
-  case 8: return extract_kernel<8, ROUTED>;
-  case 9: return extract_kernel<9, ROUTED>;
-  case 10: return extract_kernel<10, ROUTED>;
-  case 13: return extract_kernel<13, ROUTED>;
-  default: return extract_kernel<0, ROUTED>;
+  case 6: return extract_kernel<6, ROUTED, SMALL>;
+  case 7: return extract_kernel<7, ROUTED, SMALL>;
+  case 8: return extract_kernel<8, ROUTED, SMALL>;
+  case 9: return extract_kernel<9, ROUTED, SMALL>;
+  case 10: return extract_kernel<10, ROUTED, SMALL>;
+  case 13: return extract_kernel<13, ROUTED, SMALL>;
+  default: return extract_kernel<0, ROUTED, SMALL>;
   }
 }
-ExtractFn extract_fn_for(uint32_t hash_num, bool routed = false)
+// small_filter: fewer than 2^31 bits (BloomView::bits32 set), the 32-bit remainder variant
+ExtractFn extract_fn_for(uint32_t hash_num, bool routed, bool small_filter)
 {
-  return routed ? extract_fn_sel<true>(hash_num) : extract_fn_sel<false>(hash_num);
+  if (small_filter) return routed ? extract_fn_sel<true, true>(hash_num) : extract_fn_sel<false, true>(hash_num);
+  return routed ? extract_fn_sel<true, false>(hash_num) : extract_fn_sel<false, false>(hash_num);
 }
 const uint32_t kExtractVariants[] = {0, 6, 7, 8, 9, 10, 13};
 
@@ -998,9 +1001,10 @@ int links_create(links_ctx** out, const links_params* p)
     CUC(c->d_cursor.ensure(64));
     int occ = 0;
     for (uint32_t h : kExtractVariants)
-      for (int routed = 0; routed < 2; ++routed) {
-        CUC(cudaFuncSetAttribute(extract_fn_for(h, routed), cudaFuncAttributeMaxDynamicSharedMemorySize, int(extract_smem_bytes(p->k))));
-        CUC(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, extract_fn_for(h, routed), kCtaThreads, extract_smem_bytes(p->k)));
+      for (int v = 0; v < 4; ++v) {
+        const ExtractFn fn = extract_fn_for(h, (v & 1) != 0, (v & 2) != 0);
+        CUC(cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, int(extract_smem_bytes(p->k))));
+        CUC(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, fn, kCtaThreads, extract_smem_bytes(p->k)));
         c->extract_ctas_per_sm = std::max(occ, 1);
       }
     {
@@ -1236,7 +1240,7 @@ static int push_read_chunk(links_ctx* c, const char* seq, const uint8_t* dev_seq
                    first_read_idx, c->d_cursor.as<unsigned int>()};
       DistParams dp{c->d_dist.as<uint32_t>(), c->d_step.as<uint32_t>(), c->prm.n_dist, c->prm.offset};
       CU(c, cudaMemsetAsync(c->d_cursor.p, 0, sizeof(unsigned int), c->s_compute));
-      extract_fn_for(c->hash_num, fused)<<<grid_for(c, b.n_tiles, kWarpsPerCta, c->extract_ctas_per_sm), kCtaThreads,
+      extract_fn_for(c->hash_num, fused, bloom_view(c).bits32 != 0)<<<grid_for(c, b.n_tiles, kWarpsPerCta, c->extract_ctas_per_sm), kCtaThreads,
                                            extract_smem_bytes(c->prm.k), c->s_compute>>>(
         rb, dp, int(c->prm.k), c->kseed, c->d_tab2.as<ulonglong2>(), bloom_view(c), member_view(c),
         pair_view(c), c->d_ctr.as<Counters>(), c->d_xdev.as<ExchangeDev>(), c->x_lay, c->x_epoch);

@@ -131,6 +131,44 @@ __device__ __forceinline__ void hash_kmer2(const uint32_t* __restrict__ packed, 
   rev = r;
 }
 
+// Same hash from the table split into its forward and reverse halves (8-byte entries).  A 16-entry table of 8-byte
+// entries spans all 32 banks exactly once, so a half-warp's LDS.64 is conflict-free whatever the bases are; with
+// 16-byte entries two of the 16 entries share each bank group and the lookups ran at 1.8x their ideal wavefronts
+// (ncu: 60 M shared wavefronts per launch against 33 M ideal), on the L1/shared pipe that bounds extract_kernel.
+__device__ __forceinline__ void hash_kmer2_split(const uint32_t* __restrict__ packed, uint64_t g, int k,
+                                                 const uint64_t* __restrict__ tf, const uint64_t* __restrict__ tr, uint64_t& fwd,
+                                                 uint64_t& rev)
+{
+  const uint64_t w = g >> 4;
+  const int sh = int(g & 15) * 2;
+  const int npairs = (k + 1) >> 1;
+  uint32_t cur = __ldg(packed + w);
+  uint64_t f = 0, r = 0;
+  for (int p0 = 0; p0 < npairs; p0 += 8) {
+    const uint32_t nxt = __ldg(packed + w + 1 + (p0 >> 3));
+    const uint32_t win = __funnelshift_r(cur, nxt, sh);
+    const uint64_t* af = tf + p0 * 16;
+    const uint64_t* ar = tr + p0 * 16;
+    if (npairs - p0 >= 8) {
+#pragma unroll
+      for (int p = 0; p < 8; ++p) {
+        const uint32_t e = p * 16 + ((win >> (4 * p)) & 15u);
+        f ^= af[e];
+        r ^= ar[e];
+      }
+    } else {
+      for (int p = 0; p < npairs - p0; ++p) {
+        const uint32_t e = p * 16 + ((win >> (4 * p)) & 15u);
+        f ^= af[e];
+        r ^= ar[e];
+      }
+    }
+    cur = nxt;
+  }
+  fwd = f;
+  rev = r;
+}
+
 // true iff none of the bases g .. g+k-1 is flagged in the invalid-base bitmap (32 bases per u32)
 __device__ __forceinline__ bool window_valid(const uint32_t* __restrict__ inv, uint64_t g, int k)
 {
@@ -166,12 +204,22 @@ struct BloomView {
   uint64_t array_bits; // bytes * 8
   uint64_t magic;      // floor(2^64 / array_bits)
   uint32_t hash_num;
+  uint32_t bits32;     // array_bits when it is below 2^31 (filters under 256 MB), else 0
 };
 
+// SMALL: the caller knows bf.bits32 != 0 (array_bits < 2^31, i.e. a filter under 256 MB).  A compile-time choice, not a
+// branch: with both versions inlined at every probe site extract_kernel outgrew the instruction cache and ran 20 % slower.
+template <bool SMALL = false>
 __device__ __forceinline__ uint64_t bloom_mod(uint64_t h, const BloomView& bf)
 {
   // exact h % array_bits: q = floor(h*magic/2^64) is floor(h/d) or one less
   const uint64_t q = __umul64hi(h, bf.magic);
+  if (SMALL) {
+    // h - q*d lies in [0, 2d) and 2d < 2^32: the low words alone give it exactly (a third of the 64-bit version's instructions)
+    uint32_t r = uint32_t(h) - uint32_t(q) * bf.bits32;
+    if (r >= bf.bits32) r -= bf.bits32;
+    return r;
+  }
   uint64_t r = h - q * bf.array_bits;
   if (r >= bf.array_bits) r -= bf.array_bits;
   return r;
@@ -189,9 +237,10 @@ __device__ __forceinline__ bool bloom_contains(const BloomView& bf, uint64_t fwd
   return true;
 }
 
+template <bool SMALL = false>
 __device__ __forceinline__ uint32_t bloom_bit(const BloomView& bf, uint64_t h0, uint64_t kseed, uint32_t i)
 {
-  const uint64_t n = bloom_mod(multihash_i(h0, kseed, i), bf);
+  const uint64_t n = bloom_mod<SMALL>(multihash_i(h0, kseed, i), bf);
   return (__ldg(bf.words + (n >> 5)) >> (n & 31)) & 1u;
 }
 
@@ -216,29 +265,30 @@ __device__ __forceinline__ bool bloom_probe_range(const BloomView& bf, uint64_t 
 
 // N probes starting at i0, N known at compile time: all loads in flight together, no predicated-off
 // bodies.  Accounting as in bloom_probe_range.
-template <int N>
+template <int N, bool SMALL = false>
 __device__ __forceinline__ bool bloom_probe_fixed(const BloomView& bf, uint64_t h0, uint64_t kseed, uint32_t i0, uint32_t& probes)
 {
   if (N <= 0) return true;
   uint32_t miss = 0;
 #pragma unroll
-  for (int j = 0; j < N; ++j) miss |= (bloom_bit(bf, h0, kseed, i0 + j) ^ 1u) << j;
+  for (int j = 0; j < N; ++j) miss |= (bloom_bit<SMALL>(bf, h0, kseed, i0 + j) ^ 1u) << j;
   if (miss) { probes += __ffs(miss); return false; }
   probes += N;
   return true;
 }
 
 // runtime count, groups of four then singles (generic hash_num)
+template <bool SMALL = false>
 __device__ __forceinline__ bool bloom_probe_loop(const BloomView& bf, uint64_t h0, uint64_t kseed, uint32_t i0, uint32_t i1,
                                                  uint32_t& probes)
 {
   while (i0 + 4 <= i1) {
-    if (!bloom_probe_fixed<4>(bf, h0, kseed, i0, probes)) return false;
+    if (!bloom_probe_fixed<4, SMALL>(bf, h0, kseed, i0, probes)) return false;
     i0 += 4;
   }
   for (; i0 < i1; ++i0) {
     ++probes;
-    if (!bloom_bit(bf, h0, kseed, i0)) return false;
+    if (!bloom_bit<SMALL>(bf, h0, kseed, i0)) return false;
   }
   return true;
 }

@@ -541,3 +541,17 @@ def test_full_size_properties(gpu_lib, oracle, name, scale, sample_reads):
     for key in ("n_candidates", "n_survivors", "n_unique_pairs", "ct_ok_pairs", "ct_problem_pairs", "ct_ok_contig",
                 "ct_iz_issues", "ct_illogical", "ct_gate_fail"):
         assert stats3[key] == ostats[key], key
+
+
+def test_bloom_filter_of_2_pow_31_bits_and_more(gpu_lib, oracle):
+    """Filters below 2^31 bits take a 32-bit remainder path in bloom_mod (nthash.cuh); this one is just above and takes the
+    64-bit one.  Same bytes as the oracle (= btllib's h % array_bits, bloom_filter.hpp:617-646) either way."""
+    c = GoldenCase("adv_ns_lower")
+    contigs = c.contigs()
+    for nbytes in ((1 << 28) - 8, (1 << 28) + 8):
+        with _links(k=c.opts["k"], d=c.opts["d"], t=c.steps(), o=c.opts["o"], e=c.opts["e"]) as L:
+            L.bf_alloc(nbytes, 9)
+            L.push_contigs(contigs)
+            bits = L.bf_bits()
+        want = oracle.bf_build(contigs.seq, contigs.off, nbytes, 9, c.opts["k"])
+        assert sha256(bits.tobytes()) == sha256(want.tobytes()), nbytes
