@@ -601,7 +601,8 @@ int ensure_member_capacity(links_ctx* c)
     ContigBatch cb{b->packed.as<uint32_t>(), b->inv.as<uint32_t>(), b->off.as<uint64_t>(), b->base0,
                    b->segs.as<uint32_t>(), b->n_seq, b->n_tiles, b->first_id};
     contig_kernel<2><<<grid_for(c, b->n_tiles, 1, 8), kCtaThreads, c->prm.k * 4 * sizeof(ulonglong2), c->s_compute>>>(
-      cb, int(c->prm.k), c->kseed, c->d_tab.as<ulonglong2>(), bloom_view(c), TableView{nullptr, 0, 0}, member_view(c), c->d_ctr.as<Counters>());
+      cb, int(c->prm.k), c->kseed, c->d_tab.as<ulonglong2>(), bloom_view(c), TableView{nullptr, 0, 0}, member_view(c), c->d_ctr.as<Counters>(),
+      BloomPass{0, ~0ull, 1});
     c->launches++;
   }
   CU(c, cudaGetLastError());
@@ -1186,12 +1187,24 @@ static int contigs_push_impl(links_ctx* c, const char* seq, const uint8_t* dev_s
     ContigBatch cb{b->packed.as<uint32_t>(), b->inv.as<uint32_t>(), b->off.as<uint64_t>(), b->base0,
                    b->segs.as<uint32_t>(), b->n_seq, b->n_tiles, b->first_id};
     if (c->bf_insert) {
-      contig_kernel<0><<<grid_for(c, b->n_tiles, 1, 8), kCtaThreads, k * 4 * sizeof(ulonglong2), c->s_compute>>>(
-        cb, int(k), c->kseed, c->d_tab.as<ulonglong2>(), bloom_view(c), TableView{nullptr, 0, 0}, member_view(c), c->d_ctr.as<Counters>());
-      c->launches++;
+      // a filter beyond L2 is filled block by block (BloomPass): LINKS_BF_BLOCK_MB sets the block size, 0 = always one pass
+      static const uint64_t block_bytes = []() {
+        const char* e = getenv("LINKS_BF_BLOCK_MB");
+        return uint64_t((e ? strtod(e, nullptr) : 64.0) * double(1 << 20));  // fractions allowed (tests: 0.25)
+      }();
+      const uint64_t n_words = (c->bf_bytes + 3) / 4;
+      uint64_t passes = block_bytes && c->bf_bytes > block_bytes + block_bytes / 2 ? (c->bf_bytes + block_bytes - 1) / block_bytes : 1;
+      passes = std::min<uint64_t>(passes, 64);
+      for (uint64_t ps = 0; ps < passes; ++ps) {
+        const BloomPass bp{n_words * ps / passes, ps + 1 == passes ? ~0ull : n_words * (ps + 1) / passes, ps == 0};
+        contig_kernel<0><<<grid_for(c, b->n_tiles, 1, 8), kCtaThreads, k * 4 * sizeof(ulonglong2), c->s_compute>>>(
+          cb, int(k), c->kseed, c->d_tab.as<ulonglong2>(), bloom_view(c), TableView{nullptr, 0, 0}, member_view(c), c->d_ctr.as<Counters>(), bp);
+        c->launches++;
+      }
     } else if (c->member_buckets) {
       contig_kernel<2><<<grid_for(c, b->n_tiles, 1, 8), kCtaThreads, k * 4 * sizeof(ulonglong2), c->s_compute>>>(
-        cb, int(k), c->kseed, c->d_tab.as<ulonglong2>(), bloom_view(c), TableView{nullptr, 0, 0}, member_view(c), c->d_ctr.as<Counters>());
+        cb, int(k), c->kseed, c->d_tab.as<ulonglong2>(), bloom_view(c), TableView{nullptr, 0, 0}, member_view(c), c->d_ctr.as<Counters>(),
+        BloomPass{0, ~0ull, 1});
       c->launches++;
     }
     c->member_positions = c->contig_positions;
@@ -1451,7 +1464,8 @@ static int build_table(links_ctx* c, cudaStream_t st)
     ContigBatch cb{b->packed.as<uint32_t>(), b->inv.as<uint32_t>(), b->off.as<uint64_t>(), b->base0,
                    b->segs.as<uint32_t>(), b->n_seq, b->n_tiles, b->first_id};
     contig_kernel<1><<<grid_for(c, b->n_tiles, 1, 8), kCtaThreads, k * 4 * sizeof(ulonglong2), st>>>(
-      cb, int(k), c->kseed, c->d_tab.as<ulonglong2>(), bloom_view(c), table_view(c), MemberView{nullptr, 0}, c->d_ctr.as<Counters>());
+      cb, int(k), c->kseed, c->d_tab.as<ulonglong2>(), bloom_view(c), table_view(c), MemberView{nullptr, 0}, c->d_ctr.as<Counters>(),
+      BloomPass{0, ~0ull, 1});
     c->launches++;
   }
   CU(c, cudaGetLastError());

@@ -302,4 +302,16 @@ __device__ __forceinline__ void bloom_insert(const BloomView& bf, uint64_t fwd, 
   }
 }
 
+// the same insert restricted to the filter words [w_lo, w_hi) (contig_kernel's BloomPass)
+__device__ __forceinline__ void bloom_insert_range(const BloomView& bf, uint64_t fwd, uint64_t rev, uint64_t kseed, uint64_t w_lo,
+                                                   uint64_t w_hi)
+{
+  const uint64_t h0 = rev < fwd ? rev : fwd;
+  for (uint32_t i = 0; i < bf.hash_num; ++i) {
+    const uint64_t n = bloom_mod(multihash_i(h0, kseed, i), bf);
+    const uint64_t w = n >> 5;
+    if (w >= w_lo && w < w_hi) atomicOr(bf.words + w, 1u << (n & 31));
+  }
+}
+
 } // namespace links

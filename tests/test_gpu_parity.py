@@ -424,7 +424,7 @@ def test_peer_memory_exchange_equals_single_context(gpu_lib, name, n_ranks, inbo
 
 
 @pytest.mark.parametrize("name,host_threads", [("c1", None), ("adv_offset_k20", None), ("adv_ns_lower", None), ("adv_ns_lower", "1"),
-                                               ("adv_tandem", "5")])
+                                               ("adv_tandem", "5"), ("c1", "bf-blocks")])
 def test_links_cpp_binary_writes_reference_files(gpu_lib, tmp_path, name, host_threads):
     """The C++ host LINKS_CPP, run as the reference binary is run (bin/LINKS-make:121-122): same
     options in, byte-identical .bloom, and .tigpair_checkpoint.tsv / .pairing_issues equal to the
@@ -439,6 +439,9 @@ def test_links_cpp_binary_writes_reference_files(gpu_lib, tmp_path, name, host_t
     env = dict(os.environ, LINKS_STAGE_MB="2")  # small staging buffer: several pushes per file
     if name == "c1":
         env["LINKS_STAGE_MB"] = "8"  # its single 1 Mbp read must fit
+    if host_threads == "bf-blocks":  # the Bloom filter built in 6 passes of 0.25 MB blocks (contig_kernel's BloomPass), as for filters beyond L2
+        env["LINKS_BF_BLOCK_MB"] = "0.25"
+        host_threads = None
     if host_threads:  # "1": the serial reader (seq_stream.hpp); default: the multi-threaded FASTA ingest (fasta_ingest.hpp)
         env["LINKS_HOST_THREADS"] = host_threads
     r = subprocess.run(cmd, capture_output=True, text=True, env=env)
