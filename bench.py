@@ -50,6 +50,23 @@ WORKLOADS = {
 }
 
 
+_JSON_FD = 1
+
+
+def claim_stdout() -> None:
+    """The contract is ONE JSON line on stdout.  Libraries write there too (NCCL prints its version banner from C), so
+    file descriptor 1 is pointed at stderr for the run and the JSON line goes to a private copy of the real stdout."""
+    global _JSON_FD
+    sys.stdout.flush()
+    _JSON_FD = os.dup(1)
+    os.dup2(2, 1)
+
+
+def emit(obj: dict) -> None:
+    sys.stdout.flush()
+    os.write(_JSON_FD, (json.dumps(obj) + "\n").encode())
+
+
 def env_int(name: str, default: int) -> int:
     try:
         return int(os.environ.get(name, default))
@@ -226,7 +243,7 @@ def main_reference(args, rank: int, world: int):
     contigs, reads, k, d, t = load_workload(args.workload, args.scale)
     r = cpu_reference(contigs, reads, k, d, t, args.ref_candidates, runs=args.steps, warm=min(args.warmup, 1))
     if r is None:
-        print(json.dumps({"impl": "reference", "unavailable": "oracle/_ref/LINKS_CPP not built (needs /root/reference at build time)"}))
+        emit({"impl": "reference", "unavailable": "oracle/_ref/LINKS_CPP not built (needs /root/reference at build time)"})
         return
     ms = 1000.0 * sum(r["secs"]) / len(r["secs"])
     value = r["cand"] / (ms / 1000.0)
@@ -239,7 +256,7 @@ def main_reference(args, rank: int, world: int):
            "cpu_baseline": {"value": value, "unit": UNIT, "cores": r["threads"], "kind": "reference", "sample": sample},
            "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
            "host_cores": os.cpu_count()}
-    print(json.dumps(out))
+    emit(out)
 
 
 # ---------------------------------------------------------------------------------------------- our arm
@@ -450,7 +467,7 @@ def main_ours(args, rank: int, world: int, local_rank: int):
                                                  f"reference LINKS_CPP -j {r['threads']} from FASTA, {r['secs'][0]:.1f} s wall; host has {os.cpu_count()} cores"}
             else:
                 out["cpu_baseline"] = {"value": None, "unit": UNIT, "cores": 0, "kind": "reference", "sample": "oracle/_ref/LINKS_CPP missing"}
-        print(json.dumps(out))
+        emit(out)
     L.close()
     for p in (pc_seq, pc_off, pr_seq, pr_off):
         lib.links_host_free(p)
@@ -505,10 +522,10 @@ def check_sharding(args, rank: int, world: int, local_rank: int):
             rows1, issues1, stats1 = L.finalize()
         ok = (rows_digest(rows) == rows_digest(rows1) and int(tot[0]) == stats1["n_candidates"]
               and int(tot[1]) == stats1["n_unique_pairs"] and int(tot[2]) == len(issues1))
-        print(json.dumps({"check_sharding": "ok" if ok else "MISMATCH", "n_gpus": world, "workload": args.workload, "scale": args.scale,
+        emit({"check_sharding": "ok" if ok else "MISMATCH", "n_gpus": world, "workload": args.workload, "scale": args.scale,
                           "rows": len(rows1), "rows_digest_sharded": rows_digest(rows), "rows_digest_single": rows_digest(rows1),
                           "candidates": [int(tot[0]), stats1["n_candidates"]], "unique_pairs": [int(tot[1]), stats1["n_unique_pairs"]],
-                          "issues": [int(tot[2]), len(issues1)], "exchange_rank0": ex}))
+                          "issues": [int(tot[2]), len(issues1)], "exchange_rank0": ex})
         if not ok:
             raise SystemExit(1)
     if world > 1:
@@ -529,6 +546,7 @@ def main():
     ap.add_argument("--properties", action="store_true", help="size-independent checks of the last job's result (counts balance, mirror closure)")
     ap.add_argument("--check-sharding", action="store_true", help="parity of the N-rank path against one GPU (same reads split over ranks)")
     args = ap.parse_args()
+    claim_stdout()
     rank, world, local_rank = env_int("RANK", 0), env_int("WORLD_SIZE", 1), env_int("LOCAL_RANK", 0)
     if args.impl == "reference":
         main_reference(args, rank, world)
