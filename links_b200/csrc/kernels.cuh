@@ -89,15 +89,28 @@ __device__ __forceinline__ MemberBucket ld_bucket(const MemberBucket* p)
   return r;
 }
 
+#ifndef LINKS_MEMBER_INSERT_VEC
+#define LINKS_MEMBER_INSERT_VEC 1
+#endif
 __device__ __forceinline__ void member_insert(const MemberView& mv, uint64_t h0)
 {
   if (h0 == kEmpty) return;
   uint64_t b = __umul64hi(slot_hash1(h0), mv.n_buckets);
   for (;;) {
     unsigned long long* s = mv.buckets[b].s;
+#if LINKS_MEMBER_INSERT_VEC
+    // one 32-byte load of the bucket instead of up to four dependent 8-byte ones.  It may be stale, but only towards
+    // "empty" (slots are never cleared during a job), and a slot that looks empty is claimed with a CAS whose return
+    // value is the truth.
+    const MemberBucket v = ld_bucket(mv.buckets + b);
+#endif
 #pragma unroll
     for (int j = 0; j < 4; ++j) {
+#if LINKS_MEMBER_INSERT_VEC
+      unsigned long long cur = v.s[j];
+#else
       unsigned long long cur = *reinterpret_cast<volatile unsigned long long*>(s + j);
+#endif
       if (cur == kEmpty) cur = atomicCAS(s + j, kEmpty, h0);
       if (cur == kEmpty || cur == h0) return;
     }
