@@ -10,6 +10,7 @@
 // program exits non-zero.
 #include "../../../include/links_gpu.h"
 #include "fasta_ingest.hpp"
+#include "links_layout.hpp"
 #include "seq_stream.hpp"
 
 #include <chrono>
@@ -38,6 +39,7 @@ struct Options {
   float insert_stdev = 0.1f, fpr = 0.001f, max_link_ratio = 0.3f;
   bool verbose = false, bf_off = false;
   unsigned thread = 3;
+  std::string l_text, a_text, z_text;  // as typed, for the in-process layout stage (LINKS_CPP_LAYOUT=1), which reads them the Perl way
   int device = 0;  // LINKS_GPU_DEVICE environment variable (no new option letter)
   std::vector<std::string> read_files;
   bool ok = true;
@@ -90,9 +92,9 @@ Options parse(int argc, char** argv)
     case 'j': o.thread = unsigned(strtoul(optarg, nullptr, 10)); break;
     case 'o': o.offset = strtoul(optarg, nullptr, 10); break;
     case 'e': o.insert_stdev = strtof(optarg, nullptr); break;
-    case 'l': o.min_links = strtoul(optarg, nullptr, 10); break;
-    case 'a': o.max_link_ratio = strtof(optarg, nullptr); break;
-    case 'z': o.min_size = strtoul(optarg, nullptr, 10); break;
+    case 'l': o.min_links = strtoul(optarg, nullptr, 10); o.l_text = optarg; break;
+    case 'a': o.max_link_ratio = strtof(optarg, nullptr); o.a_text = optarg; break;
+    case 'z': o.min_size = strtoul(optarg, nullptr, 10); o.z_text = optarg; break;
     case 'b': o.base_name = optarg; break;
     case 'r': o.bf_file = optarg; break;
     case 'p': o.fpr = strtof(optarg, nullptr); break;
@@ -397,8 +399,25 @@ int main(int argc, char** argv)
       for (uint64_t i = 0; i < n_rows; ++i) { const int n = links_format_row(&rows[i], line, sizeof line); f.write(line, n); }
       if (!f) { std::cerr << "LINKS_CPP: cannot write " << o.base_name << ".tigpair_checkpoint.tsv\n"; return 1; }
     }
-    links_free_result(rows, issues);
     st.done("Pair contig stage completed in: ");
+    if (getenv("LINKS_CPP_LAYOUT")) {
+      // the layout stage (bin/LINKS.pl, here links_layout.hpp) on the rows still in memory -- same
+      // files as `LINKS.pl -f <f> -b <b> -l -a -z` run afterwards would write, without reading the tsv back
+      std::vector<links_layout::RowIn> in(n_rows);
+      for (uint64_t i = 0; i < n_rows; ++i)
+        in[i] = links_layout::RowIn{rows[i].bin, rows[i].tig_a, rows[i].tig_b, rows[i].rev_a != 0, rows[i].rev_b != 0, rows[i].links, rows[i].gaps};
+      links_layout::Options lo;
+      lo.assembly_file = o.assembly_file;
+      lo.base_name = o.base_name;
+      if (links_layout::perl_true(o.l_text)) lo.min_links = strtoll(o.l_text.c_str(), nullptr, 10);
+      if (links_layout::perl_true(o.z_text)) lo.min_size = strtoll(o.z_text.c_str(), nullptr, 10);
+      if (links_layout::perl_true(o.a_text)) lo.max_link_ratio = strtod(o.a_text.c_str(), nullptr);
+      Stage ls("STAGE: Scaffold layout (in process)");
+      const int lrc = links_layout::run(lo, stdout, in.data(), in.size());
+      ls.done("Layout stage completed in: ");
+      if (lrc) { links_free_result(rows, issues); return lrc; }
+    }
+    links_free_result(rows, issues);
     milestone("stage 4 done");
   }
 

@@ -147,6 +147,50 @@ inline Layer& layer_of(Node& n, const std::string& key)
   return n.layers.back();
 }
 
+// One row of <b>.tigpair_checkpoint.tsv as readContigPairs takes it (bin/LINKS.pl:1159-1215): dist, "f12", "r7", links, gaps
+inline void add_pair_row(const std::string& dist, const std::string& f1, const std::string& f2, long long links, long long gaps,
+                         bool simple_flag, const Contigs& tigs, const Options& o, PairMap& pair, SimpleMap& simple)
+{
+  // contigs shorter than -z are skipped; an unknown or empty id has length 0 (:1166-1168)
+  const std::string uid = f1.empty() ? "" : f1.substr(1), vid = f2.empty() ? "" : f2.substr(1);
+  auto len_of = [&](const std::string& id) -> long long {
+    if (id.empty()) return 0;
+    for (char ch : id) if (ch < '0' || ch > '9') return 0;
+    return (long long)tigs.length(strtoll(id.c_str(), nullptr, 10));
+  };
+  if (len_of(uid) < o.min_size || len_of(vid) < o.min_size) return;
+  if (!perl_true(f2)) return;
+  LinkGap& lg = layer_of(pair[f1], dist).list[f2];
+  lg.links += links; lg.gaps += gaps;
+  if (simple_flag) {
+    char d1, d2; long long t1, t2;
+    if (parse_tig(f1, d1, t1) && parse_tig(f2, d2, t2) && t1 < t2) {
+      Simple& s = simple[t1][t2];
+      s.has_links = true; s.links += links; s.sumgaps += gaps;
+      if (links >= s.max) {  // direction with most support (:1207-1210)
+        s.type = std::string(d1 == 'f' ? "1" : "0") + (d2 == 'f' ? "1" : "0");
+        s.max = links;
+      }
+    }
+  }
+}
+
+inline void read_simple_pairs(const std::string& simplefile, SimpleMap& simple)  // optional <b>.simplepair_checkpoint.tsv (:1218-1231)
+{
+  FILE* spr = fopen(simplefile.c_str(), "r");
+  if (!spr) return;
+  std::string line;
+  while (read_line(spr, line)) {
+    const std::vector<std::string> info = split_tab(line);
+    if (info.size() > 2 && perl_true(info[2])) {
+      Simple& s = simple[to_ll(info[0])][to_ll(info[1])];
+      s.has_links = true; s.links = to_ll(info[2]); s.sumgaps = info.size() > 3 ? to_ll(info[3]) : 0;
+      s.type = info.size() > 4 ? info[4] : "";
+    }
+  }
+  fclose(spr);
+}
+
 // bin/LINKS.pl:1146-1235
 inline void read_contig_pairs(const std::string& pairfile, const std::string& simplefile, const Contigs& tigs, const Options& o,
                               PairMap& pair, SimpleMap& simple)
@@ -159,43 +203,29 @@ inline void read_contig_pairs(const std::string& pairfile, const std::string& si
   while (read_line(in, line)) {
     const std::vector<std::string> info = split_tab(line);
     const std::string f1 = info.size() > 1 ? info[1] : "", f2 = info.size() > 2 ? info[2] : "";
-    // contigs shorter than -z are skipped; an unknown or empty id has length 0 (:1166-1168)
-    const std::string uid = f1.empty() ? "" : f1.substr(1), vid = f2.empty() ? "" : f2.substr(1);
-    auto len_of = [&](const std::string& id) -> long long {
-      if (id.empty()) return 0;
-      for (char ch : id) if (ch < '0' || ch > '9') return 0;
-      return (long long)tigs.length(strtoll(id.c_str(), nullptr, 10));
-    };
-    if (len_of(uid) < o.min_size || len_of(vid) < o.min_size) continue;
-    if (!perl_true(f2)) continue;
-    const std::string dist = info[0];
-    const long long links = info.size() > 3 ? to_ll(info[3]) : 0, gaps = info.size() > 4 ? to_ll(info[4]) : 0;
-    LinkGap& lg = layer_of(pair[f1], dist).list[f2];
-    lg.links += links; lg.gaps += gaps;
-    if (simple_flag) {
-      char d1, d2; long long t1, t2;
-      if (parse_tig(f1, d1, t1) && parse_tig(f2, d2, t2) && t1 < t2) {
-        Simple& s = simple[t1][t2];
-        s.has_links = true; s.links += links; s.sumgaps += gaps;
-        if (links >= s.max) {  // direction with most support (:1207-1210)
-          s.type = std::string(d1 == 'f' ? "1" : "0") + (d2 == 'f' ? "1" : "0");
-          s.max = links;
-        }
-      }
-    }
+    add_pair_row(info[0], f1, f2, info.size() > 3 ? to_ll(info[3]) : 0, info.size() > 4 ? to_ll(info[4]) : 0, simple_flag, tigs, o, pair,
+                 simple);
   }
   fclose(in);
-  if (FILE* spr = fopen(simplefile.c_str(), "r")) {  // optional <b>.simplepair_checkpoint.tsv (:1218-1231)
-    while (read_line(spr, line)) {
-      const std::vector<std::string> info = split_tab(line);
-      if (info.size() > 2 && perl_true(info[2])) {
-        Simple& s = simple[to_ll(info[0])][to_ll(info[1])];
-        s.has_links = true; s.links = to_ll(info[2]); s.sumgaps = info.size() > 3 ? to_ll(info[3]) : 0;
-        s.type = info.size() > 4 ? info[4] : "";
-      }
-    }
-    fclose(spr);
+  read_simple_pairs(simplefile, simple);
+}
+
+// The same from rows still in memory (no round trip through the tsv).  A row is what
+// links_finalize returns (include/links_gpu.h: links_row) and what links_format_row prints as one tsv line.
+struct RowIn { int bin; uint32_t tig_a, tig_b; bool rev_a, rev_b; unsigned long long links; long long gaps; };
+inline void pairs_from_rows(const RowIn* rows, size_t n, const std::string& simplefile, const Contigs& tigs, const Options& o,
+                            PairMap& pair, SimpleMap& simple)
+{
+  bool simple_flag = true;
+  if (FILE* t = fopen(simplefile.c_str(), "r")) { simple_flag = false; fclose(t); }
+  for (size_t i = 0; i < n; ++i) {
+    const RowIn& r = rows[i];
+    // contig id 0 prints as an empty id, as links_format_row does
+    const std::string a = r.tig_a ? std::to_string(r.tig_a) : std::string(), b = r.tig_b ? std::to_string(r.tig_b) : std::string();
+    add_pair_row(std::to_string(r.bin), (r.rev_a ? "r" : "f") + a, (r.rev_b ? "r" : "f") + b, (long long)r.links, r.gaps, simple_flag, tigs,
+                 o, pair, simple);
   }
+  read_simple_pairs(simplefile, simple);
 }
 
 // Perl prints a number with %.15g; `if ($ratio =~ /(\d+\.\d{2})/){$ratio = $1;}` (:757) then keeps the first
@@ -425,14 +455,15 @@ inline std::string date_now()
 }
 
 // The whole Perl stage (bin/LINKS.pl:117-186): reads <b>.tigpair_checkpoint.tsv, writes the scaffold files.
-inline int run(const Options& o, FILE* log_to = stdout)
+// rows != nullptr: the pairs come from memory (n_rows of them) and <b>.tigpair_checkpoint.tsv is not read.
+inline int run(const Options& o, FILE* log_to = stdout, const RowIn* rows = nullptr, size_t n_rows = 0)
 {
   const std::string b = o.base_name;
   const std::string scaffold = b + ".scaffolds", graph = b + ".gv", corr = b + ".assembly_correspondence.tsv";
   const std::string tigpair = b + ".tigpair_checkpoint.tsv", simplepair = b + ".simplepair_checkpoint.tsv", logf = b + ".log";
   FILE* lg = fopen(logf.c_str(), "a");
   auto say = [&](const std::string& m) { fputs(m.c_str(), log_to); if (lg) fputs(m.c_str(), lg); };
-  {
+  if (!rows) {
     FILE* t = fopen(tigpair.c_str(), "r");
     if (!t) { fputs("No checkpoint provided", log_to); if (lg) fclose(lg); return 0; }  // :121-124
     fclose(t);
@@ -443,7 +474,8 @@ inline int run(const Options& o, FILE* log_to = stdout)
     const Contigs tigs = read_contigs_memory(o.assembly_file);
     say("\ndone.\nReading sequence pairs from " + tigpair + " : " + date_now() + "\n");
     LayoutState st;
-    read_contig_pairs(tigpair, simplepair, tigs, o, st.pair, st.simple);
+    if (rows) pairs_from_rows(rows, n_rows, simplepair, tigs, o, st.pair, st.simple);
+    else read_contig_pairs(tigpair, simplepair, tigs, o, st.pair, st.simple);
     say("\ndone.\nBuilding scaffolds : " + date_now() + "\n");
     const std::vector<Scaffold> scaffolds = build_scaffolds(st, tigs, o, scaffold);
     const std::string date = date_now();

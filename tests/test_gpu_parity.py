@@ -424,7 +424,7 @@ def test_peer_memory_exchange_equals_single_context(gpu_lib, name, n_ranks, inbo
 
 
 @pytest.mark.parametrize("name,host_threads", [("c1", None), ("adv_offset_k20", None), ("adv_ns_lower", None), ("adv_ns_lower", "1"),
-                                               ("adv_tandem", "5"), ("c1", "bf-blocks")])
+                                               ("adv_tandem", "5"), ("c1", "bf-blocks"), ("adv_k40", "layout-in-process")])
 def test_links_cpp_binary_writes_reference_files(gpu_lib, tmp_path, name, host_threads):
     """The C++ host LINKS_CPP, run as the reference binary is run (bin/LINKS-make:121-122): same
     options in, byte-identical .bloom, and .tigpair_checkpoint.tsv / .pairing_issues equal to the
@@ -439,6 +439,13 @@ def test_links_cpp_binary_writes_reference_files(gpu_lib, tmp_path, name, host_t
     env = dict(os.environ, LINKS_STAGE_MB="2")  # small staging buffer: several pushes per file
     if name == "c1":
         env["LINKS_STAGE_MB"] = "8"  # its single 1 Mbp read must fit
+    lay_meta = None
+    if host_threads == "layout-in-process":  # LINKS_CPP_LAYOUT=1: the layout stage runs inside LINKS_CPP on the rows still in memory
+        import json
+        lay_meta = json.load(open(os.path.join(GOLDEN_DIR, name, "layout", "layout.json")))
+        env["LINKS_CPP_LAYOUT"] = "1"
+        cmd += ["-l", str(lay_meta["opts"]["l"]), "-a", str(lay_meta["opts"]["a"]), "-z", str(lay_meta["opts"]["z"])]
+        host_threads = None
     if host_threads == "bf-blocks":  # the Bloom filter built in 6 passes of 0.25 MB blocks (contig_kernel's BloomPass), as for filters beyond L2
         env["LINKS_BF_BLOCK_MB"] = "0.25"
         host_threads = None
@@ -452,6 +459,13 @@ def test_links_cpp_binary_writes_reference_files(gpu_lib, tmp_path, name, host_t
     assert sha256(open(base + ".bloom", "rb").read()) == c.meta["bloom_sha256"]
     assert sort_lines(open(base + ".tigpair_checkpoint.tsv", "rb").read()) == c.expected_tsv()
     assert sort_issue_records(open(base + ".pairing_issues", "rb").read()) == c.expected_issues()
+    if lay_meta:
+        import hashlib
+        assert "STAGE: Scaffold layout (in process)" in r.stdout
+        assert open(base + ".scaffolds", "rb").read() == open(os.path.join(GOLDEN_DIR, name, "layout", "expected.scaffolds"), "rb").read()
+        assert hashlib.sha256(open(base + ".scaffolds.fa", "rb").read()).hexdigest() == lay_meta["scaffolds_fa_sha256"]
+        for suffix in (".scaffolds", ".scaffolds.fa", ".gv", ".assembly_correspondence.tsv"):
+            os.remove(base + suffix)  # the separate layout run below must recreate them
     # -r: reuse the filter just written
     r = subprocess.run(cmd[:6] + [base + "2"] + cmd[7:] + ["-r", base + ".bloom"], capture_output=True, text=True, env=env)
     assert r.returncode == 0, r.stderr

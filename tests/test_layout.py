@@ -96,3 +96,36 @@ def test_layout_option_and_input_quirks(layout_bin, tmp_path):
     assert sc == ["scaffold1,1800,f1z800k7a0m100_f2Z1000", "scaffold2,3,f3Z3"]
     fa = open(os.path.join(wd, "out.scaffolds.fa")).read().splitlines()
     assert fa[1] == "ACGT" * 200 + "N" * 100 + "TTGCA" * 200
+
+
+@pytest.mark.parametrize("case", ["c1", "lay_stress_loose", "adv_ns_lower"])
+def test_layout_from_rows_in_memory_equals_layout_from_tsv(tmp_path, case):
+    """LINKS_CPP can hand its rows to the layout stage in memory (LINKS_CPP_LAYOUT=1); the files must
+    be the ones the stage writes after reading the tsv those rows print as."""
+    ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    exe = str(tmp_path / "layout_rows_check")
+    subprocess.run(["g++", "-O2", "-std=c++17", "-I", os.path.join(ROOT, "links_b200", "csrc", "host"),
+                    os.path.join(ROOT, "tests", "host", "layout_rows_check.cpp"), "-o", exe], check=True)
+    d = os.path.join(GOLDEN, case, "layout")
+    meta = json.load(open(os.path.join(d, "layout.json")))
+    wd = str(tmp_path)
+    d_in = os.path.join(GOLDEN, meta.get("input_from", case), "layout")
+    tsv = os.path.join(d_in, "input.tigpair_checkpoint.tsv")
+    if not os.path.exists(tsv):
+        tsv = os.path.join(GOLDEN, case, "expected.tigpair_checkpoint.tsv")
+    if "stress" in meta:
+        from links_b200 import synth
+        from links_b200.seqio import write_fasta
+        st = meta["stress"]
+        contigs = synth.make_contigs(synth.make_genome(st["genome"], seed=st["seeds"][0]), st["contigs"], seed=st["seeds"][1])
+        contigs.names = [str(i + 1) for i in range(contigs.n)]
+        write_fasta(os.path.join(wd, "contigs.fa"), synth.unique_lengths(contigs))
+    else:
+        open(os.path.join(wd, "contigs.fa"), "wb").write(gzip.open(os.path.join(GOLDEN, case, "contigs.fa.gz"), "rb").read())
+    o = meta["opts"]
+    subprocess.run([exe, "contigs.fa", tsv, "file", "mem", str(o["l"]), str(o["a"]), str(o["z"])], cwd=wd, check=True)
+    rd = lambda b, s: open(os.path.join(wd, b + "." + s), "rb").read()  # noqa: E731
+    assert rd("mem", "scaffolds") == rd("file", "scaffolds") == open(os.path.join(d, "expected.scaffolds"), "rb").read()
+    assert rd("mem", "scaffolds.fa") == rd("file", "scaffolds.fa")
+    assert _below_label(rd("mem", "gv")) == _below_label(rd("file", "gv")) == open(os.path.join(d, "expected.gv_body"), "rb").read()
+    assert rd("mem", "assembly_correspondence.tsv").split(b"\n", 1)[1] == rd("file", "assembly_correspondence.tsv").split(b"\n", 1)[1]
