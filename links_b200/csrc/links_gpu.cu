@@ -952,7 +952,10 @@ int links_create(links_ctx** out, const links_params* p)
       return LINKS_E_CUDA;                                                                                 \
     }                                                                                                      \
   } while (0)
+  host_mark(c, "create: device count known (driver initialised)");
   CUC(cudaSetDevice(c->device));
+  CUC(cudaFree(nullptr));  // force the primary context now so that the marks below separate it from the module load
+  host_mark(c, "create: primary context ready");
   cudaDeviceProp prop;
   CUC(cudaGetDeviceProperties(&prop, c->device));
   c->sm_count = prop.multiProcessorCount;
@@ -1000,6 +1003,7 @@ int links_create(links_ctx** out, const links_params* p)
     CUC(c->d_tab2.ensure(tab2.size() * sizeof(ulonglong2)));
     CUC(cudaMemcpy(c->d_tab2.p, tab2.data(), tab2.size() * sizeof(ulonglong2), cudaMemcpyHostToDevice));
     CUC(c->d_cursor.ensure(64));
+    host_mark(c, "create: streams, events, hash tables on device");
     int occ = 0;
     for (uint32_t h : kExtractVariants)
       for (int v = 0; v < 4; ++v) {
@@ -1023,7 +1027,9 @@ int links_create(links_ctx** out, const links_params* p)
                            (const void*)scan_apply_kernel, (const void*)scan_small_kernel, (const void*)radix_hist_kernel,
                            (const void*)radix_scatter_kernel, (const void*)head_flags_kernel, (const void*)reduce_by_key_kernel,
                            (const void*)rows_segment_sum_kernel};
+      host_mark(c, "create: extract variants configured");
       for (const void* f : fns) CUC(cudaFuncGetAttributes(&fa, f));
+      host_mark(c, "create: all kernels loaded");
     }
     CUC(cudaHostAlloc(reinterpret_cast<void**>(&c->h_snap), sizeof(Counters) * links_ctx::kSnaps, cudaHostAllocDefault));
     for (int i = 0; i < links_ctx::kSnaps; ++i) CUC(cudaEventCreateWithFlags(&c->ev_snap[i], cudaEventDisableTiming));
