@@ -9,6 +9,7 @@
 #pragma once
 #include <cstdint>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <functional>
 #include <stdexcept>
@@ -50,7 +51,8 @@ public:
   explicit ByteSource(const std::string& path)
   {
     const char* tool = nullptr;
-    if (ends_with(path, ".gz")) tool = "gzip -dc";
+    // pigz when the machine has it, else gzip -- btllib's own order of preference (data_stream.hpp:36-37)
+    if (ends_with(path, ".gz") || ends_with(path, ".z")) tool = system("command -v pigz >/dev/null 2>&1") == 0 ? "pigz -dc" : "gzip -dc";
     else if (ends_with(path, ".bz2")) tool = "bzip2 -dc";
     else if (ends_with(path, ".xz")) tool = "xz -dc";
     else if (ends_with(path, ".zst")) tool = "zstd -dc";
