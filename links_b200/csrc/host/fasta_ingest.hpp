@@ -1,4 +1,4 @@
-// links_b200/csrc/host/fasta_ingest.hpp -- multi-threaded ingest of plain (uncompressed) FASTA files.
+// links_b200/csrc/host/fasta_ingest.hpp -- multi-threaded ingest of plain (uncompressed) FASTA and four-line FASTQ files.
 //
 // SURVEY 8(f) row 1.  The reference reads sequences with btllib::SeqReader worker threads feeding LINKS'
 // InputWorker (reference src/LINKS.hpp:404-468); with the hot path on the GPU the single-threaded line
@@ -10,8 +10,12 @@
 //
 // Record semantics are those of seq_stream.hpp (and so of SeqReader in LONG_MODE): records in file order,
 // bases untouched, lines joined, trailing '\r' dropped, a header directly followed by another header is an
-// empty record.  FASTQ, compressed or non-regular inputs are not handled here: usable() is false and the
-// caller falls back to stream_file().
+// empty record.  FASTQ is taken when the WHOLE file is strict four-line FASTQ (one sequence line, one quality line of
+// the same length per record, no blank lines but at the end): the constructor indexes and verifies it with T threads --
+// every thread finds its first record by "a line starting with '@' whose second successor starts with '+'", and the
+// pieces must meet exactly -- and anything else (wrapped FASTQ, truncated records, mixed files) is left to the serial
+// reader, whose behaviour is the definition.  Compressed or non-regular inputs are not handled here either: usable()
+// is false and the caller falls back to stream_file().
 #pragma once
 #include <fcntl.h>
 #include <sys/mman.h>
@@ -37,7 +41,9 @@ public:
   // Called from ONE thread, in file order; the buffer may be reused as soon as it returns.
   using Sink = std::function<void(const char*, const uint64_t*, size_t, uint64_t)>;
 
-  ParallelFastaIngest(const std::string& path, unsigned threads) : path_(path), threads_(std::max(threads, 1u))
+  // min_segment: least bytes of file per indexing thread (tests shrink it so that small files are cut into many pieces)
+  ParallelFastaIngest(const std::string& path, unsigned threads, uint64_t min_segment = 1u << 16)
+    : path_(path), threads_(std::max(threads, 1u)), min_segment_(std::max<uint64_t>(min_segment, 1))
   {
     for (const char* suf : {".gz", ".bz2", ".xz", ".zst", ".zip", ".lrz", ".7z"})
       if (path.size() >= strlen(suf) && path.compare(path.size() - strlen(suf), strlen(suf), suf) == 0) return;
@@ -52,8 +58,9 @@ public:
     madvise(const_cast<char*>(data_), size_, MADV_SEQUENTIAL);
     // first non-blank line decides the format, as in stream_file()
     uint64_t p = 0;
-    while (p < size_ && (data_[p] == '\n' || (data_[p] == '\r' && p + 1 < size_ && data_[p + 1] == '\n'))) ++p;
+    while (p < size_ && data_[p] == '\n') ++p;  // (a line holding only '\r' is not blank to stream_file(): it rejects the file)
     if (p < size_ && data_[p] == '>' && (p == 0 || data_[p - 1] == '\n')) { first_header_ = p; usable_ = true; }
+    else if (p < size_ && data_[p] == '@' && (p == 0 || data_[p - 1] == '\n')) { first_header_ = p; fastq_ = true; usable_ = index_fastq(); }
   }
   ~ParallelFastaIngest()
   {
@@ -64,6 +71,7 @@ public:
   ParallelFastaIngest& operator=(const ParallelFastaIngest&) = delete;
 
   bool usable() const { return usable_; }
+  bool is_fastq() const { return fastq_; }
   void set_window_bytes(uint64_t w) { window_ = std::max<uint64_t>(w, 1); }  // tests shrink it to exercise the seams
 
   // Streams every record to `sink` in batches of at most cap bytes / max_records records, alternating between
@@ -94,10 +102,28 @@ private:
 
   std::string path_;
   unsigned threads_;
+  uint64_t min_segment_;
   int fd_ = -1;
   const char* data_ = nullptr;
   uint64_t size_ = 0, first_header_ = 0, window_ = 256ull << 20;
-  bool usable_ = false;
+  bool usable_ = false, fastq_ = false;
+  std::vector<Rec> fq_recs_;  // FASTQ: every record of the file (index_fastq)
+
+  // end of the line starting at p (position of its '\n', or size_ when the last line has none)
+  uint64_t line_end(uint64_t p) const
+  {
+    const void* nl = memchr(data_ + p, '\n', size_ - p);
+    return nl ? uint64_t(static_cast<const char*>(nl) - data_) : size_;
+  }
+  bool rest_is_blank(uint64_t p) const
+  {
+    for (; p < size_; ++p)
+      if (data_[p] != '\n') return false;  // a "\r\n" blank line is an error to stream_file(): let it say so
+    return true;
+  }
+  uint64_t fastq_record_at_or_after(uint64_t s) const;
+  bool index_fastq_segment(uint64_t p, uint64_t e, std::vector<Rec>& out, uint64_t& end_pos) const;
+  bool index_fastq();
 };
 
 inline void ParallelFastaIngest::index_segment(uint64_t s, uint64_t e, std::vector<Rec>& out) const
@@ -124,6 +150,81 @@ inline void ParallelFastaIngest::index_segment(uint64_t s, uint64_t e, std::vect
     out.push_back(r);
     p = q;
   }
+}
+
+// first position >= s that starts a line with '@' whose second successor line starts with '+' (size_ if none).
+// In four-line FASTQ a quality line may start with '@' too, but two lines below it is a sequence line, never a '+'.
+inline uint64_t ParallelFastaIngest::fastq_record_at_or_after(uint64_t s) const
+{
+  uint64_t p = line_start_at_or_after(s);
+  while (p < size_) {
+    const uint64_t e0 = line_end(p);
+    if (data_[p] == '@' && e0 < size_) {
+      const uint64_t e1 = line_end(e0 + 1);
+      if (e1 < size_ && e1 + 1 < size_ && data_[e1 + 1] == '+') return p;
+    }
+    if (e0 >= size_) break;
+    p = e0 + 1;
+  }
+  return size_;
+}
+
+// records starting in [p, e), p being a record start; false = not strict four-line FASTQ here
+inline bool ParallelFastaIngest::index_fastq_segment(uint64_t p, uint64_t e, std::vector<Rec>& out, uint64_t& end_pos) const
+{
+  auto stripped = [&](uint64_t b, uint64_t le, bool has_nl) -> uint64_t {  // line length without the '\r' of a CRLF
+    uint64_t l = le - b;
+    if (l && has_nl && data_[le - 1] == '\r') --l;
+    return l;
+  };
+  while (p < e && p < size_) {
+    if (data_[p] != '@') {  // only blank lines may follow the last record
+      if (!rest_is_blank(p)) return false;
+      p = size_;
+      break;
+    }
+    const uint64_t e0 = line_end(p);
+    if (e0 >= size_) return false;
+    const uint64_t b1 = e0 + 1, e1 = line_end(b1);
+    if (e1 >= size_ || (b1 < e1 && (data_[b1] == '+' || data_[b1] == '@' || data_[b1] == '>'))) return false;
+    const uint64_t b2 = e1 + 1;
+    if (b2 >= size_ || data_[b2] != '+') return false;
+    const uint64_t e2 = line_end(b2);
+    if (e2 >= size_) return false;
+    const uint64_t b3 = e2 + 1, e3 = line_end(b3);
+    const uint64_t seq_len = stripped(b1, e1, true);
+    if (seq_len == 0) return false;  // the serial reader closes such a record at the '+' line: leave it to that reader
+    if (stripped(b3, e3, e3 < size_) != seq_len) return false;  // wrapped or truncated quality
+    out.push_back(Rec{b1, e1, seq_len});
+    p = e3 < size_ ? e3 + 1 : size_;
+  }
+  end_pos = p;
+  return true;
+}
+
+inline bool ParallelFastaIngest::index_fastq()
+{
+  const uint64_t span = size_ - first_header_;
+  const unsigned T = unsigned(std::min<uint64_t>(threads_, std::max<uint64_t>(span / min_segment_, 1)));
+  std::vector<std::vector<Rec>> per(T);
+  std::vector<uint64_t> first(T, 0), last(T, 0);
+  std::vector<char> ok(T, 1);
+  parallel(T, [&](unsigned t) {
+    const uint64_t s = first_header_ + span * t / T, e = t + 1 == T ? size_ : first_header_ + span * (t + 1) / T;
+    const uint64_t p = t == 0 ? first_header_ : fastq_record_at_or_after(s);
+    first[t] = last[t] = p;
+    if (p < e) ok[t] = index_fastq_segment(p, e, per[t], last[t]) ? 1 : 0;
+  });
+  for (unsigned t = 0; t < T; ++t) {
+    if (!ok[t]) return false;
+    if (t && first[t] != last[t - 1]) return false;  // the pieces must meet exactly, or the heuristic start was wrong
+  }
+  if (last[T - 1] != size_ && !rest_is_blank(last[T - 1])) return false;
+  size_t n = 0;
+  for (auto& v : per) n += v.size();
+  fq_recs_.reserve(n);
+  for (auto& v : per) fq_recs_.insert(fq_recs_.end(), v.begin(), v.end());
+  return true;
 }
 
 inline void ParallelFastaIngest::copy_record(const Rec& r, char* dst) const
@@ -189,18 +290,24 @@ inline uint64_t ParallelFastaIngest::run(char* const buf[2], size_t cap, size_t 
     std::vector<std::vector<Rec>> per(threads_);
     std::vector<Rec> recs;
     while (pos < size_) {
-      const uint64_t wend = std::min(size_, pos + window_);
-      const unsigned T = unsigned(std::min<uint64_t>(threads_, std::max<uint64_t>((wend - pos) >> 16, 1)));
-      parallel(T, [&](unsigned t) {
-        per[t].clear();
-        const uint64_t s = t == 0 ? pos : line_start_at_or_after(pos + (wend - pos) * t / T);
-        const uint64_t e = t + 1 == T ? wend : line_start_at_or_after(pos + (wend - pos) * (t + 1) / T);
-        if (s < e) index_segment(s, e, per[t]);
-      });
-      recs.clear();
-      for (unsigned t = 0; t < T; ++t) recs.insert(recs.end(), per[t].begin(), per[t].end());
-      if (recs.empty()) break;  // only an unterminated header line was left
-      pos = recs.back().end;
+      if (fastq_) {  // indexed and verified as a whole by the constructor
+        recs.swap(fq_recs_);
+        pos = size_;
+        if (recs.empty()) break;
+      } else {
+        const uint64_t wend = std::min(size_, pos + window_);
+        const unsigned T = unsigned(std::min<uint64_t>(threads_, std::max<uint64_t>((wend - pos) / min_segment_, 1)));
+        parallel(T, [&](unsigned t) {
+          per[t].clear();
+          const uint64_t s = t == 0 ? pos : line_start_at_or_after(pos + (wend - pos) * t / T);
+          const uint64_t e = t + 1 == T ? wend : line_start_at_or_after(pos + (wend - pos) * (t + 1) / T);
+          if (s < e) index_segment(s, e, per[t]);
+        });
+        recs.clear();
+        for (unsigned t = 0; t < T; ++t) recs.insert(recs.end(), per[t].begin(), per[t].end());
+        if (recs.empty()) break;  // only an unterminated header line was left
+        pos = recs.back().end;
+      }
       // cut the window's records into batches and fill them
       size_t i0 = 0;
       while (i0 < recs.size()) {

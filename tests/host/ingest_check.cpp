@@ -1,6 +1,6 @@
 // tests/host/ingest_check.cpp -- the multi-threaded FASTA ingest (links_b200/csrc/host/fasta_ingest.hpp) against the
 // serial reader (seq_stream.hpp) on the same file: same records, same order, same ordinals.  CPU only.
-//   ingest_check <file> <threads> <cap_bytes> <window_bytes> <max_records>
+//   ingest_check <file> <threads> <cap_bytes> <window_bytes> <max_records> [min_segment_bytes]
 // prints "OK <records> <bases>" / "FALLBACK" (file is not plain FASTA) / "ERROR <what>" / "MISMATCH ..."
 #include <cstdio>
 #include <cstdlib>
@@ -34,7 +34,7 @@ int main(int argc, char** argv)
       });
     } catch (const std::exception& e) { serial_err = e.what(); }
   }
-  links_host::ParallelFastaIngest ing(path, threads);
+  links_host::ParallelFastaIngest ing(path, threads, argc > 6 ? uint64_t(atoll(argv[6])) : (1u << 16));
   if (!ing.usable()) { printf("FALLBACK\n"); return 0; }
   ing.set_window_bytes(window);
   std::vector<char> b0(cap), b1(cap);

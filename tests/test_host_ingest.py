@@ -40,8 +40,8 @@ def _fasta(rng, n_records, max_len, width, crlf=False, blank=0.0, empty=0.0, fin
     return data
 
 
-def _check(exe, path, threads, cap, window, max_records=1 << 20):
-    r = subprocess.run([exe, path, str(threads), str(cap), str(window), str(max_records)], capture_output=True, text=True)
+def _check(exe, path, threads, cap, window, max_records=1 << 20, min_segment=1 << 16):
+    r = subprocess.run([exe, path, str(threads), str(cap), str(window), str(max_records), str(min_segment)], capture_output=True, text=True)
     assert r.returncode == 0, r.stdout + r.stderr
     return r.stdout.split()
 
@@ -72,7 +72,11 @@ def test_parallel_ingest_edges(ingest_check, tmp_path):
     assert run(b">a\nAC\n>b\n>c\n\n\nGT\n>d") == ["OK", "3", "4"]          # empty record kept; unterminated last header is no record
     assert run(b"\n\n>a\nACGT") == ["OK", "1", "4"]                         # leading blank lines, no final newline
     assert run(b">only header\n") == ["OK", "1", "0"]
-    assert run(b"@r\nACGT\n+\nIIII\n") == ["FALLBACK"]                      # FASTQ stays with the serial reader
+    assert run(b"@r\nACGT\n+\nIIII\n") == ["OK", "1", "4"]                  # strict four-line FASTQ is taken
+    assert run(b"@r\nACGT\nAC\n+\nIIIIII\n") == ["FALLBACK"]               # wrapped FASTQ stays with the serial reader
+    assert run(b"@r\nACGT\n+\nIII\n") == ["FALLBACK"]                       # so does a truncated quality line
+    assert run(b"@r\n\n+\n\n@s\nA\n+\nI\n") == ["FALLBACK"]                # and an empty sequence
+    assert run(b"@r\nACGT\n+\nIIII\n>x\nAC\n") == ["FALLBACK"]              # and a file that changes format
     assert run(b">a\nACGT\n", name="e.fa.gz") == ["FALLBACK"]               # so do compressed inputs (by suffix, as btllib decides)
     assert run(b"") == ["FALLBACK"]
     assert run(b">a\n" + b"A" * 2000 + b"\n", cap=1000) == ["ERROR", "both"]  # one record larger than the staging buffer
@@ -80,3 +84,48 @@ def test_parallel_ingest_edges(ingest_check, tmp_path):
     assert run(b">a\nAC>GT\n>b\nA\n") == ["OK", "2", "6"]
     # max_records = 3 cuts batches by count
     assert run(b"".join(b">%d\nA\n" % i for i in range(10)), cap=1000, window=1 << 20) == ["OK", "10", "10"]
+
+
+def _fastq(rng, n_records, max_len, crlf=False, final_newline=True, trailing_blank=0) -> bytes:
+    nl = b"\r\n" if crlf else b"\n"
+    out = []
+    bases = np.frombuffer(b"ACGTacgtN", np.uint8)
+    quals = np.frombuffer(b"@+@+!I5>#", np.uint8)  # quality lines that start with '@' or '+' are the hard case
+    for i in range(n_records):
+        n = int(rng.integers(1, max_len + 1))
+        out += [b"@r%d/1 @+" % i, nl, bases[rng.integers(0, len(bases), n)].tobytes(), nl, b"+" + (b"r%d" % i if i % 3 == 0 else b""), nl,
+                quals[rng.integers(0, len(quals), n)].tobytes(), nl]
+    data = b"".join(out)
+    if not final_newline:
+        data = data[:-len(nl)]
+    return data + nl * trailing_blank
+
+
+@pytest.mark.parametrize("seed", range(6))
+def test_parallel_fastq_ingest_equals_serial_reader(ingest_check, tmp_path, seed):
+    rng = np.random.default_rng(100 + seed)
+    data = _fastq(rng, n_records=int(rng.integers(1, 300)), max_len=int(rng.choice([3, 40, 5000])), crlf=bool(seed % 2),
+                  final_newline=bool(seed % 3), trailing_blank=2 if seed == 4 else 0)  # (CRLF blank lines are an error to the serial reader)
+    p = str(tmp_path / "x.fq")
+    open(p, "wb").write(data)
+    expect = None
+    for threads in (1, 3, 8, 16):
+        for min_segment in (1, 7, 64, 1 << 16):  # 1: as many pieces as threads, cut anywhere -- also inside quality lines
+            for cap in (5001, 1 << 22):
+                got = _check(ingest_check, p, threads, cap, 1 << 20, min_segment=min_segment)
+                assert got[0] in ("OK", "FALLBACK"), got  # FALLBACK (serial reader) is always correct; OK must agree with it
+                if got[0] == "OK":
+                    expect = expect or got
+                    assert got == expect
+    assert expect is not None  # at least the one-piece run must have taken the parallel path
+
+
+def test_parallel_fastq_on_the_golden_fastq_input(ingest_check, tmp_path):
+    """tests/golden/adv_offset_k20 has FASTQ reads: the file LINKS_CPP gets in the GPU test."""
+    from .conftest import GoldenCase
+    c = GoldenCase("adv_offset_k20")
+    _cp, fof = c.materialize(str(tmp_path))
+    for path in open(fof).read().split():
+        if open(path, "rb").read(1) == b"@":
+            for min_segment in (1 << 16, 1000):
+                assert _check(ingest_check, path, 8, 1 << 22, 1 << 20, min_segment=min_segment)[0] == "OK"
