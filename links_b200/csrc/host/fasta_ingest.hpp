@@ -75,8 +75,11 @@ public:
   void set_window_bytes(uint64_t w) { window_ = std::max<uint64_t>(w, 1); }  // tests shrink it to exercise the seams
 
   // Streams every record to `sink` in batches of at most cap bytes / max_records records, alternating between
-  // buf[0] and buf[1].  Returns the number of records.  Throws std::runtime_error for a record larger than cap.
-  uint64_t run(char* const buf[2], size_t cap, size_t max_records, uint64_t first_ordinal, const Sink& sink);
+  // buf[0] and buf[1].  Returns the number of records.  A record larger than cap: `grow(need)` is called with no batch
+  // in flight and may replace buf[0], buf[1] and cap by larger buffers (returning true); without it, or if it returns
+  // false, std::runtime_error is thrown.
+  using Grow = std::function<bool(size_t need, char* buf[2], size_t& cap)>;
+  uint64_t run(char* buf[2], size_t& cap, size_t max_records, uint64_t first_ordinal, const Sink& sink, const Grow& grow = nullptr);
 
 private:
   struct Rec { uint64_t seq_begin, end, len; };  // file span of the sequence lines, bases in them
@@ -241,7 +244,7 @@ inline void ParallelFastaIngest::copy_record(const Rec& r, char* dst) const
   }
 }
 
-inline uint64_t ParallelFastaIngest::run(char* const buf[2], size_t cap, size_t max_records, uint64_t first_ordinal, const Sink& sink)
+inline uint64_t ParallelFastaIngest::run(char* buf[2], size_t& cap, size_t max_records, uint64_t first_ordinal, const Sink& sink, const Grow& grow)
 {
   if (!usable_) throw std::runtime_error("ParallelFastaIngest: " + path_ + " is not a plain FASTA file");
   // pusher thread: takes filled buffers in order
@@ -318,7 +321,16 @@ inline uint64_t ParallelFastaIngest::run(char* const buf[2], size_t cap, size_t 
           if (j.off.back() + recs[i].len > cap) break;
           j.off.push_back(j.off.back() + recs[i].len);
         }
-        if (i == i0) throw std::runtime_error("record larger than the staging buffer in " + path_);
+        if (i == i0) {  // this record alone does not fit: wait for the pushes in flight, then ask for larger buffers
+          {
+            std::unique_lock<std::mutex> lk(mu);
+            cv.wait(lk, [&] { return (!busy[0] && !busy[1] && queue.empty()) || !error.empty(); });
+            if (!error.empty()) throw std::runtime_error(error);
+          }
+          if (!grow || !grow(size_t(recs[i0].len), buf, cap) || recs[i0].len > cap)
+            throw std::runtime_error("record larger than the staging buffer in " + path_);
+          continue;
+        }
         j.b = next_buf;
         j.first = ordinal;
         {

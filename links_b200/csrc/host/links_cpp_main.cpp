@@ -16,6 +16,7 @@
 #include <chrono>
 #include <cinttypes>
 #include <cstdlib>
+#include <cstring>
 #include <fstream>
 #include <getopt.h>
 #include <iostream>
@@ -261,8 +262,8 @@ int main(int argc, char** argv)
   // two pinned staging buffers shared by the contig and read streams: while one is on its way to the device
   // the ingest threads fill the other.  No larger than the largest input needs (pinning memory is not free).
   size_t stage_mb = 64;  // x2; pinning costs ~0.35 ms per MB, and 64 MB batches already keep the device busy (profiles/r01zb_e2e_binary_c2.json)
-  if (const char* e = getenv("LINKS_STAGE_MB")) stage_mb = std::max<size_t>(size_t(atoll(e)), 1);
   size_t stage_cap = stage_mb << 20;
+  if (const char* e = getenv("LINKS_STAGE_MB")) stage_cap = std::max<size_t>(size_t(strtod(e, nullptr) * double(1 << 20)), 4096);  // fractions allowed
   {
     uint64_t need = 0;
     bool known = true;
@@ -285,6 +286,21 @@ int main(int argc, char** argv)
   links_host::SeqBatch batch;
   batch.cap = stage_cap;
   batch.seq = stage[0];
+  // One record longer than a staging buffer (a chromosome-scale contig): both buffers are replaced by larger ones.  Both
+  // readers call this with no push in flight; `keep` bytes at the start of stage[0] (the serial reader's open record) survive.
+  auto grow_stage = [&](size_t need, size_t keep) -> bool {
+    const size_t ncap = ((std::max(need + need / 4, stage_cap * 2) >> 20) + 1) << 20;
+    char* a = static_cast<char*>(links_host_alloc(ncap));
+    char* b = a ? static_cast<char*>(links_host_alloc(ncap)) : nullptr;
+    if (!a || !b) { if (a) links_host_free(a); return false; }
+    if (keep) memcpy(a, stage[0], keep);
+    links_host_free(stage[0]);
+    links_host_free(stage[1]);
+    stage[0] = a; stage[1] = b; stage_cap = ncap;
+    batch.seq = a; batch.cap = ncap;
+    return true;
+  };
+  batch.grow = [&](links_host::SeqBatch&, size_t need, size_t keep) { return grow_stage(need, keep); };
   // One input file -> batches for push(seq, off, n, first_ordinal); returns the records read.  Plain FASTA goes
   // through the multi-threaded reader; FASTQ, compressed inputs and pipes through the serial
   // one, exactly as before.  A batch never spans two files.
@@ -292,7 +308,9 @@ int main(int argc, char** argv)
                     const std::function<void(const char*, const uint64_t*, size_t, uint64_t)>& push) -> uint64_t {
     if (host_threads > 1) {
       links_host::ParallelFastaIngest par(path, host_threads);
-      if (par.usable()) return par.run(stage, stage_cap, max_records, first_ordinal, push);
+      if (par.usable())
+        return par.run(stage, stage_cap, max_records, first_ordinal, push,
+                       [&](size_t need, char**, size_t&) { return grow_stage(need, 0); });  // (stage / stage_cap are the very objects run() holds)
     }
     batch.clear(first_ordinal);
     return links_host::stream_file(path, batch, max_records, true,

@@ -23,6 +23,9 @@ struct SeqBatch {
   size_t cap = 0;               // bytes available in seq
   std::vector<uint64_t> off;    // n+1 offsets into seq
   uint64_t first_ordinal = 0;   // ordinal of record 0 of this batch
+  // optional: called when ONE record needs more than cap bytes (the batch then holds nothing but the first `keep` bytes
+  // of that record at seq[0..keep)); it may point seq at a larger buffer holding the same bytes and raise cap
+  std::function<bool(SeqBatch&, size_t need, size_t keep)> grow;
   size_t n() const { return off.empty() ? 0 : off.size() - 1; }
   size_t bytes() const { return off.empty() ? 0 : size_t(off.back()); }
   void clear(uint64_t next_ordinal)
@@ -105,13 +108,14 @@ inline uint64_t stream_file(const std::string& path, SeqBatch& batch, size_t max
   };
   auto append = [&](const char* p, size_t n) {
     if (batch.bytes() + cur_len + n > batch.cap) {
-      // move the open record to the front of a fresh batch
-      if (batch.n() == 0) throw std::runtime_error("record larger than the staging buffer in " + path);
-      const uint64_t start = batch.off.back();
-      flush(batch);
-      memmove(batch.seq, batch.seq + start, cur_len);
-      batch.clear(ordinal_next());
-      if (cur_len + n > batch.cap) throw std::runtime_error("record larger than the staging buffer in " + path);
+      if (batch.n() > 0) {  // move the open record to the front of a fresh batch
+        const uint64_t start = batch.off.back();
+        flush(batch);
+        memmove(batch.seq, batch.seq + start, cur_len);
+        batch.clear(ordinal_next());
+      }
+      if (cur_len + n > batch.cap && (!batch.grow || !batch.grow(batch, cur_len + n, cur_len) || cur_len + n > batch.cap))
+        throw std::runtime_error("record larger than the staging buffer in " + path);
     }
     memcpy(batch.seq + batch.off.back() + cur_len, p, n);
     cur_len += n;

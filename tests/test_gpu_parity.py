@@ -424,7 +424,7 @@ def test_peer_memory_exchange_equals_single_context(gpu_lib, name, n_ranks, inbo
 
 
 @pytest.mark.parametrize("name,host_threads", [("c1", None), ("adv_offset_k20", None), ("adv_ns_lower", None), ("adv_ns_lower", "1"),
-                                               ("adv_tandem", "5"), ("c1", "bf-blocks"), ("adv_k40", "layout-in-process")])
+                                               ("adv_tandem", "5"), ("c1", "bf-blocks"), ("adv_k40", "layout-in-process"), ("c1", "stage-grows"), ("c1", "stage-grows-serial")])
 def test_links_cpp_binary_writes_reference_files(gpu_lib, tmp_path, name, host_threads):
     """The C++ host LINKS_CPP, run as the reference binary is run (bin/LINKS-make:121-122): same
     options in, byte-identical .bloom, and .tigpair_checkpoint.tsv / .pairing_issues equal to the
@@ -440,6 +440,9 @@ def test_links_cpp_binary_writes_reference_files(gpu_lib, tmp_path, name, host_t
     if name == "c1":
         env["LINKS_STAGE_MB"] = "8"  # its single 1 Mbp read must fit
     lay_meta = None
+    if host_threads in ("stage-grows", "stage-grows-serial"):  # the 1 Mbp read does not fit 0.25 MB: the staging buffers are replaced by larger ones
+        env["LINKS_STAGE_MB"] = "0.25"
+        host_threads = "1" if host_threads.endswith("serial") else None
     if host_threads == "layout-in-process":  # LINKS_CPP_LAYOUT=1: the layout stage runs inside LINKS_CPP on the rows still in memory
         import json
         lay_meta = json.load(open(os.path.join(GOLDEN_DIR, name, "layout", "layout.json")))

@@ -40,8 +40,9 @@ def _fasta(rng, n_records, max_len, width, crlf=False, blank=0.0, empty=0.0, fin
     return data
 
 
-def _check(exe, path, threads, cap, window, max_records=1 << 20, min_segment=1 << 16):
-    r = subprocess.run([exe, path, str(threads), str(cap), str(window), str(max_records), str(min_segment)], capture_output=True, text=True)
+def _check(exe, path, threads, cap, window, max_records=1 << 20, min_segment=1 << 16, grow=False):
+    r = subprocess.run([exe, path, str(threads), str(cap), str(window), str(max_records), str(min_segment)] + (["grow"] if grow else []),
+                       capture_output=True, text=True, env=dict(os.environ, **({"INGEST_CHECK_VERBOSE": "1"} if grow else {})))
     assert r.returncode == 0, r.stdout + r.stderr
     return r.stdout.split()
 
@@ -129,3 +130,26 @@ def test_parallel_fastq_on_the_golden_fastq_input(ingest_check, tmp_path):
         if open(path, "rb").read(1) == b"@":
             for min_segment in (1 << 16, 1000):
                 assert _check(ingest_check, path, 8, 1 << 22, 1 << 20, min_segment=min_segment)[0] == "OK"
+
+
+@pytest.mark.parametrize("fmt", ["fasta", "fastq", "fastq-wrapped"])
+def test_a_record_larger_than_the_staging_buffer_grows_it(ingest_check, tmp_path, fmt):
+    """A chromosome-scale contig must not depend on LINKS_STAGE_MB: both readers ask for larger buffers (LINKS_CPP's grow_stage)
+    and carry on -- records before and after the long one included, the serial reader keeping the part it had already copied."""
+    rng = np.random.default_rng(7)
+    alphabet = np.frombuffer(b"ACGT", np.uint8)
+    lens = [50, 900, 30000, 120, 70000, 10]
+    seqs = [alphabet[rng.integers(0, 4, n)].tobytes() for n in lens]
+    if fmt == "fasta":
+        data = b"".join(b">r%d\n" % i + b"\n".join(s[j:j + 70] for j in range(0, len(s), 70)) + b"\n" for i, s in enumerate(seqs))
+    elif fmt == "fastq":
+        data = b"".join(b"@r%d\n" % i + s + b"\n+\n" + b"I" * len(s) + b"\n" for i, s in enumerate(seqs))
+    else:  # wrapped FASTQ: the serial reader's job
+        wrap = lambda x: b"\n".join(x[j:j + 100] for j in range(0, len(x), 100))  # noqa: E731
+        data = b"".join(b"@r%d\n" % i + wrap(s) + b"\n+\n" + wrap(b"I" * len(s)) + b"\n" for i, s in enumerate(seqs))
+    p = str(tmp_path / ("x.fa" if fmt == "fasta" else "x.fq"))
+    open(p, "wb").write(data)
+    want = (["FALLBACK"] if fmt == "fastq-wrapped" else ["OK"]) + ["6", str(sum(lens))]
+    assert _check(ingest_check, p, 4, 1000, 1 << 20, min_segment=1000, grow=True) == want
+    if fmt != "fastq-wrapped":
+        assert _check(ingest_check, p, 4, 1000, 1 << 20, min_segment=1000, grow=False) == ["ERROR", "both"]
