@@ -139,6 +139,19 @@ int links_contigs_push(links_ctx* ctx, const char* seq, const uint64_t* off, uin
 /* Same, with the concatenated ASCII already resident in device memory (offsets stay on the host). */
 int links_contigs_push_dev(links_ctx* ctx, const void* dev_seq, const uint64_t* off, uint32_t n, uint32_t first_tig_id);
 
+/* The contig k-mer table (LINKS::track_all_test, src/LINKS.hpp:379-402) comes in two builds with identical results:
+ *   FULL   every contig k-mer, built on a side stream while the reads are processed (64 bytes per contig position);
+ *   MATES  only the hashes that occur in a distinct pair -- the reference's own rule, populate_mate_info stores a contig
+ *          k-mer only `if (mates.find(hash) != mates.end())` (src/LINKS.hpp:580,591) -- built by links_finalize once the
+ *          pairs are known (at most ~50 bytes per distinct pair, whatever the assembly's size; with an attached
+ *          exchange: per distinct pair this rank OWNS).
+ * AUTO (default; LINKS_TABLE_MODE=auto|full|mates overrides at links_create) takes FULL while that table is under an
+ * eighth of the device's memory.  Call before the job's first links_reads_push; the choice survives links_reset. */
+#define LINKS_TABLE_AUTO 0
+#define LINKS_TABLE_FULL 1
+#define LINKS_TABLE_MATES 2
+int links_table_mode(links_ctx* ctx, int mode);
+
 /* ---- stage 2: reads.  Replaces start_read_fasta / extract_mate_pair / write_from_block_to_map
  * (src/LINKS.hpp:354-378,470-486,515-567,602-638).  first_read_idx = ordinal of record 0 over
  * all files of the .fof (defines first-wins order when n_dist > 1). */

@@ -73,6 +73,7 @@ SIGNATURES = {
     "links_sync": (C.c_int, [C.c_void_p]),
     "links_set_stream": (C.c_int, [C.c_void_p, C.c_void_p]),
     "links_reset": (C.c_int, [C.c_void_p]),
+    "links_table_mode": (C.c_int, [C.c_void_p, C.c_int]),
     "links_contigs_push_dev": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint32, C.c_uint32]),
     "links_reads_push_dev": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint32, C.c_uint64]),
     "links_host_alloc": (C.c_void_p, [C.c_size_t]),

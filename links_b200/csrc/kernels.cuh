@@ -379,9 +379,58 @@ __device__ __forceinline__ uint64_t table_lookup(const TableView& tv, uint64_t h
   }
 }
 
+// ---- the table restricted to `mates` (reference src/LINKS.hpp:374-375: mates = every h_a, h_b of mate_pair;
+// populate_mate_info :580,591 keeps a contig k-mer only if its hash is in there).  Same slots, two steps:
+//   table_seed    every hash the (owned) pairs refer to claims a slot {h, 0}: "a mate, not seen in a contig yet"
+//   table_update  a contig k-mer whose hash has a slot fills it in (first occurrence) or marks it multiple;
+//                 a hash without a slot is no mate and leaves no trace
+// classify's table_lookup then reads val = 0 for an absent mate -> the default KmerInfo, as in the full table.
+// Size is bounded by twice the distinct pairs instead of twice the genome (3.1 Gbp: 198 GB full, replicated).
+__device__ __forceinline__ void table_seed(const TableView& tv, uint64_t h)
+{
+  if (h == kEmpty) return;  // owns the extra slot [cap], which always exists
+  uint64_t i = slot_hash1(h) >> tv.shift;
+  for (;;) {
+    ulonglong2 cur = __ldcg(reinterpret_cast<const ulonglong2*>(&tv.slots[i]));
+    if (cur.x == kEmpty) cur = cas128_raw(&tv.slots[i], make_ulonglong2(kEmpty, 0ull), make_ulonglong2(h, 0ull));  // (a stale "empty" is settled by the CAS)
+    if (cur.x == kEmpty || cur.x == h) return;
+    i = (i + 1) & tv.mask;
+  }
+}
+
+__device__ __forceinline__ void table_update(const TableView& tv, uint64_t h, uint64_t payload)
+{
+  if (h == kEmpty) { table_insert(tv, h, payload); return; }
+  uint64_t i = slot_hash1(h) >> tv.shift;
+  for (;;) {
+    // keys are final (seeded by the previous kernel); values move 0 -> payload|1 -> |2 only
+    ulonglong2 s = __ldcg(reinterpret_cast<const ulonglong2*>(&tv.slots[i]));
+    if (s.x == h) {
+      if (s.y == 0ull) {
+        s = cas128_raw(&tv.slots[i], make_ulonglong2(h, 0ull), make_ulonglong2(h, payload | 1ull));
+        if (s.y == 0ull) return;  // first of this hash: (tig,pos,orient)
+      }
+      if (!(s.y & 2ull)) atomicOr(reinterpret_cast<unsigned long long*>(&tv.slots[i].val), 2ull);  // seen again: multiple (ref :398-400)
+      return;
+    }
+    if (s.x == kEmpty) return;  // not in mates (ref :580,591)
+    i = (i + 1) & tv.mask;
+  }
+}
+
+__global__ void __launch_bounds__(kCtaThreads) table_seed_kernel(const ulonglong2* __restrict__ list, uint64_t n_pairs, TableView tv)
+{
+  for (uint64_t i = uint64_t(blockIdx.x) * blockDim.x + threadIdx.x; i < n_pairs; i += uint64_t(gridDim.x) * blockDim.x) {
+    const ulonglong2 hk = __ldg(list + i);
+    table_seed(tv, hk.x);
+    table_seed(tv, hk.y);
+  }
+}
+
 // MODE 0: Bloom insert (KmerBloomFilter::insert, bloom_filter.hpp:814-821) + member-set insert (mv.buckets != nullptr)
 // MODE 1: table insert of fwd and rev hash of every valid position (populate_mate_info, :577-598)
 // MODE 2: member-set insert only (the filter's bits came from links_bf_load*, the caller vouches they cover these contigs)
+// MODE 3: update of the table restricted to `mates` (table_update): only hashes that already own a slot are recorded
 // A filter far larger than L2 is built in several passes over the contigs (MODE 0): a pass sets only the bits whose
 // 32-bit word lies in [w_lo, w_hi), so its atomics stay in L2 (3.2 G positions/s with a DRAM-resident 180 MB filter
 // against 21 G/s when the filter fits); the member set is filled by the first pass only.  One pass = {0, ~0, 1}.
@@ -415,6 +464,11 @@ __global__ void __launch_bounds__(kCtaThreads) contig_kernel(ContigBatch cb, int
         if (bp.with_set && mv.buckets) member_insert(mv, r < f ? r : f);
       } else if (MODE == 2) {
         member_insert(mv, r < f ? r : f);
+      } else if (MODE == 3) {
+        const uint64_t payload = (p << 32) | (uint64_t(cb.first_tig + c) << 3);
+        table_update(tv, f, payload);
+        table_update(tv, r, payload | 4ull);
+        n_kmers += 2;
       } else {
         const uint64_t payload = (p << 32) | (uint64_t(cb.first_tig + c) << 3);
         table_insert(tv, f, payload);
@@ -424,7 +478,7 @@ __global__ void __launch_bounds__(kCtaThreads) contig_kernel(ContigBatch cb, int
     }
     __syncthreads();
   }
-  if (MODE == 1) {
+  if (MODE == 1 || MODE == 3) {
     n_kmers = warp_sum_ull(n_kmers);
     if ((threadIdx.x & 31) == 0 && n_kmers) atomicAdd(&ctr->n_contig_kmers, n_kmers);
   }
@@ -468,14 +522,18 @@ __device__ __forceinline__ bool pair_insert(const PairView& pv, uint64_t a, uint
   }
 }
 
-// order key of a pair known to be present
+// order key of a pair known to be present.  L2 loads, not the read-only path: the incremental classify_kernel runs
+// beside an extract_kernel that is claiming slots of the same table and lowering order keys.  What it reads is still
+// final: a listed pair's slot never moves, the slots in front of it on its probe chain were occupied before it was
+// inserted, and its order key can only be lowered by a read with a smaller global ordinal, which classify_increment
+// rules out (reads arrive in increasing ordinal, else cls_valid is dropped).
 __device__ __forceinline__ uint64_t pair_okey(const PairView& pv, uint64_t a, uint64_t b)
 {
   uint64_t i = slot_hash2(a, b) >> pv.shift;
   for (;;) {
     const PairSlot* s = pv.slots + i;
-    const ulonglong2 cur = __ldg(reinterpret_cast<const ulonglong2*>(s));
-    if (cur.x == a && cur.y == b) return pv.okeys ? pv.okeys[i] : 0ull;
+    const ulonglong2 cur = __ldcg(reinterpret_cast<const ulonglong2*>(s));
+    if (cur.x == a && cur.y == b) return pv.okeys ? __ldcg(pv.okeys + i) : 0ull;
     if (cur.x == kEmpty && cur.y == kEmpty) return kEmpty; // not present (cannot happen for listed pairs)
     i = (i + 1) & pv.mask;
   }

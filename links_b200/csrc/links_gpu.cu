@@ -131,6 +131,10 @@ struct links_ctx {
   cudaEvent_t ev_table = nullptr, ev_fork = nullptr;
   size_t table_batches_built = 0;
   bool table_started = false;
+  // LINKS_TABLE_* (links_gpu.h): FULL = every contig k-mer, built beside the extraction; MATES = only the hashes the
+  // (owned) pairs refer to, built at finalize (reference src/LINKS.hpp:580,591); AUTO picks by the full table's size
+  int table_mode = LINKS_TABLE_AUTO;
+  bool table_mates = false;  // this job's choice
 
   // stage-4 scratch (kept across links_reset so repeated jobs do not re-allocate)
   DevBuf f_final;
@@ -972,6 +976,7 @@ int links_create(links_ctx** out, const links_params* p)
   CUC(c->d_cls.ensure(64));
   CUC(cudaMemset(c->d_cls.p, 0, 64));
   { const char* e = getenv("LINKS_INCREMENTAL_CLASSIFY"); c->cls_on = !(e && e[0] == '0'); c->cls_valid = c->cls_on; }
+  { const char* e = getenv("LINKS_TABLE_MODE"); c->table_mode = !e ? LINKS_TABLE_AUTO : !strcmp(e, "full") ? LINKS_TABLE_FULL : !strcmp(e, "mates") ? LINKS_TABLE_MATES : LINKS_TABLE_AUTO; }
   CUC(cudaEventCreateWithFlags(&c->ev_extracted, cudaEventDisableTiming));
   CUC(cudaEventCreateWithFlags(&c->ev_routed, cudaEventDisableTiming));
   CUC(cudaEventCreateWithFlags(&c->ev_imported, cudaEventDisableTiming));
@@ -1018,6 +1023,7 @@ int links_create(links_ctx** out, const links_params* p)
       cudaFuncAttributes fa;
       const void* fns[] = {(const void*)pack_kernel, (const void*)rank_build_kernel, (const void*)table_init_kernel,
                            (const void*)contig_kernel<0>, (const void*)contig_kernel<1>, (const void*)contig_kernel<2>,
+                           (const void*)contig_kernel<3>, (const void*)table_seed_kernel,
                            (const void*)pair_rehash_kernel, (const void*)classify_kernel, (const void*)mirror_expand_kernel,
                            (const void*)gather_rows_kernel, (const void*)pair_bucket_count_kernel, (const void*)pair_bucket_scatter_kernel,
                            (const void*)pair_import_kernel, (const void*)pair_export_kernel, (const void*)route_kernel,
@@ -1200,7 +1206,10 @@ static int contigs_push_impl(links_ctx* c, const char* seq, const uint8_t* dev_s
       }();
       const uint64_t n_words = (c->bf_bytes + 3) / 4;
       uint64_t passes = block_bytes && c->bf_bytes > block_bytes + block_bytes / 2 ? (c->bf_bytes + block_bytes - 1) / block_bytes : 1;
-      passes = std::min<uint64_t>(passes, 64);
+      // every pass hashes all k-mers again (~20 G positions/s with the atomics in L2) against ~3.2 G positions/s for one
+      // pass with DRAM-resident atomics: beyond six blocks the single pass is the cheaper one
+      static const uint64_t max_passes = []() { const char* e = getenv("LINKS_BF_MAX_PASSES"); return e ? strtoull(e, nullptr, 10) : 6ull; }();
+      if (passes > max_passes) passes = 1;
       for (uint64_t ps = 0; ps < passes; ++ps) {
         const BloomPass bp{n_words * ps / passes, ps + 1 == passes ? ~0ull : n_words * (ps + 1) / passes, ps == 0};
         contig_kernel<0><<<grid_for(c, b->n_tiles, 1, 8), kCtaThreads, k * 4 * sizeof(ulonglong2), c->s_compute>>>(
@@ -1291,7 +1300,9 @@ static int reads_push_impl(links_ctx* c, const char* seq, const uint8_t* dev_seq
   if (!c->bf_ready) return fail(c, LINKS_E_INVAL, "links_reads_push: no Bloom filter yet");
   if (c->finalized) return fail(c, LINKS_E_INVAL, "links_reads_push: context already finalized (links_reset first)");
   if (n == 0) return LINKS_OK;
-  if (first_read_idx + n >= (1ull << 28)) return fail(c, LINKS_E_LIMIT, "links_reads_push: more than 2^28 reads");
+  // the 64-bit order key (28 bits of read ordinal, 8 of distance index, 28 of k-mer rank) only exists with several distances
+  const bool okey_limits = c->prm.n_dist > 1;
+  if (okey_limits && first_read_idx + n >= (1ull << 28)) return fail(c, LINKS_E_LIMIT, "links_reads_push: more than 2^28 reads with several -d values");
   CU(c, cudaSetDevice(c->device));
   {
     const int rc = start_table_build(c);
@@ -1319,7 +1330,8 @@ static int reads_push_impl(links_ctx* c, const char* seq, const uint8_t* dev_seq
   for (uint32_t i = 0; i < n; ++i) {
     if (off[i + 1] < off[i]) return fail(c, LINKS_E_INVAL, "links_reads_push: offsets not monotone");
     const uint64_t len = off[i + 1] - off[i];
-    if (len >= (1ull << 28)) return fail(c, LINKS_E_LIMIT, "links_reads_push: read longer than 2^28-1");
+    if (okey_limits && len >= (1ull << 28)) return fail(c, LINKS_E_LIMIT, "links_reads_push: read longer than 2^28-1 with several -d values");
+    if (len >= (1ull << 32)) return fail(c, LINKS_E_LIMIT, "links_reads_push: read longer than 2^32-1");
     for (uint32_t di = 0; di < nd; ++di) total_cand += seg_count(len, di);
   }
   c->x_cand_hint = std::max(c->x_cand_hint, total_cand);
@@ -1366,6 +1378,15 @@ int links_reads_push_dev(links_ctx* c, const void* dev_seq, const uint64_t* off,
   return reads_push_impl(c, nullptr, static_cast<const uint8_t*>(dev_seq), off, n, first_read_idx);
 }
 
+int links_table_mode(links_ctx* c, int mode)
+{
+  if (!c) return LINKS_E_INVAL;
+  if (mode != LINKS_TABLE_AUTO && mode != LINKS_TABLE_FULL && mode != LINKS_TABLE_MATES) return fail(c, LINKS_E_INVAL, "links_table_mode: mode %d", mode);
+  if (c->table_started || c->table_mates) return fail(c, LINKS_E_INVAL, "links_table_mode: call before the job's first links_reads_push");
+  c->table_mode = mode;
+  return LINKS_OK;
+}
+
 int links_set_stream(links_ctx* c, void* cuda_stream)
 {
   if (!c) return LINKS_E_INVAL;
@@ -1390,7 +1411,7 @@ int links_reset(links_ctx* c)
   CU(c, cudaStreamSynchronize(c->s_cls));
   CU(c, cudaStreamSynchronize(c->s_import));
   host_mark(c, "reset: streams idle");
-  c->table_started = false; c->table_batches_built = 0;
+  c->table_started = false; c->table_batches_built = 0; c->table_mates = false;
   poll_snapshots(c);
   for (auto* b : c->contig_batches) c->contig_pool.push_back(b);
   c->contig_batches.clear();
@@ -1453,11 +1474,12 @@ int links_get_timing(links_ctx* c, links_timing* t, int reset)
   return LINKS_OK;
 }
 
+static uint64_t full_table_cap(const links_ctx* c);
+
 static int build_table(links_ctx* c, cudaStream_t st)
 {
   const uint32_t k = c->prm.k;
-  const uint64_t entries = c->contig_positions * 2;
-  const uint64_t cap = 1ull << log2_ceil(std::max<uint64_t>(entries * 2, 1ull << 10));
+  const uint64_t cap = full_table_cap(c);
   CU(c, c->d_table.ensure((cap + 1) * sizeof(TableSlot)));
   c->table_cap = cap;
   Span sp(c, F_TABLE, st);
@@ -1483,9 +1505,53 @@ static int build_table(links_ctx* c, cudaStream_t st)
 // arrives (call order of the reference: Bloom filter -> reads -> contigs; here the contigs come
 // with the filter).  Start it on the auxiliary stream at the first reads push so it runs under the
 // reads' H2D copies and extract launches instead of in front of stage 4.
+// The table restricted to `mates` (kernels.cuh table_seed / table_update): slots for the hashes of the n_pairs listed
+// pairs, then one pass over the resident contigs that fills in those slots only.
+static int build_table_mates(links_ctx* c, cudaStream_t st, uint64_t n_pairs)
+{
+  const uint32_t k = c->prm.k;
+  const uint64_t cap = 1ull << log2_ceil(std::max<uint64_t>(n_pairs * 2 * 10 / 6, 1ull << 10));  // <= 2 hashes per pair, load <= 0.6
+  CU(c, c->d_table.ensure((cap + 1) * sizeof(TableSlot)));
+  c->table_cap = cap;
+  Span sp(c, F_TABLE, st);
+  CU(c, cudaMemsetAsync(reinterpret_cast<char*>(c->d_ctr.p) + offsetof(Counters, n_contig_kmers), 0, sizeof(unsigned long long), st));
+  table_init_kernel<<<grid_for(c, cap + 1, 256 * 4, 16), 256, 0, st>>>(c->d_table.as<TableSlot>(), cap + 1);
+  c->launches++;
+  if (n_pairs) {
+    table_seed_kernel<<<grid_for(c, n_pairs, kCtaThreads, 8), kCtaThreads, 0, st>>>(c->d_pair_list.as<ulonglong2>(), n_pairs, table_view(c));
+    c->launches++;
+  }
+  for (auto* b : c->contig_batches) {
+    if (!b->n_tiles) continue;
+    ContigBatch cb{b->packed.as<uint32_t>(), b->inv.as<uint32_t>(), b->off.as<uint64_t>(), b->base0,
+                   b->segs.as<uint32_t>(), b->n_seq, b->n_tiles, b->first_id};
+    contig_kernel<3><<<grid_for(c, b->n_tiles, 1, 8), kCtaThreads, k * 4 * sizeof(ulonglong2), st>>>(
+      cb, int(k), c->kseed, c->d_tab.as<ulonglong2>(), bloom_view(c), table_view(c), MemberView{nullptr, 0}, c->d_ctr.as<Counters>(),
+      BloomPass{0, ~0ull, 1});
+    c->launches++;
+  }
+  CU(c, cudaGetLastError());
+  return LINKS_OK;
+}
+
+static uint64_t full_table_cap(const links_ctx* c)
+{
+  return 1ull << log2_ceil(std::max<uint64_t>(c->contig_positions * 4, 1ull << 10));  // 2 entries per position, load <= 0.5
+}
+
+// FULL costs 64 bytes per contig position whatever the reads are and is built while they stream in; MATES costs at most
+// ~50 bytes per distinct pair and is built after the last read.  AUTO keeps FULL while it is a small part of the device.
+static bool want_mates_table(const links_ctx* c)
+{
+  if (c->table_mode == LINKS_TABLE_FULL) return false;
+  if (c->table_mode == LINKS_TABLE_MATES) return true;
+  return (full_table_cap(c) + 1) * sizeof(TableSlot) > c->dev_total_mem / 8;
+}
+
 static int start_table_build(links_ctx* c)
 {
-  if (c->table_started || c->contig_batches.empty()) return LINKS_OK;
+  if (c->table_started || c->table_mates || c->contig_batches.empty()) return LINKS_OK;
+  if (want_mates_table(c)) { c->table_mates = true; return LINKS_OK; }
   CU(c, cudaEventRecord(c->ev_fork, c->s_compute));  // contig packs (and the counter reset) are ordered before
   CU(c, cudaStreamWaitEvent(c->s_aux, c->ev_fork, 0));
   int rc = build_table(c, c->s_aux);
@@ -1508,7 +1574,10 @@ int links_finalize(links_ctx* c, links_row** rows_out, uint64_t* n_rows_out, lin
   CU(c, cudaStreamSynchronize(c->s_copy));
   CU(c, cudaStreamWaitEvent(s, c->ev_cleared, 0));
   int rc = LINKS_OK;
-  if (c->table_started && c->table_batches_built == c->contig_batches.size()) {
+  if (!c->table_started && !c->table_mates && want_mates_table(c)) c->table_mates = true;  // no read was pushed
+  if (c->table_mates) {
+    // built below, once the (owned) pairs are all here
+  } else if (c->table_started && c->table_batches_built == c->contig_batches.size()) {
     CU(c, cudaStreamWaitEvent(s, c->ev_table, 0));
   } else {  // no read was pushed, or contigs arrived after the early build: (re)build here
     if (c->table_started) CU(c, cudaStreamSynchronize(c->s_aux));
@@ -1531,6 +1600,10 @@ int links_finalize(links_ctx* c, links_row** rows_out, uint64_t* n_rows_out, lin
   CU(c, cudaMemcpy(&h, c->d_ctr.p, sizeof h, cudaMemcpyDeviceToHost));
   const uint64_t n_unique = h.n_unique;
   if (n_unique >= (1ull << 32) - kSortTile) return fail(c, LINKS_E_LIMIT, "links_finalize: more than 2^32 unique pairs on one GPU");
+  if (c->table_mates) {
+    rc = build_table_mates(c, s, c->pair_cap ? n_unique : 0);
+    if (rc) return rc;
+  }
 
   const int tb = log2_ceil(uint64_t(c->n_tigs_seen) * 2 + 2);
   DevBuf (&d_keys)[2] = c->f_keys; DevBuf (&d_vals)[2] = c->f_vals;

@@ -246,6 +246,13 @@ class Links:
         """Vouch that a loaded filter was built from the contigs about to be pushed (links_gpu.h)."""
         self._check(self._lib.links_bf_covers_contigs(self._h, 1 if yes else 0))
 
+    TABLE_MODES = {"auto": 0, "full": 1, "mates": 2}
+
+    def table_mode(self, mode: str) -> None:
+        """Contig k-mer table build (links_gpu.h LINKS_TABLE_*): 'full', 'mates' (only hashes that occur in a pair,
+        reference src/LINKS.hpp:580,591) or 'auto'."""
+        self._check(self._lib.links_table_mode(self._h, self.TABLE_MODES[mode]))
+
     def set_stream(self, cuda_stream: int) -> None:
         self._check(self._lib.links_set_stream(self._h, cuda_stream))
 

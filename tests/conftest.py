@@ -21,7 +21,7 @@ if ROOT not in sys.path:
     sys.path.insert(0, ROOT)
 
 GOLDEN = os.path.join(ROOT, "tests", "golden")
-GOLDEN_CASES = sorted(d for d in os.listdir(GOLDEN) if not d.startswith("cfg_") and os.path.exists(os.path.join(GOLDEN, d, "case.json")))
+GOLDEN_CASES = sorted(d for d in os.listdir(GOLDEN) if not d.startswith(("cfg_", "full_")) and os.path.exists(os.path.join(GOLDEN, d, "case.json")))
 
 
 def pytest_configure(config):

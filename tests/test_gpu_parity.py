@@ -77,12 +77,14 @@ def test_bloom_contains_matches_oracle(gpu_lib, oracle):
     assert exp[-1000:].all() and not exp[:3000].all()
 
 
-def _run_gpu(c: GoldenCase, chunk_reads: int | None = None):
+def _run_gpu(c: GoldenCase, chunk_reads: int | None = None, table: str | None = None):
     from links_b200 import bf_size
     from links_b200.seqio import SeqSet
     contigs, reads = c.contigs(), c.reads()
     m, nbytes, h = bf_size(c.meta["contigs_file_bytes"], c.opts["p"])
     with _links(k=c.opts["k"], d=c.opts["d"], t=c.opts["t"], o=c.opts["o"], e=c.opts["e"]) as L:
+        if table:
+            L.table_mode(table)
         L.bf_alloc(nbytes, h)
         L.push_contigs(contigs)
         if chunk_reads is None:
@@ -105,15 +107,28 @@ def test_whole_path_matches_reference_goldens(gpu_lib, golden_case):
     assert stats["n_rows"] == golden_case.meta["n_rows"]
 
 
-def test_baseline_configs_match_reference(gpu_lib, config_case):
+def test_mates_table_matches_reference_goldens(gpu_lib, golden_case):
+    """The contig table restricted to the hashes that occur in a pair (LINKS_TABLE_MATES = the reference's own rule,
+    src/LINKS.hpp:580,591; what makes a 3.1 Gbp assembly fit) against the same goldens, one push and many."""
+    for chunk in (None, 3):
+        tsv, issues, stats, _ = _run_gpu(golden_case, chunk_reads=chunk, table="mates")
+        assert sort_lines(tsv) == golden_case.expected_tsv()
+        assert sort_issue_records(issues) == golden_case.expected_issues()
+        assert stats["n_rows"] == golden_case.meta["n_rows"]
+
+
+@pytest.mark.parametrize("table", ["full", "mates"])
+def test_baseline_configs_match_reference(gpu_lib, config_case, table):
     """BASELINE.json configs[2..4] (multi-distance with per-distance steps; k 20 d 5000 t 5; the step sweep
-    t = 1 ... 100 at d 10000) at a size the unmodified reference ran here: .bloom, tsv and issues bit-exact."""
+    t = 1 ... 100 at d 10000) at a size the unmodified reference ran here: .bloom, tsv and issues bit-exact,
+    with either build of the contig table."""
     from links_b200 import bf_size
     c = config_case
     contigs, reads = c.inputs()
     o = c.opts
     _m, nbytes, h = bf_size(c.meta["contigs_file_bytes"], o["p"])
     with _links(k=o["k"], d=o["d"], t=o["t"], o=o["o"], e=o["e"]) as L:
+        L.table_mode(table)
         L.bf_alloc(nbytes, h)
         L.push_contigs(contigs)
         L.push_reads(reads)
@@ -561,6 +576,45 @@ def test_full_size_properties(gpu_lib, oracle, name, scale, sample_reads):
     for key in ("n_candidates", "n_survivors", "n_unique_pairs", "ct_ok_pairs", "ct_problem_pairs", "ct_ok_contig",
                 "ct_iz_issues", "ct_illogical", "ct_gate_fail"):
         assert stats3[key] == ostats[key], key
+
+
+FULL_CASES = sorted(d[5:] for d in os.listdir(GOLDEN_DIR) if d.startswith("full_"))
+
+
+@pytest.mark.parametrize("name", FULL_CASES)
+def test_full_size_digests_match_reference(gpu_lib, name):
+    """BASELINE.json configs at their FULL size against the unmodified reference, bit for bit: tools/make_fullsize_golden.py
+    ran oracle/_ref/LINKS_CPP -j 1 on the same seeded inputs (C2: 75 M candidate pairs; C5's dense point -t 1: 175 M; C3:
+    789 M over three distances) and stored sha256 digests of the byte-sorted .tigpair_checkpoint.tsv, of the
+    record-sorted .pairing_issues and of the .bloom file, plus the counters of its PAIRED K-MER STATS block."""
+    import hashlib
+    import json
+
+    from links_b200 import bf_header, bf_size, synth
+    meta = json.load(open(os.path.join(GOLDEN_DIR, "full_" + name, "case.json")))
+    _g, contigs, reads, k, d, t = synth.make_config(meta["workload"], meta["scale"])
+    h_in = hashlib.sha256()
+    for a in (contigs.seq, contigs.off, reads.seq, reads.off):
+        h_in.update(memoryview(np.ascontiguousarray(a)))
+    assert h_in.hexdigest() == meta["inputs_sha256"], "links_b200.synth no longer reproduces the golden inputs"
+    o = meta["opts"]
+    assert (k, list(d), list(t)) == (o["k"], o["d"], o["t"])
+    _m, nbytes, h = bf_size(meta["contigs_file_bytes"], o["p"])
+    assert (_m, h) == (meta["bf_m_bits"], meta["bf_hash_num"])
+    with _links(k=k, d=d, t=t, o=o["o"], e=o["e"]) as L:
+        L.bf_alloc(nbytes, h)
+        L.push_contigs(contigs)
+        L.push_reads(reads)
+        hb = hashlib.sha256(bf_header(k, h, nbytes))
+        hb.update(memoryview(L.bf_bits()))
+        rows, issues, stats = L.finalize()
+        tsv, iss = L.format_rows(rows), L.format_issues(issues)
+    assert len(rows) == meta["n_rows"] and len(issues) == meta["n_issues"]
+    assert sha256(sort_lines(tsv)) == meta["tsv_sha256"]
+    assert sha256(sort_issue_records(iss)) == meta["issues_sha256"]
+    assert hb.hexdigest() == meta["bloom_sha256"]
+    for key, want in meta["stats"].items():  # the order-independent counters the reference prints (src/LINKS.hpp:985-1012)
+        assert stats[key] == want, key
 
 
 def test_bloom_filter_of_2_pow_31_bits_and_more(gpu_lib, oracle):
