@@ -88,8 +88,32 @@ def build_layout(force: bool = False) -> str:
     return LAYOUT_BIN
 
 
+SYNTHGEN_DIR = os.path.join(ROOT, "tools", "synthgen")
+SYNTHGEN_LIB = os.path.join(SYNTHGEN_DIR, "libsynth_gpu.so")
+
+
+def build_synthgen(force: bool = False) -> str:
+    """Device-side generator of the human-scale synthetic workload (bench / test infrastructure, its own library)."""
+    src = os.path.join(SYNTHGEN_DIR, "synth_gen.cu")
+    if force or not _newer(SYNTHGEN_LIB, [src]):
+        subprocess.run([_nvcc(), *NVCC_FLAGS, "-shared", "-o", SYNTHGEN_LIB, src], check=True)
+    return SYNTHGEN_LIB
+
+
+GATHER_PEAK_BIN = os.path.join(ROOT, "tools", "gather_peak")
+
+
+def build_tools(force: bool = False) -> None:
+    """Measurement probes under tools/ (random-sector gather ceiling)."""
+    src = os.path.join(ROOT, "tools", "gather_peak.cu")
+    if os.path.exists(src) and (force or not _newer(GATHER_PEAK_BIN, [src])):
+        subprocess.run([_nvcc(), *NVCC_FLAGS, "-o", GATHER_PEAK_BIN, src], check=True)
+
+
 def build_all(force: bool = False, verbose: bool = False) -> None:
     build_lib(force, verbose)
+    build_synthgen(force)
+    build_tools(force)
     build_host(force)
     build_layout(force)
 
