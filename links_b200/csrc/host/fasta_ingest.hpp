@@ -33,6 +33,8 @@
 #include <thread>
 #include <vector>
 
+#include "seq_stream.hpp"  // rstrip_len: the line rule both readers share
+
 namespace links_host {
 
 class ParallelFastaIngest {
@@ -144,8 +146,7 @@ inline void ParallelFastaIngest::index_segment(uint64_t s, uint64_t e, std::vect
     while (q < size_ && data_[q] != '>') {
       const void* nl = memchr(data_ + q, '\n', size_ - q);
       const uint64_t lend = nl ? uint64_t(static_cast<const char*>(nl) - data_) : size_;
-      uint64_t l = lend - q;
-      if (l && data_[lend - 1] == '\r') --l;
+      const uint64_t l = links_host::rstrip_len(data_ + q, lend - q);
       r.len += l;
       q = nl ? lend + 1 : size_;
     }
@@ -176,9 +177,8 @@ inline uint64_t ParallelFastaIngest::fastq_record_at_or_after(uint64_t s) const
 inline bool ParallelFastaIngest::index_fastq_segment(uint64_t p, uint64_t e, std::vector<Rec>& out, uint64_t& end_pos) const
 {
   auto stripped = [&](uint64_t b, uint64_t le, bool has_nl) -> uint64_t {  // line length without the '\r' of a CRLF
-    uint64_t l = le - b;
-    if (l && has_nl && data_[le - 1] == '\r') --l;
-    return l;
+    (void)has_nl;
+    return links_host::rstrip_len(data_ + b, le - b);
   };
   while (p < e && p < size_) {
     if (data_[p] != '@') {  // only blank lines may follow the last record
@@ -236,8 +236,7 @@ inline void ParallelFastaIngest::copy_record(const Rec& r, char* dst) const
   while (q < r.end) {
     const void* nl = memchr(data_ + q, '\n', r.end - q);
     const uint64_t lend = nl ? uint64_t(static_cast<const char*>(nl) - data_) : r.end;
-    uint64_t l = lend - q;
-    if (l && data_[lend - 1] == '\r') --l;
+    const uint64_t l = links_host::rstrip_len(data_ + q, lend - q);
     memcpy(dst, data_ + q, l);
     dst += l;
     q = nl ? lend + 1 : r.end;

@@ -7,6 +7,7 @@
 // keyed on the file suffix.  Records are delivered in BATCHES laid out exactly as
 // links_reads_push / links_contigs_push take them: one concatenated ASCII buffer + n+1 offsets.
 #pragma once
+#include <cctype>
 #include <cstdint>
 #include <cstdio>
 #include <cstdlib>
@@ -15,6 +16,9 @@
 #include <stdexcept>
 #include <string>
 #include <vector>
+
+#include <sys/wait.h>
+#include <unistd.h>
 
 namespace links_host {
 
@@ -48,6 +52,15 @@ inline std::string shell_quote(const std::string& s)
   return q + "'";
 }
 
+// length of [p, p+l) without its trailing whitespace: btllib's readers rtrim() the sequence after every line they append
+// (seq_reader_multiline_fasta_module.hpp:108,190,201; util.hpp:83-101: std::isspace), so blanks and tabs before the newline
+// never become bases, while blanks inside a line do (as invalid ones)
+inline size_t rstrip_len(const char* p, size_t l)
+{
+  while (l && std::isspace(static_cast<unsigned char>(p[l - 1]))) --l;
+  return l;
+}
+
 // Opens path directly or through a decompressor pipe; closes the right way.
 class ByteSource {
 public:
@@ -59,7 +72,11 @@ public:
     else if (ends_with(path, ".bz2")) tool = "bzip2 -dc";
     else if (ends_with(path, ".xz")) tool = "xz -dc";
     else if (ends_with(path, ".zst")) tool = "zstd -dc";
+    path_ = path;
     if (tool) {
+      // popen() succeeds whatever the file is: check it ourselves, as btllib's DataSource does before it forks
+      // (data_stream.hpp:112-118), and check the decompressor's exit status in finish()
+      if (access(path.c_str(), R_OK) != 0) throw std::runtime_error("cannot open " + path);
       const std::string cmd = std::string(tool) + " " + shell_quote(path);
       f_ = popen(cmd.c_str(), "r");
       piped_ = true;
@@ -74,12 +91,25 @@ public:
     if (piped_) pclose(f_); else fclose(f_);
   }
   size_t read(char* dst, size_t n) { return fread(dst, 1, n, f_); }
+  // after the last read: a decompressor that did not exit with status 0 (truncated or corrupt archive, missing tool)
+  // has delivered partial data -- an error, never a shorter input
+  void finish()
+  {
+    if (!f_) return;
+    FILE* f = f_;
+    f_ = nullptr;
+    if (!piped_) { fclose(f); return; }
+    const int st = pclose(f);
+    if (st == -1 || !WIFEXITED(st) || WEXITSTATUS(st) != 0)
+      throw std::runtime_error("decompressing " + path_ + " failed (exit status " + std::to_string(st == -1 ? -1 : WIFEXITED(st) ? WEXITSTATUS(st) : 128) + ")");
+  }
   ByteSource(const ByteSource&) = delete;
   ByteSource& operator=(const ByteSource&) = delete;
 
 private:
   FILE* f_ = nullptr;
   bool piped_ = false;
+  std::string path_;
 };
 
 // Parses one file, appending records to `batch`; calls flush(batch) whenever the batch is full
@@ -97,6 +127,7 @@ inline uint64_t stream_file(const std::string& path, SeqBatch& batch, size_t max
   uint64_t qual_left = 0;  // FASTQ: quality characters still to skip
   bool open_rec = false;
   bool line_start = true;
+  std::string pend_ws;     // trailing whitespace of a sequence line cut by the read buffer: bases only if the line goes on
 
   auto ordinal_next = [&]() { return batch.first_ordinal + batch.n(); };
   auto close_record = [&]() {
@@ -144,14 +175,19 @@ inline uint64_t stream_file(const std::string& path, SeqBatch& batch, size_t max
       switch (st) {
       case FA_SEQ:
       case FQ_SEQ: {
-        size_t l = len;
-        if (l && p[l - 1] == '\r') --l;
-        if (l) { open_rec = true; append(p, l); }
+        const size_t l = rstrip_len(p, len);
+        if (l) {
+          open_rec = true;
+          if (!pend_ws.empty()) { append(pend_ws.data(), pend_ws.size()); pend_ws.clear(); }
+          append(p, l);
+        }
+        if (nl) pend_ws.clear();                  // whitespace before the newline: dropped
+        else pend_ws.append(p + l, len - l);      // the line continues in the next buffer
         break;
       }
       case FQ_QUAL: {
         size_t l = len;
-        if (l && p[l - 1] == '\r' && nl) --l;
+        if (nl) l = rstrip_len(p, l);
         qual_left = l >= qual_left ? 0 : qual_left - l;
         break;
       }
@@ -170,6 +206,7 @@ inline uint64_t stream_file(const std::string& path, SeqBatch& batch, size_t max
       }
     }
   }
+  src.finish();
   if (open_rec && (st == FA_SEQ || st == FA_HEADER || st == FQ_SEQ || st == FQ_PLUS || st == FQ_QUAL)) close_record();
   if (flush_at_end && batch.n()) { flush(batch); batch.clear(ordinal_next()); }
   return n_records;

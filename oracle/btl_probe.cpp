@@ -7,6 +7,7 @@
 // (`make -C oracle ref`), into oracle/_ref/libbtl_probe.so.
 #include "btllib/bloom_filter.hpp"
 #include "btllib/nthash.hpp"
+#include "btllib/seq_reader.hpp"
 
 #include <cstdint>
 #include <cstring>
@@ -55,6 +56,24 @@ btl_bf_build(uint64_t bytes, unsigned hash_num, unsigned k, const char* seqs, co
     }
   }
   return nb;
+}
+
+// Read `path` with btllib::SeqReader exactly as LINKS opens its inputs (Flag::LONG_MODE, src/LINKS.hpp:415-419); for
+// record i (i < cap): lens[i] = bases, fnv[i] = FNV-1a of the sequence, nums[i] = record.num.  Returns the record count.
+uint64_t
+btl_read_records(const char* path, uint64_t cap, uint64_t* lens, uint64_t* fnv, uint64_t* nums)
+{
+  btllib::SeqReader reader(path, btllib::SeqReader::Flag::LONG_MODE);
+  uint64_t n = 0;
+  for (auto record : reader) {
+    if (n < cap) {
+      uint64_t h = 1469598103934665603ull;
+      for (unsigned char c : record.seq) h = (h ^ c) * 1099511628211ull;
+      lens[n] = record.seq.size(); fnv[n] = h; nums[n] = record.num;
+    }
+    ++n;
+  }
+  return n;
 }
 
 } // extern "C"

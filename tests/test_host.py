@@ -133,3 +133,80 @@ def test_links_cpp_cli_contract_without_gpu(tmp_path):
         r = subprocess.run([exe, "-f", str(fa), "-s", str(fof), "-b", str(tmp_path / "o")], capture_output=True, text=True)
         assert r.returncode == 1 and "no CPU path" in r.stderr
         assert "-d \n" in r.stdout.replace("-d  \n", "-d \n") and "-k 15" in r.stdout and "-t 2" in r.stdout
+
+
+def _btllib_records(path: str):
+    """(length, FNV-1a, ordinal) of every record as btllib::SeqReader (LONG_MODE) hands it to the reference."""
+    import ctypes as C
+    from oracle import oracle_py
+    if not os.path.exists(oracle_py.REF_PROBE):
+        pytest.skip("oracle/_ref/libbtl_probe.so not built (needs /root/reference at build time)")
+    lib = C.CDLL(oracle_py.REF_PROBE)
+    lib.btl_read_records.restype = C.c_uint64
+    lib.btl_read_records.argtypes = [C.c_char_p, C.c_uint64, C.c_void_p, C.c_void_p, C.c_void_p]
+    cap = 4096
+    lens, fnv, nums = (np.zeros(cap, np.uint64) for _ in range(3))
+    n = lib.btl_read_records(path.encode(), cap, lens.ctypes.data, fnv.ctypes.data, nums.ctypes.data)
+    assert n <= cap
+    return [(int(lens[i]), int(fnv[i]), int(nums[i])) for i in range(n)]
+
+
+def test_readers_follow_btllib_on_trailing_whitespace_and_fail_on_bad_archives(tmp_path):
+    """btllib rtrim()s the sequence after every line (all trailing whitespace, not just one CR); blanks INSIDE a line stay and
+    become invalid bases.  The serial reader, the multi-threaded reader and the Python reader must give the records the real
+    btllib::SeqReader gives.  A missing or truncated compressed input is an error, never a shorter input (btllib's DataSource
+    aborts; popen() alone would not notice)."""
+    import subprocess
+    from .conftest import ROOT
+    exe = str(tmp_path / "seq_stream_dump")
+    subprocess.run(["g++", "-std=c++17", "-O1", "-Wall", os.path.join(ROOT, "tests", "cpp", "seq_stream_dump.cpp"), "-o", exe], check=True)
+    chk = str(tmp_path / "ingest_check")
+    subprocess.run(["g++", "-O2", "-std=c++17", "-pthread", "-I", os.path.join(ROOT, "links_b200", "csrc", "host"),
+                    os.path.join(ROOT, "tests", "host", "ingest_check.cpp"), "-o", chk], check=True)
+    rng = np.random.default_rng(21)
+    alphabet = np.frombuffer(b"ACGTacgtN", np.uint8)
+    tails = [b"", b" ", b"\t", b" \t ", b"\r", b" \r", b"\t\t\r", b"\x0b", b"\x0c "]
+    out = []
+    for i in range(60):
+        out.append(b">r%d desc\n" % i)
+        if i == 0:
+            # btllib decides the format on the first 16 KB (seq_reader.hpp:168) and REJECTS a file with a blank or tab there
+            # (seq_reader_multiline_fasta_module.hpp:64-75, only CR is tolerated): the odd lines start after a clean 20 KB record
+            for _ in range(250):
+                out.append(alphabet[rng.integers(0, len(alphabet), 80)].tobytes() + b"\r\n")
+            continue
+        for _ in range(int(rng.integers(1, 5))):
+            line = alphabet[rng.integers(0, len(alphabet), int(rng.integers(1, 90)))].tobytes()
+            if rng.random() < 0.2:  # a blank in the middle of a line is data
+                cut = int(rng.integers(0, len(line) + 1))
+                line = line[:cut] + b" " + line[cut:]
+            if line[:1] == b" ":
+                line = b"A" + line
+            out.append(line + tails[int(rng.integers(0, len(tails)))] + b"\n")
+    fa = str(tmp_path / "ws.fa")
+    open(fa, "wb").write(b"".join(out))
+    want = _btllib_records(fa)
+    assert len(want) == 60 and [w[2] for w in want] == list(range(60))
+    s = read_seqfile(fa)
+    assert [(len(s.record(i)), _fnv1a(s.record(i)), i) for i in range(s.n)] == want
+    # serial reader, small read buffers do not exist as a knob: the 8 MB buffer sees whole lines here; the staging cap is varied
+    for cap in (1 << 15, 1 << 20):
+        rows = [ln.split("\t") for ln in subprocess.run([exe, str(cap), "7", fa], check=True, capture_output=True, text=True).stdout.split("\n") if ln]
+        assert [(int(r[1]), int(r[2], 16), int(r[0])) for r in rows] == want
+    # the multi-threaded reader against the serial one (ingest_check compares record by record)
+    for threads, window in ((1, 1 << 30), (3, 977), (8, 1)):
+        r = subprocess.run([chk, fa, str(threads), str(1 << 20), str(window), str(1 << 20), "64"], capture_output=True, text=True)
+        assert r.returncode == 0, r.stdout + r.stderr
+    # compressed inputs: missing file, truncated archive
+    gz = str(tmp_path / "ok.fa.gz")
+    with gzip.open(gz, "wb") as f:
+        f.write(b"".join(out) * 50)
+    ok = subprocess.run([exe, str(1 << 20), "100", gz], capture_output=True, text=True)
+    assert ok.returncode == 0 and len([ln for ln in ok.stdout.split("\n") if ln]) == 60 * 50
+    missing = subprocess.run([exe, str(1 << 20), "100", str(tmp_path / "nope.fa.gz")], capture_output=True, text=True)
+    assert missing.returncode != 0 and "cannot open" in missing.stderr
+    data = open(gz, "rb").read()
+    cut = str(tmp_path / "cut.fa.gz")
+    open(cut, "wb").write(data[:len(data) // 2])
+    bad = subprocess.run([exe, str(1 << 20), "100", cut], capture_output=True, text=True)
+    assert bad.returncode != 0 and "decompressing" in bad.stderr
