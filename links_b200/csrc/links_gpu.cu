@@ -12,6 +12,8 @@
 #include "extract.cuh"
 #include "kernels.cuh"
 
+#include <nvtx3/nvToolsExt.h>  // header-only; ranges cost nothing unless a profiler (nsys, ncu --nvtx) is attached
+
 #include <algorithm>
 #include <cmath>
 #include <cstdarg>
@@ -262,15 +264,28 @@ cudaEvent_t get_event(links_ctx* c)
   return e;
 }
 
+// NVTX range over a C-ABI call or a phase of one (host side: what was enqueued where; the kernels show under it in nsys)
+struct NvtxRange {
+  explicit NvtxRange(const char* name) { nvtxRangePushA(name); }
+  ~NvtxRange() { nvtxRangePop(); }
+  NvtxRange(const NvtxRange&) = delete;
+  NvtxRange& operator=(const NvtxRange&) = delete;
+};
+
+const char* const kFamilyNames[F_COUNT] = {"links:h2d", "links:pack", "links:bloom_build", "links:table_build", "links:extract",
+                                           "links:classify", "links:sort_reduce", "links:d2h", "links:grow", "links:exchange"};
+
 struct Span {
   links_ctx* c; int fam; cudaStream_t s; cudaEvent_t a = nullptr;
   Span(links_ctx* c_, int fam_, cudaStream_t s_) : c(c_), fam(fam_), s(s_)
   {
+    nvtxRangePushA(kFamilyNames[fam]);
     if (c->timing) { a = get_event(c); cudaEventRecord(a, s); }
   }
   ~Span()
   {
     if (c->timing) { cudaEvent_t b = get_event(c); cudaEventRecord(b, s); c->spans.push_back({fam, a, b}); }
+    nvtxRangePop();
   }
 };
 
@@ -658,6 +673,8 @@ int ensure_owned(links_ctx* c, uint64_t min_cap)
   return LINKS_OK;
 }
 
+int classify_increment_owned(links_ctx* c);
+
 // s_import, after ev_routed: insert what has arrived (with `finish`: wait for every rank's "done" first)
 int exchange_import_round(links_ctx* c, bool finish)
 {
@@ -674,7 +691,7 @@ int exchange_import_round(links_ctx* c, bool finish)
     c->launches += 2;
   }
   CU(c, cudaGetLastError());
-  return LINKS_OK;
+  return finish ? LINKS_OK : classify_increment_owned(c);
 }
 
 // s_compute: route the new part of the dense pair list + publish; s_import: insert what has arrived
@@ -720,6 +737,7 @@ int exchange_after_routed_extract(links_ctx* c, bool finish)
 int exchange_settle(links_ctx* c)
 {
   if (c->x_settled) return LINKS_OK;
+  NvtxRange nvtx_("links:exchange_settle (wait for peers, last import)");
   if (!c->x_finished) return fail(c, LINKS_E_INVAL, "links_finalize: links_exchange_finish has not been called on this rank");
   ExchangeDev* x = c->d_xdev.as<ExchangeDev>();
   for (int attempt = 0;; ++attempt) {
@@ -740,6 +758,7 @@ int exchange_settle(links_ctx* c)
     }
     if (attempt) return fail(c, LINKS_E_CUDA, "pair exchange: owned set overflow after re-import");
     // the inbox still holds every record of this job: start over in a table sized for all of them
+    c->cls_valid = false;  // rows of the abandoned table are dropped: stage 4 runs once, from scratch, in links_finalize
     InboxHeader hdr;
     CU(c, cudaMemcpy(&hdr, inbox_half(h.inbox[c->x_lay.rank], c->x_lay, c->x_epoch), sizeof hdr, cudaMemcpyDeviceToHost));
     uint64_t total = 0;
@@ -769,6 +788,7 @@ int exchange_settle(links_ctx* c)
 // those arrays on rank 0, 0 elsewhere (the job's rows are delivered on rank 0).
 int exchange_rows(links_ctx* c, cudaStream_t s, uint32_t n, int key_bits, uint32_t* n_out)
 {
+  NvtxRange nvtx_("links:exchange_rows (partial link rows to rank 0)");
   ExchangeDev* x = c->d_xdev.as<ExchangeDev>();
   const InboxLayout& L = c->x_lay;
   if (n > L.row_cap) return fail(c, LINKS_E_LIMIT, "row exchange: %u rows, inbox has room for %llu per rank", n, (unsigned long long)L.row_cap);
@@ -863,6 +883,47 @@ int classify_increment(links_ctx* c)
     ClassifyParams cp{c->d_dist.as<uint32_t>(), c->d_minallowed.as<int32_t>(), c->prm.n_dist, c->f_tiglen.as<uint32_t>(), tb,
                       c->f_keys[0].as<uint64_t>(), c->f_vals[0].as<int32_t>(), c->cls_row_cap, c->f_issues.as<IssueRec>(), c->cls_issue_cap};
     classify_kernel<<<c->sm_count * 4, kCtaThreads, 0, c->s_cls>>>(pair_view(c), 0, table_view(c), cp, int(c->prm.k),
+                                                                   c->d_ctr.as<Counters>(), range);
+    range_advance_kernel<<<1, 1, 0, c->s_cls>>>(range);
+    c->launches += 2;
+  }
+  CU(c, cudaGetLastError());
+  CU(c, cudaEventRecord(c->ev_cls_done, c->s_cls));
+  return LINKS_OK;
+}
+
+// The same beside the imports of an attached exchange: after every import round the pairs it appended to the OWNED list are
+// classified on s_cls, so links_finalize is left with the last round's share instead of the whole owned set (the tail every
+// rank waits for).  Single distance only: with several, a pair's winning distance may still be lowered by a record of
+// another rank that arrives later.  Needs the full contig table (the one restricted to mates is seeded from the final list).
+int classify_increment_owned(links_ctx* c)
+{
+  if (!c->cls_valid || c->prm.n_dist > 1 || !c->owned_cap) return LINKS_OK;
+  if (!(c->table_started && c->table_batches_built == c->contig_batches.size())) return LINKS_OK;
+  if (!c->cls_started) {
+    c->cls_row_cap = pair_list_capacity(c->owned_cap);
+    c->cls_pair_cap = c->owned_cap;
+    c->cls_issue_cap = c->issue_cap_hint;
+    CU(c, c->f_keys[0].ensure(c->cls_row_cap * 8)); CU(c, c->f_vals[0].ensure(c->cls_row_cap * 4));
+    CU(c, c->f_issues.ensure(c->cls_issue_cap * sizeof(IssueRec)));
+    CU(c, c->f_tiglen.ensure(c->tig_len.size() * 4));
+    CU(c, cudaMemcpyAsync(c->f_tiglen.p, c->tig_len.data(), c->tig_len.size() * 4, cudaMemcpyHostToDevice, c->s_cls));
+    c->cls_started = true;
+  }
+  if (c->owned_cap != c->cls_pair_cap) { c->cls_valid = false; return LINKS_OK; }
+  unsigned long long* range = c->d_cls.as<unsigned long long>();
+  ExchangeDev* x = c->d_xdev.as<ExchangeDev>();
+  CU(c, cudaStreamWaitEvent(c->s_import, c->ev_cls_done, 0));  // the previous round still reads its upper bound
+  CU(c, cudaMemcpyAsync(range + 1, &x->n_owned, 8, cudaMemcpyDeviceToDevice, c->s_import));
+  CU(c, cudaEventRecord(c->ev_imported, c->s_import));
+  CU(c, cudaStreamWaitEvent(c->s_cls, c->ev_imported, 0));
+  CU(c, cudaStreamWaitEvent(c->s_cls, c->ev_table, 0));
+  {
+    Span sp(c, F_CLASSIFY, c->s_cls);
+    const int tb = log2_ceil(uint64_t(c->n_tigs_seen) * 2 + 2);
+    ClassifyParams cp{c->d_dist.as<uint32_t>(), c->d_minallowed.as<int32_t>(), c->prm.n_dist, c->f_tiglen.as<uint32_t>(), tb,
+                      c->f_keys[0].as<uint64_t>(), c->f_vals[0].as<int32_t>(), c->cls_row_cap, c->f_issues.as<IssueRec>(), c->cls_issue_cap};
+    classify_kernel<<<c->sm_count * 2, kCtaThreads, 0, c->s_cls>>>(owned_view(c), 0, table_view(c), cp, int(c->prm.k),
                                                                    c->d_ctr.as<Counters>(), range);
     range_advance_kernel<<<1, 1, 0, c->s_cls>>>(range);
     c->launches += 2;
@@ -1152,6 +1213,7 @@ int links_bf_download(links_ctx* c, uint8_t* dst)
 static int contigs_push_impl(links_ctx* c, const char* seq, const uint8_t* dev_seq, const uint64_t* off, uint32_t n,
                              uint32_t first_tig_id)
 {
+  NvtxRange nvtx_("links_contigs_push");
   if (!c || !off || (!seq && !dev_seq && n && off[n] != off[0])) return LINKS_E_INVAL;
   if (!c->bf_ready) return fail(c, LINKS_E_INVAL, "links_contigs_push: call links_bf_alloc or links_bf_load first");
   if (first_tig_id == 0) return fail(c, LINKS_E_INVAL, "links_contigs_push: contig ids are 1-based");
@@ -1296,6 +1358,7 @@ static int start_table_build(links_ctx* c);
 static int reads_push_impl(links_ctx* c, const char* seq, const uint8_t* dev_seq, const uint64_t* off, uint32_t n,
                            uint64_t first_read_idx)
 {
+  NvtxRange nvtx_("links_reads_push");
   if (!c || !off || (!seq && !dev_seq && n && off[n] != off[0])) return LINKS_E_INVAL;
   if (!c->bf_ready) return fail(c, LINKS_E_INVAL, "links_reads_push: no Bloom filter yet");
   if (c->finalized) return fail(c, LINKS_E_INVAL, "links_reads_push: context already finalized (links_reset first)");
@@ -1402,6 +1465,7 @@ int links_set_stream(links_ctx* c, void* cuda_stream)
 int links_reset(links_ctx* c)
 {
   if (!c) return LINKS_E_INVAL;
+  NvtxRange nvtx_("links_reset");
   CU(c, cudaSetDevice(c->device));
   host_mark(c, "reset: enter");
   CU(c, cudaStreamSynchronize(c->s_copy));
@@ -1568,6 +1632,7 @@ int links_finalize(links_ctx* c, links_row** rows_out, uint64_t* n_rows_out, lin
   *rows_out = nullptr; *n_rows_out = 0;
   if (issues_out) *issues_out = nullptr;
   if (n_issues_out) *n_issues_out = 0;
+  NvtxRange nvtx_("links_finalize");
   CU(c, cudaSetDevice(c->device));
   host_mark(c, "finalize: enter");
   cudaStream_t s = c->s_compute;
@@ -1609,7 +1674,7 @@ int links_finalize(links_ctx* c, links_row** rows_out, uint64_t* n_rows_out, lin
   DevBuf (&d_keys)[2] = c->f_keys; DevBuf (&d_vals)[2] = c->f_vals;
   DevBuf &d_issues = c->f_issues, &d_tiglen = c->f_tiglen, &d_scan_tmp = c->f_scan_tmp, &d_flags = c->f_flags,
          &d_total = c->f_total, &d_okeys = c->f_okeys, &d_olinks = c->f_olinks, &d_ogaps = c->f_ogaps;
-  const bool incremental = c->cls_valid && c->cls_started && !c->x_attached && c->pair_cap == c->cls_pair_cap;
+  const bool incremental = c->cls_valid && c->cls_started && c->pair_cap == c->cls_pair_cap;
   const uint64_t row_cap = incremental ? c->cls_row_cap : std::max<uint64_t>(n_unique, 1);
   uint64_t issue_cap = incremental ? c->cls_issue_cap : c->issue_cap_hint;
   CU(c, d_keys[0].ensure(row_cap * 8)); CU(c, d_vals[0].ensure(row_cap * 4));
@@ -2068,6 +2133,7 @@ int links_exchange_finish(links_ctx* c)
   if (!c) return LINKS_E_INVAL;
   if (!c->x_attached) return fail(c, LINKS_E_INVAL, "links_exchange_finish: no inbox attached");
   if (c->x_finished) return LINKS_OK;
+  NvtxRange nvtx_("links_exchange_finish");
   CU(c, cudaSetDevice(c->device));
   CU(c, cudaStreamWaitEvent(c->s_compute, c->ev_cleared, 0));
   int rc = c->x_fused ? exchange_after_routed_extract(c, true) : exchange_route(c, true);

@@ -382,7 +382,9 @@ def test_pair_exchange_between_contexts_equals_single_context(gpu_lib, name, n_r
 @pytest.mark.timeout(280)
 @pytest.mark.parametrize("name,n_ranks,inbox_mb,dedup", [("adv_tandem", 2, 1024, "owner"), ("adv_tandem", 2, 64, "local"),
                                                          ("adv_offset_k20", 3, 1024, "owner"), ("c1", 2, 1024, "owner"),
-                                                         ("c1", 2, 512, "local")])
+                                                         ("c1", 2, 512, "local"),
+                                                         # one distance: stage 4 runs beside the imports (classify_increment_owned)
+                                                         ("adv_k40", 2, 1024, "owner"), ("adv_k40", 3, 64, "local")])
 def test_peer_memory_exchange_equals_single_context(gpu_lib, name, n_ranks, inbox_mb, dedup):
     """links_exchange_attach/finish as deployed: one PROCESS per rank (tests/_exchange_worker.py), here all
     on GPU 0, inboxes shared through CUDA IPC like peer memory on an NVLink box.  Reads are sharded;
@@ -629,3 +631,47 @@ def test_bloom_filter_of_2_pow_31_bits_and_more(gpu_lib, oracle):
             bits = L.bf_bits()
         want = oracle.bf_build(contigs.seq, contigs.off, nbytes, 9, c.opts["k"])
         assert sha256(bits.tobytes()) == sha256(want.tobytes()), nbytes
+
+
+C1_DISTANCES = "1000,2000,3000,4000,5000,6000,7000,8000,9000,10000,12000,14000,16000,18000,20000"
+
+
+@pytest.mark.parametrize("layout", ["ours", "perl"])
+def test_unmodified_wrapper_chain_over_gpu_binary(gpu_lib, tmp_path, layout):
+    """The reference's own command line, unmodified: `LINKS` (sh, bin/LINKS:42-124) -> `LINKS-make` (bin/LINKS-make:121-128)
+    -> whatever `LINKS_CPP` and `LINKS.pl` are first on PATH.  Exactly tests/run_me.sh:1-2 (the installation test: 15
+    distances, defaults otherwise; LINKS-make derives -b, passes -r/-x/-v/-j in its own order), then the two sorted diffs of
+    azure-pipelines.yml:43-47.  `ours`: this repo's GPU LINKS_CPP + C++ layout; `perl`: GPU LINKS_CPP + the reference's Perl.
+    The wrappers are the reference's files installed by oracle/Makefile into oracle/_ref (git-ignored); skipped without them."""
+    import hashlib
+    import json
+    import shutil
+    import subprocess
+    from links_b200 import build
+    ref = os.path.join(os.path.dirname(GOLDEN_DIR), "..", "oracle", "_ref")
+    ref = os.path.abspath(ref)
+    if not os.path.exists(os.path.join(ref, "bin", "LINKS-make")) or not shutil.which("make"):
+        pytest.skip("oracle/_ref/bin/LINKS-make (the reference's wrappers) or make not available on this box")
+    if layout == "perl" and (not shutil.which("perl") or not os.path.exists(os.path.join(ref, "perl", "LINKS.pl"))):
+        pytest.skip("perl or the reference's LINKS.pl not available on this box")
+    build.build_all()
+    ours = os.path.dirname(build.HOST_BIN)
+    only_cpp = str(tmp_path / "only_cpp")  # a directory that holds our LINKS_CPP and nothing else
+    os.makedirs(only_cpp)
+    os.symlink(build.HOST_BIN, os.path.join(only_cpp, "LINKS_CPP"))
+    path = ([ours] if layout == "ours" else [only_cpp, os.path.join(ref, "perl")]) + [os.path.join(ref, "bin"), os.environ.get("PATH", "")]
+    c = GoldenCase("c1")
+    wd = tmp_path / "run"
+    wd.mkdir()
+    open(wd / "simulated_contigs.fa", "wb").write(c.raw("contigs.fa"))
+    open(wd / "simulated_genome.fa", "wb").write(c.raw("simulated_genome.fa"))
+    open(wd / "reads.fof", "w").write("simulated_genome.fa\n")
+    r = subprocess.run(["LINKS", "-f", "simulated_contigs.fa", "-s", "reads.fof", "-d", C1_DISTANCES, "-b", "installation_test"],
+                       cwd=wd, capture_output=True, text=True, env=dict(os.environ, PATH=os.pathsep.join(path), LINKS_STAGE_MB="8"))
+    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
+    assert "Running Command: LINKS-make LINKS" in r.stdout
+    assert sort_lines(open(wd / "installation_test.tigpair_checkpoint.tsv", "rb").read()) == c.expected_tsv()
+    assert sha256(open(wd / "installation_test.bloom", "rb").read()) == c.meta["bloom_sha256"]
+    meta = json.load(open(os.path.join(GOLDEN_DIR, "c1", "layout", "layout.json")))
+    assert hashlib.sha256(open(wd / "installation_test.scaffolds.fa", "rb").read()).hexdigest() == meta["scaffolds_fa_sha256"]
+    assert open(wd / "installation_test.scaffolds", "rb").read() == open(os.path.join(GOLDEN_DIR, "c1", "layout", "expected.scaffolds"), "rb").read()

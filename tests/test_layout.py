@@ -129,3 +129,37 @@ def test_layout_from_rows_in_memory_equals_layout_from_tsv(tmp_path, case):
     assert rd("mem", "scaffolds.fa") == rd("file", "scaffolds.fa")
     assert _below_label(rd("mem", "gv")) == _below_label(rd("file", "gv")) == open(os.path.join(d, "expected.gv_body"), "rb").read()
     assert rd("mem", "assembly_correspondence.tsv").split(b"\n", 1)[1] == rd("file", "assembly_correspondence.tsv").split(b"\n", 1)[1]
+
+
+def test_unmodified_wrapper_chain_finds_our_layout_program(tmp_path):
+    """`LINKS` -> `LINKS-make` (the reference's wrappers, installed unmodified into oracle/_ref/bin) with THIS repo's C++
+    `LINKS.pl` on PATH and the tsv already there (make skips the LINKS_CPP rule: the checkpoint semantics of
+    bin/LINKS-make:121): the layout stage must be found, take LINKS-make's fixed option order (-f -s -b -l -a -e -z -p -v,
+    bin/LINKS-make:125) and write the installation test's scaffolds.  CPU only; the GPU half of the chain is
+    tests/test_gpu_parity.py::test_unmodified_wrapper_chain_over_gpu_binary."""
+    import gzip
+    import hashlib
+    import json
+    import shutil
+    import subprocess
+    import time
+    from links_b200 import build
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    ref = os.path.join(root, "oracle", "_ref")
+    if not os.path.exists(os.path.join(ref, "bin", "LINKS-make")) or not shutil.which("make"):
+        pytest.skip("oracle/_ref/bin/LINKS-make (the reference's wrappers) or make not available")
+    build.build_layout()
+    gold = os.path.join(root, "tests", "golden", "c1")
+    for fn, dst in (("contigs.fa.gz", "simulated_contigs.fa"), ("simulated_genome.fa.gz", "simulated_genome.fa")):
+        open(tmp_path / dst, "wb").write(gzip.open(os.path.join(gold, fn), "rb").read())
+    open(tmp_path / "reads.fof", "w").write("simulated_genome.fa\n")
+    time.sleep(0.05)
+    shutil.copy(os.path.join(gold, "layout", "input.tigpair_checkpoint.tsv"), tmp_path / "installation_test.tigpair_checkpoint.tsv")
+    fake = tmp_path / "nobin"  # LINKS_CPP must NOT be needed: make sees an up-to-date checkpoint
+    fake.mkdir()
+    path = os.pathsep.join([os.path.dirname(build.LAYOUT_BIN), str(fake), os.path.join(ref, "bin"), os.environ.get("PATH", "")])
+    r = subprocess.run(["LINKS", "-f", "simulated_contigs.fa", "-s", "reads.fof", "-b", "installation_test"], cwd=tmp_path,
+                       capture_output=True, text=True, env=dict(os.environ, PATH=path))
+    assert r.returncode == 0, r.stdout[-1500:] + r.stderr[-1500:]
+    meta = json.load(open(os.path.join(gold, "layout", "layout.json")))
+    assert hashlib.sha256(open(tmp_path / "installation_test.scaffolds.fa", "rb").read()).hexdigest() == meta["scaffolds_fa_sha256"]
