@@ -21,6 +21,7 @@
 #pragma once
 #include "exchange.cuh"
 #include "kernels.cuh"
+#include "member_map.cuh"
 
 namespace links {
 
@@ -32,6 +33,9 @@ namespace links {
 #endif
 #ifndef LINKS_EXTRACT_MIN_CTAS
 #define LINKS_EXTRACT_MIN_CTAS 4
+#endif
+#ifndef LINKS_REST_FIRST
+#define LINKS_REST_FIRST 0   // > 0: S2 / S4 test that many of the remaining Bloom bits first and the others only if those are all set
 #endif
 constexpr int kExtractTile = LINKS_EXTRACT_TILE;  // candidates of one (read, distance) per warp tile
 #ifndef LINKS_HASH_SPLIT
@@ -63,6 +67,25 @@ __host__ __device__ inline size_t extract_smem_bytes(uint32_t k)
   return size_t((k + 1) / 2) * 16 * sizeof(ulonglong2) + size_t(kWarpsPerCta) * sizeof(WarpQueues);
 }
 
+// probes kFirst .. H-1 of a k-mer whose first kFirst bits were set (stages S2 and S4).  All together (one memory round
+// trip, H - kFirst sectors), or -- LINKS_REST_FIRST = g -- g of them first and the rest only for the lanes that still
+// pass: a k-mer that is not in the filter got here by chance (2^-kFirst) and fails each further bit with probability
+// ~1/2, so the second group is rarely needed and its sectors are saved at the price of a second round trip for few lanes.
+template <int H, bool SMALL>
+__device__ __forceinline__ bool bloom_probe_rest(const BloomView& bf, uint64_t h0, uint64_t kseed, uint32_t h_first, uint32_t hn,
+                                                 uint32_t& n_probe, uint32_t& n_load)
+{
+  constexpr int kFirst = H >= 2 ? 2 : H;
+  constexpr int kRest = H >= 2 ? H - 2 : 0;
+  if (H == 0) { n_load += hn - h_first; return bloom_probe_loop<SMALL>(bf, h0, kseed, h_first, hn, n_probe); }
+  constexpr int g = LINKS_REST_FIRST > 0 && LINKS_REST_FIRST < kRest ? LINKS_REST_FIRST : kRest;
+  n_load += g;
+  if (!bloom_probe_fixed<g, SMALL>(bf, h0, kseed, kFirst, n_probe)) return false;
+  if (g == kRest) return true;
+  n_load += kRest - g;
+  return bloom_probe_fixed<kRest - g, SMALL>(bf, h0, kseed, kFirst + g, n_probe);
+}
+
 // lanes with `pass` get consecutive slots starting at `n`; returns the new count (warp-uniform)
 __device__ __forceinline__ uint32_t warp_push_slot(bool pass, uint32_t n, uint32_t& slot)
 {
@@ -77,11 +100,12 @@ __device__ __forceinline__ uint32_t warp_push_slot(bool pass, uint32_t n, uint32
 // the kernel's last block publishes the new record counts after system-scope fences.  The transfer is part of
 // the extraction, tile by tile; the owner de-duplicates while this rank keeps extracting.
 // SMALL: the filter has fewer than 2^31 bits (bf.bits32 set): 32-bit remainder in bloom_mod
-template <int H, bool ROUTED, bool SMALL>
+// MAP: the launch comes with a member map (member_map.cuh); reads without an invalid base take their filter answers from it
+template <int H, bool ROUTED, bool SMALL, bool MAP>
 __global__ void __launch_bounds__(kCtaThreads, LINKS_EXTRACT_MIN_CTAS) extract_kernel(ReadBatch rb, DistParams dp, int k, uint64_t kseed,
                                                                  const ulonglong2* __restrict__ g_tab2, BloomView bf,
                                                                  MemberView mv, PairView pv, Counters* __restrict__ ctr,
-                                                                 ExchangeDev* __restrict__ x, InboxLayout L, uint64_t epoch)
+                                                                 ExchangeDev* __restrict__ x, InboxLayout L, uint64_t epoch, MemberMap mm)
 {
   extern __shared__ ulonglong2 s_dyn[];
   const int n_tab = ((k + 1) >> 1) * 16;
@@ -103,7 +127,6 @@ __global__ void __launch_bounds__(kCtaThreads, LINKS_EXTRACT_MIN_CTAS) extract_k
   const uint32_t hn = H ? uint32_t(H) : bf.hash_num;
   const uint32_t h_first = hn < 2u ? hn : 2u;
   constexpr int kFirst = H >= 2 ? 2 : H;        // compile-time split when H is known
-  constexpr int kRest = H >= 2 ? H - 2 : 0;
   const uint32_t n_seg = rb.n_seq * dp.n_dist;
   unsigned long long n_cand = 0, n_surv = 0;
   uint32_t n_probe = 0, n_load = 0, n_msec = 0;  // reference-order bit tests, bit tests issued, member-set sectors
@@ -136,6 +159,9 @@ __global__ void __launch_bounds__(kCtaThreads, LINKS_EXTRACT_MIN_CTAS) extract_k
       const uint32_t na = rv.total - va0, nb = rv.total - vb0;
       cnt = (na < nb ? na : nb) / t;
     }
+    // member_map.cuh: the filter's answers for this read's k-mers are already in the byte map (reads without an invalid base)
+    const bool use_map = MAP && !flagged;
+    const uint8_t* map_r = use_map ? mm.bytes + mm.base[r] : nullptr;
     const uint64_t j_begin = uint64_t(tile - rb.seg_tile_start[s]) * kExtractTile;
     const uint32_t n_tile = j_begin < cnt ? uint32_t(min((unsigned long long)kExtractTile, cnt - j_begin)) : 0u;
     if (lane == 0) n_cand += n_tile;
@@ -163,7 +189,24 @@ __global__ void __launch_bounds__(kCtaThreads, LINKS_EXTRACT_MIN_CTAS) extract_k
       else if (n5) stage = 6;
       else break;
 
-      if (stage == 1) {  // ---- S1: hash A, first probes
+      if (stage == 1 && use_map) {  // ---- S1 with the map: two byte loads answer contains(A) && contains(B); survivors go to S5
+        const uint32_t q = next_q + lane;
+        bool pass = false;
+        if (q < n_tile) {
+          const uint64_t n = rank_n(q);
+          const uint8_t ba = __ldg(map_r + map_entry_of(mm, n));
+          n_probe += ba & 0x7Fu;
+          if (ba & 0x80u) {  // ref :554: B is only asked when A is in the filter
+            const uint8_t bb = __ldg(map_r + map_entry_of(mm, n + d));
+            n_probe += bb & 0x7Fu;
+            pass = (bb & 0x80u) != 0;
+          }
+        }
+        next_q += 32;
+        uint32_t slot;
+        n4 = warp_push_slot(pass, n4, slot);
+        if (pass) Q.q4_i[slot] = uint16_t(q);
+      } else if (stage == 1) {  // ---- S1: hash A, first probes
         const uint32_t q = next_q + lane;
         bool pass = false, member = false;
         uint64_t h0 = 0;
@@ -186,6 +229,7 @@ __global__ void __launch_bounds__(kCtaThreads, LINKS_EXTRACT_MIN_CTAS) extract_k
             pass = H ? bloom_probe_fixed<kFirst, SMALL>(bf, h0, kseed, 0, n_probe) : bloom_probe_loop<SMALL>(bf, h0, kseed, 0, h_first, n_probe);
             n_load += h_first;
           }
+#endif
         }
         next_q += 32;
         uint32_t slot;
@@ -195,7 +239,6 @@ __global__ void __launch_bounds__(kCtaThreads, LINKS_EXTRACT_MIN_CTAS) extract_k
           n2 = warp_push_slot(member, n2, slot);
           if (member) Q.q2_i[slot] = uint16_t(q);
         }
-#endif
       } else if (stage == 2) {  // ---- S2: remaining probes of A
         const uint32_t take = n1 < 32u ? n1 : 32u;
         n1 -= take;
@@ -204,8 +247,7 @@ __global__ void __launch_bounds__(kCtaThreads, LINKS_EXTRACT_MIN_CTAS) extract_k
         if (uint32_t(lane) < take) {
           q = Q.q1_i[n1 + lane];
           const uint64_t h0 = Q.q1_h[n1 + lane];
-          pass = H ? bloom_probe_fixed<kRest, SMALL>(bf, h0, kseed, kFirst, n_probe) : bloom_probe_loop<SMALL>(bf, h0, kseed, h_first, hn, n_probe);
-          n_load += hn - h_first;
+          pass = bloom_probe_rest<H, SMALL>(bf, h0, kseed, h_first, hn, n_probe, n_load);
         }
         __syncwarp();
         uint32_t slot;
@@ -253,8 +295,7 @@ __global__ void __launch_bounds__(kCtaThreads, LINKS_EXTRACT_MIN_CTAS) extract_k
         if (uint32_t(lane) < take) {
           q = Q.q3_i[n3 + lane]; f = Q.q3_f[n3 + lane]; rr = Q.q3_r[n3 + lane];
           const uint64_t h0 = rr < f ? rr : f;
-          pass = H ? bloom_probe_fixed<kRest, SMALL>(bf, h0, kseed, kFirst, n_probe) : bloom_probe_loop<SMALL>(bf, h0, kseed, h_first, hn, n_probe);
-          n_load += hn - h_first;
+          pass = bloom_probe_rest<H, SMALL>(bf, h0, kseed, h_first, hn, n_probe, n_load);
         }
         __syncwarp();
         uint32_t slot;
@@ -267,8 +308,10 @@ __global__ void __launch_bounds__(kCtaThreads, LINKS_EXTRACT_MIN_CTAS) extract_k
         uint64_t h_a = 0, h_b = 0, okey_r = 0;
         if (uint32_t(lane) < take) {
           const uint32_t q = Q.q4_i[n4 + lane];
-          const uint64_t fb = Q.q4_f[n4 + lane], rbv = Q.q4_r[n4 + lane];
+          uint64_t fb, rbv;
           const uint64_t n = rank_n(q);
+          if (use_map) LINKS_HASH(pos_b(n), fb, rbv);  // the map path carries no hashes
+          else { fb = Q.q4_f[n4 + lane]; rbv = Q.q4_r[n4 + lane]; }
           uint64_t fa, ra;
           LINKS_HASH(pos_a(n), fa, ra);
           if (fa < rbv) { h_a = rbv; h_b = ra; } else { h_a = fa; h_b = fb; }

@@ -51,10 +51,11 @@ struct DevBuf {
 
 struct SeqBatchDev { // device-resident packed sequences of one push/chunk
   DevBuf packed, inv, off, segs, flags, vs, vrank;
+  DevBuf mm_bytes, mm_base, mm_segs;  // member map of a read chunk (member_map.cuh)
   uint64_t n_bases = 0, base0 = 0;
   uint32_t n_seq = 0, n_tiles = 0, first_id = 0;
   uint64_t first_read_idx = 0;
-  void release() { packed.release(); inv.release(); off.release(); segs.release(); flags.release(); vs.release(); vrank.release(); }
+  void release() { packed.release(); inv.release(); off.release(); segs.release(); flags.release(); vs.release(); vrank.release(); mm_bytes.release(); mm_base.release(); mm_segs.release(); }
 };
 
 enum Family { F_H2D, F_PACK, F_BF, F_TABLE, F_EXTRACT, F_CLASSIFY, F_SORT, F_D2H, F_GROW, F_EXCHANGE, F_COUNT };
@@ -85,6 +86,12 @@ struct links_ctx {
   uint32_t hash_num = 0;
   bool bf_ready = false, bf_insert = false;
   bool bf_covers_contigs = false;  // links_bf_covers_contigs(): a loaded filter is vouched to hold every pushed contig k-mer
+
+  // member map (member_map.cuh): which x = position - offset any (distance, role) can use, periodic with map_T = lcm(steps)
+  DevBuf d_need_idx, d_need_res;
+  std::vector<int16_t> need_idx;
+  uint32_t map_T = 0, map_c = 0;   // map_T == 0: no map for these options
+  int map_mode = -1;               // LINKS_MEMBER_MAP=0/1 forces it off/on; -1: per chunk, where it saves filter walks
 
   // exact member set of the filter's keys (kernels.cuh MemberView); empty when disabled or not provable
   DevBuf d_members;
@@ -370,25 +377,49 @@ BloomView bloom_view(links_ctx* c)
 // extract_kernel is instantiated for the Bloom hash counts LINKS produces in practice
 // (hash_num = floor(-log2(fpr)): 9 for the default -p 0.001) and once with a runtime count.
 using ExtractFn = void (*)(ReadBatch, DistParams, int, uint64_t, const ulonglong2*, BloomView, MemberView, PairView, Counters*,
-                           ExchangeDev*, InboxLayout, uint64_t);
-template <bool ROUTED, bool SMALL>
+                           ExchangeDev*, InboxLayout, uint64_t, MemberMap);
+using MapFn = void (*)(MapBatch, MemberMap, int, uint64_t, uint64_t, const ulonglong2*, BloomView, MemberView, Counters*);
+template <bool SMALL>
+MapFn map_fn_sel(uint32_t hash_num)
+{
+  switch (hash_num) {
+  case 6: return member_map_kernel<6, SMALL>;
+  case 7: return member_map_kernel<7, SMALL>;
+  case 8: return member_map_kernel<8, SMALL>;
+  case 9: return member_map_kernel<9, SMALL>;
+  case 10: return member_map_kernel<10, SMALL>;
+  case 13: return member_map_kernel<13, SMALL>;
+  default: return member_map_kernel<0, SMALL>;
+  }
+}
+MapFn map_fn_for(uint32_t hash_num, bool small_filter) { return small_filter ? map_fn_sel<true>(hash_num) : map_fn_sel<false>(hash_num); }
+template <bool ROUTED, bool SMALL, bool MAP>
 ExtractFn extract_fn_sel(uint32_t hash_num)
 {
   switch (hash_num) {
-  case 6: return extract_kernel<6, ROUTED, SMALL>;
-  case 7: return extract_kernel<7, ROUTED, SMALL>;
-  case 8: return extract_kernel<8, ROUTED, SMALL>;
-  case 9: return extract_kernel<9, ROUTED, SMALL>;
-  case 10: return extract_kernel<10, ROUTED, SMALL>;
-  case 13: return extract_kernel<13, ROUTED, SMALL>;
-  default: return extract_kernel<0, ROUTED, SMALL>;
+  case 6: return extract_kernel<6, ROUTED, SMALL, MAP>;
+  case 7: return extract_kernel<7, ROUTED, SMALL, MAP>;
+  case 8: return extract_kernel<8, ROUTED, SMALL, MAP>;
+  case 9: return extract_kernel<9, ROUTED, SMALL, MAP>;
+  case 10: return extract_kernel<10, ROUTED, SMALL, MAP>;
+  case 13: return extract_kernel<13, ROUTED, SMALL, MAP>;
+  default: return extract_kernel<0, ROUTED, SMALL, MAP>;
   }
 }
-// small_filter: fewer than 2^31 bits (BloomView::bits32 set), the 32-bit remainder variant
-ExtractFn extract_fn_for(uint32_t hash_num, bool routed, bool small_filter)
+// small_filter: fewer than 2^31 bits (BloomView::bits32 set), the 32-bit remainder variant; mapped: a member map comes with the launch
+ExtractFn extract_fn_for(uint32_t hash_num, bool routed, bool small_filter, bool mapped)
 {
-  if (small_filter) return routed ? extract_fn_sel<true, true>(hash_num) : extract_fn_sel<false, true>(hash_num);
-  return routed ? extract_fn_sel<true, false>(hash_num) : extract_fn_sel<false, false>(hash_num);
+  const int v = (routed ? 1 : 0) | (small_filter ? 2 : 0) | (mapped ? 4 : 0);
+  switch (v) {
+  case 0: return extract_fn_sel<false, false, false>(hash_num);
+  case 1: return extract_fn_sel<true, false, false>(hash_num);
+  case 2: return extract_fn_sel<false, true, false>(hash_num);
+  case 3: return extract_fn_sel<true, true, false>(hash_num);
+  case 4: return extract_fn_sel<false, false, true>(hash_num);
+  case 5: return extract_fn_sel<true, false, true>(hash_num);
+  case 6: return extract_fn_sel<false, true, true>(hash_num);
+  default: return extract_fn_sel<true, true, true>(hash_num);
+  }
 }
 const uint32_t kExtractVariants[] = {0, 6, 7, 8, 9, 10, 13};
 
@@ -1069,14 +1100,43 @@ int links_create(links_ctx** out, const links_params* p)
     CUC(c->d_tab2.ensure(tab2.size() * sizeof(ulonglong2)));
     CUC(cudaMemcpy(c->d_tab2.p, tab2.data(), tab2.size() * sizeof(ulonglong2), cudaMemcpyHostToDevice));
     CUC(c->d_cursor.ensure(64));
+    {
+      // member map (member_map.cuh): x is needed iff (x+1) % t_i == 0 [an A k-mer] or (x+1-d_i) % t_i == 0 [a B k-mer] for some i
+      const char* e = getenv("LINKS_MEMBER_MAP");
+      c->map_mode = !e ? -1 : e[0] == '0' ? 0 : 1;
+      uint64_t T = 1;
+      for (uint32_t i = 0; i < p->n_dist && T <= kMapMaxPeriod; ++i) { uint64_t a = T, b = c->step[i]; while (b) { const uint64_t r = a % b; a = b; b = r; } T = T / a * c->step[i]; }
+      if (T <= kMapMaxPeriod && c->map_mode != 0) {
+        c->need_idx.assign(size_t(T), int16_t(-1));
+        std::vector<uint16_t> res;
+        for (uint64_t x = 0; x < T; ++x) {
+          bool need = false;
+          for (uint32_t i = 0; i < p->n_dist && !need; ++i) {
+            const uint64_t t = c->step[i], d = c->dist[i];
+            need = (x + 1) % t == 0 || (x + 1 + t - d % t) % t == 0;
+          }
+          if (need) { c->need_idx[size_t(x)] = int16_t(res.size()); res.push_back(uint16_t(x)); }
+        }
+        c->map_T = uint32_t(T); c->map_c = uint32_t(res.size());
+        CUC(c->d_need_idx.ensure(c->need_idx.size() * 2));
+        CUC(cudaMemcpy(c->d_need_idx.p, c->need_idx.data(), c->need_idx.size() * 2, cudaMemcpyHostToDevice));
+        CUC(c->d_need_res.ensure(res.size() * 2));
+        CUC(cudaMemcpy(c->d_need_res.p, res.data(), res.size() * 2, cudaMemcpyHostToDevice));
+      }
+    }
     host_mark(c, "create: streams, events, hash tables on device");
     int occ = 0;
     for (uint32_t h : kExtractVariants)
-      for (int v = 0; v < 4; ++v) {
-        const ExtractFn fn = extract_fn_for(h, (v & 1) != 0, (v & 2) != 0);
+      for (int v = 0; v < 8; ++v) {
+        const ExtractFn fn = extract_fn_for(h, (v & 1) != 0, (v & 2) != 0, (v & 4) != 0);
         CUC(cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, int(extract_smem_bytes(p->k))));
         CUC(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, fn, kCtaThreads, extract_smem_bytes(p->k)));
         c->extract_ctas_per_sm = std::max(occ, 1);
+      }
+    for (uint32_t h : kExtractVariants)
+      for (int v = 0; v < 2; ++v) {
+        cudaFuncAttributes fa;
+        CUC(cudaFuncGetAttributes(&fa, map_fn_for(h, v != 0)));
       }
     {
       // load every kernel now: with CUDA's lazy module loading a first launch may have to wait for the
@@ -1146,7 +1206,7 @@ void links_destroy(links_ctx* c)
   if (c->ev_routed) cudaEventDestroy(c->ev_routed);
   if (c->ev_imported) cudaEventDestroy(c->ev_imported);
   c->d_xdev.release(); c->d_owned.release(); c->d_owned_list.release(); c->d_owned_okeys.release(); c->f_rowcnt.release();
-  c->d_members.release();
+  c->d_members.release(); c->d_need_idx.release(); c->d_need_res.release();
   if (c->ev_table) cudaEventDestroy(c->ev_table);
   if (c->ev_fork) cudaEventDestroy(c->ev_fork);
   cudaGetLastError();
@@ -1301,8 +1361,10 @@ int links_contigs_push_dev(links_ctx* c, const void* dev_seq, const uint64_t* of
   return contigs_push_impl(c, nullptr, static_cast<const uint8_t*>(dev_seq), off, n, first_tig_id);
 }
 
+// map_base / map_segs: empty = this chunk walks the filter per candidate; else (n+1 entries each) the member map's layout
 static int push_read_chunk(links_ctx* c, const char* seq, const uint8_t* dev_seq, const uint64_t* off, uint32_t n,
-                           uint64_t first_read_idx, const std::vector<uint32_t>& segs, uint64_t cand, uint64_t later)
+                           uint64_t first_read_idx, const std::vector<uint32_t>& segs, uint64_t cand, uint64_t later,
+                           const std::vector<unsigned long long>& map_base, const std::vector<uint32_t>& map_segs)
 {
   const int si = c->next_slot;
   c->next_slot = (si + 1) % links_ctx::kSlots;
@@ -1316,6 +1378,14 @@ static int push_read_chunk(links_ctx* c, const char* seq, const uint8_t* dev_seq
   if (rc) return rc;
   SeqBatchDev& b = c->slot[si];
   b.first_read_idx = first_read_idx;
+  const bool mapped = !map_base.empty() && map_base.back() > 0;
+  if (mapped) {  // (on s_copy in front of upload_and_pack's copies: covered by the same ev_copied)
+    CU(c, b.mm_bytes.ensure(map_base.back()));
+    CU(c, b.mm_base.ensure(map_base.size() * 8));
+    CU(c, b.mm_segs.ensure(map_segs.size() * 4));
+    CU(c, cudaMemcpyAsync(b.mm_base.p, map_base.data(), map_base.size() * 8, cudaMemcpyHostToDevice, c->s_copy));
+    CU(c, cudaMemcpyAsync(b.mm_segs.p, map_segs.data(), map_segs.size() * 4, cudaMemcpyHostToDevice, c->s_copy));
+  }
   // copy on s_copy, pack on s_pack, extract on s_compute: chunk i+1 is packed while chunk i is being extracted
   rc = upload_and_pack(c, b, c->slot_ascii[si], seq, dev_seq, off, n, segs, true, c->s_copy, c->s_pack, c->ev_copied[si]);
   if (rc) return rc;
@@ -1330,10 +1400,20 @@ static int push_read_chunk(links_ctx* c, const char* seq, const uint8_t* dev_seq
                    first_read_idx, c->d_cursor.as<unsigned int>()};
       DistParams dp{c->d_dist.as<uint32_t>(), c->d_step.as<uint32_t>(), c->prm.n_dist, c->prm.offset};
       CU(c, cudaMemsetAsync(c->d_cursor.p, 0, sizeof(unsigned int), c->s_compute));
-      extract_fn_for(c->hash_num, fused, bloom_view(c).bits32 != 0)<<<grid_for(c, b.n_tiles, kWarpsPerCta, c->extract_ctas_per_sm), kCtaThreads,
+      MemberMap mm{nullptr, nullptr, nullptr, nullptr, 0, 0};
+      if (mapped) {
+        mm = MemberMap{b.mm_bytes.as<uint8_t>(), b.mm_base.as<unsigned long long>(), c->d_need_idx.as<int16_t>(), c->d_need_res.as<uint16_t>(),
+                       c->map_T, c->map_c};
+        MapBatch mb{b.packed.as<uint32_t>(), b.off.as<uint64_t>(), b.base0, b.mm_segs.as<uint32_t>(), b.n_seq, map_segs.back(), b.flags.as<uint32_t>()};
+        map_fn_for(c->hash_num, bloom_view(c).bits32 != 0)<<<grid_for(c, map_segs.back(), 1, 8), kCtaThreads,
+                                                           size_t((c->prm.k + 1) / 2) * 16 * sizeof(ulonglong2), c->s_compute>>>(
+          mb, mm, int(c->prm.k), c->prm.offset, c->kseed, c->d_tab2.as<ulonglong2>(), bloom_view(c), member_view(c), c->d_ctr.as<Counters>());
+        c->launches++;
+      }
+      extract_fn_for(c->hash_num, fused, bloom_view(c).bits32 != 0, mapped)<<<grid_for(c, b.n_tiles, kWarpsPerCta, c->extract_ctas_per_sm), kCtaThreads,
                                            extract_smem_bytes(c->prm.k), c->s_compute>>>(
         rb, dp, int(c->prm.k), c->kseed, c->d_tab2.as<ulonglong2>(), bloom_view(c), member_view(c),
-        pair_view(c), c->d_ctr.as<Counters>(), c->d_xdev.as<ExchangeDev>(), c->x_lay, c->x_epoch);
+        pair_view(c), c->d_ctr.as<Counters>(), c->d_xdev.as<ExchangeDev>(), c->x_lay, c->x_epoch, mm);
       c->launches++;
       c->extract_launches++;
       CU(c, cudaGetLastError());
@@ -1402,10 +1482,12 @@ static int reads_push_impl(links_ctx* c, const char* seq, const uint8_t* dev_seq
   c->max_read_end = std::max<uint64_t>(c->max_read_end, first_read_idx + n);
   uint32_t i0 = 0;
   uint64_t done_cand = 0;
-  std::vector<uint32_t> segs;
+  std::vector<uint32_t> segs, map_segs;
+  std::vector<unsigned long long> map_base;
+  const bool map_possible = c->map_T && c->hash_num <= 127 && c->map_mode != 0;
   while (i0 < n) {
-    segs.clear();
-    uint64_t tiles = 0, cand = 0;
+    segs.clear(); map_segs.clear(); map_base.clear();
+    uint64_t tiles = 0, cand = 0, map_entries = 0, map_tiles = 0;
     uint32_t i = i0;
     // host pushes also taper off: the last chunk's kernels run after its copy with nothing left to overlap
     const uint64_t chunk_limit = dev_seq ? kChunkBases : std::min(kChunkBases, std::max<uint64_t>((off[n] - off[i0]) / 2, 8ull << 20));
@@ -1419,10 +1501,26 @@ static int reads_push_impl(links_ctx* c, const char* seq, const uint8_t* dev_seq
         cand += cnt;
       }
       if (tiles >= (1ull << 31)) return fail(c, LINKS_E_LIMIT, "links_reads_push: chunk too large");
+      if (map_possible) {  // member map: c entries per period of T positions over x = position - offset in [0, npos - offset)
+        map_base.push_back(map_entries);
+        map_segs.push_back(uint32_t(map_tiles));
+        const uint64_t X = len >= k && len - k + 1 > o ? len - k + 1 - o : 0;
+        const uint64_t e = (X + c->map_T - 1) / c->map_T * c->map_c;
+        map_entries += e;
+        map_tiles += (e + kMapTile - 1) / kMapTile;
+      }
     }
     segs.push_back(uint32_t(tiles));
+    if (map_possible) {
+      map_base.push_back(map_entries);
+      map_segs.push_back(uint32_t(map_tiles));
+      // One filter walk per map entry against ~1.45 per candidate (B is only asked when A passes, ~45 % on ONT-like reads):
+      // the map pays with several distances that share positions, not for one distance on reads barely longer than it
+      const bool pays = c->map_mode == 1 || double(map_entries) < 0.8 * 1.45 * double(cand);
+      if (!pays || map_tiles >= (1ull << 31)) { map_base.clear(); map_segs.clear(); }
+    }
     done_cand += cand;
-    int rc = push_read_chunk(c, seq, dev_seq, off + i0, i - i0, first_read_idx + i0, segs, cand, total_cand - done_cand);
+    int rc = push_read_chunk(c, seq, dev_seq, off + i0, i - i0, first_read_idx + i0, segs, cand, total_cand - done_cand, map_base, map_segs);
     if (rc) return rc;
     i0 = i;
     kChunkBases = std::min(kChunkMax, kChunkBases * 2);

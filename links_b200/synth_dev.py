@@ -139,12 +139,15 @@ def make_config_dev(name: str, scale: float, device, rank: int = 0, world: int =
         c_start, c_len, c_rc, n_idx, n_pos_in, n_len = lay["contigs"]
         c_off = np.concatenate([[0], np.cumsum(c_len)]).astype(np.uint64)
         d_contigs = torch.empty(int(c_off[-1]), dtype=torch.uint8, device=device)
-        _ck(lib.synth_copy_ranges(genome.data_ptr(), d_contigs.data_ptr(), _dev(c_off[:-1], device).data_ptr(), _dev(c_start, device).data_ptr(),
-                                  _dev(c_len, device).data_ptr(), _dev(c_rc, device).data_ptr(), len(c_len)), "contigs")
+        # (device copies of the small arrays are held in names: a temporary would be freed, and its block reused, mid-call)
+        t_off, t_start, t_len, t_rc = _dev(c_off[:-1], device), _dev(c_start, device), _dev(c_len, device), _dev(c_rc, device)
+        _ck(lib.synth_copy_ranges(genome.data_ptr(), d_contigs.data_ptr(), t_off.data_ptr(), t_start.data_ptr(), t_len.data_ptr(),
+                                  t_rc.data_ptr(), len(c_len)), "contigs")
         if len(n_idx):
             pos = (c_off[n_idx] + n_pos_in).astype(np.uint64)
             ln = np.minimum(n_len.astype(np.uint64), c_off[n_idx + 1] - pos).astype(np.uint32)
-            _ck(lib.synth_fill_runs(d_contigs.data_ptr(), _dev(pos, device).data_ptr(), _dev(ln, device).data_ptr(), len(pos), ord("N")), "N runs")
+            t_pos, t_ln = _dev(pos, device), _dev(ln, device)
+            _ck(lib.synth_fill_runs(d_contigs.data_ptr(), t_pos.data_ptr(), t_ln.data_ptr(), len(pos), ord("N")), "N runs")
         n = len(c_len)
         digits = np.floor(np.log10(np.arange(1, n + 1))).astype(np.int64) + 1
         file_bytes = int(c_off[-1]) + int(digits.sum()) + 2 * n  # ">" + ordinal + "\n" + sequence + "\n"
@@ -157,7 +160,8 @@ def make_config_dev(name: str, scale: float, device, rank: int = 0, world: int =
         _ck(lib.synth_read_lengths(d_rlen.data_ptr(), m, lo, seed + 1, err, d_olen.data_ptr()), "read lengths")
         r_off = np.concatenate([[0], np.cumsum(d_olen[:m].cpu().numpy().astype(np.uint64))]).astype(np.uint64)
         d_reads = torch.empty(max(int(r_off[-1]), 1), dtype=torch.uint8, device=device)
-        _ck(lib.synth_reads(genome.data_ptr(), d_rstart.data_ptr(), d_rlen.data_ptr(), d_rrc.data_ptr(), _dev(r_off, device).data_ptr(), m, lo,
+        t_roff = _dev(r_off, device)
+        _ck(lib.synth_reads(genome.data_ptr(), d_rstart.data_ptr(), d_rlen.data_ptr(), d_rrc.data_ptr(), t_roff.data_ptr(), m, lo,
                             seed + 1, err, n_read_frac, d_reads.data_ptr()), "reads")
         del genome
         torch.cuda.empty_cache()

@@ -117,6 +117,22 @@ def test_mates_table_matches_reference_goldens(gpu_lib, golden_case):
         assert stats["n_rows"] == golden_case.meta["n_rows"]
 
 
+def test_member_map_matches_reference_goldens(gpu_lib, golden_case, monkeypatch):
+    """The Bloom filter asked once per sampled read position (member_map.cuh) instead of once per candidate pair: forced on
+    (LINKS_MEMBER_MAP=1) and off, both against the reference's output; the count of bit tests the reference's own loop makes
+    (n_bf_probes) must come out the same either way.  Reads with an invalid base keep the per-candidate path inside the
+    same launch (adv_ns_lower mixes both)."""
+    probes = {}
+    for mode in ("1", "0"):
+        monkeypatch.setenv("LINKS_MEMBER_MAP", mode)
+        for chunk in (None, 2):
+            tsv, issues, stats, _ = _run_gpu(golden_case, chunk_reads=chunk)
+            assert sort_lines(tsv) == golden_case.expected_tsv(), (mode, chunk)
+            assert sort_issue_records(issues) == golden_case.expected_issues(), (mode, chunk)
+            probes[(mode, chunk)] = (stats["n_bf_probes"], stats["n_candidates"], stats["n_survivors"], stats["n_unique_pairs"])
+    assert len(set(probes.values())) == 1, probes
+
+
 @pytest.mark.parametrize("table", ["full", "mates"])
 def test_baseline_configs_match_reference(gpu_lib, config_case, table):
     """BASELINE.json configs[2..4] (multi-distance with per-distance steps; k 20 d 5000 t 5; the step sweep
