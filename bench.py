@@ -481,7 +481,12 @@ def measure_job(args, job: Job, lib, dist, rank: int, world: int, local_rank: in
     # N > 1: pairs travel to their owner ranks through NVLink peer memory from inside extract_kernel while the reads are still
     # being extracted (links_exchange_attach); LINKS_EXCHANGE=nccl selects the stop-and-exchange all-to-all instead
     p2p = world > 1 and os.environ.get("LINKS_EXCHANGE", "p2p") != "nccl"
-    bloom_bcast = os.environ.get("LINKS_BLOOM", "local") == "broadcast"
+    bloom_mode = os.environ.get("LINKS_BLOOM", "auto")
+    bloom_bcast = bloom_mode == "broadcast"
+    # a filter of hundreds of MB is DRAM-resident and its build (hash_num random read-modify-writes per contig k-mer) is the
+    # longest stage of a human-scale job: built in shares, OR-ed over NVLink (links_bf_alloc_shared / links_bf_allreduce)
+    bloom_shared = world > 1 and (bloom_mode == "shared" or (bloom_mode == "auto" and bf_bytes >= (256 << 20)))
+    keep_bloom, bloom_ptrs = multi.alloc_shared_bloom(dist, dev, bf_bytes) if bloom_shared else (None, None)
     keep_alive = None
     if p2p:
         # every survivor (before de-duplication) becomes a record in its owner's inbox: ~0.12 per read base at k 15 / 5 % errors
@@ -514,7 +519,9 @@ def measure_job(args, job: Job, lib, dist, rank: int, world: int, local_rank: in
         mark(None)
         L.reset()
         mark("reset")
-        if world > 1 and bloom_bcast:
+        if bloom_shared:
+            multi.build_bloom_shared(L, bf_bytes, hash_num, bloom_ptrs, lambda: push_contigs(resident), dist)
+        elif world > 1 and bloom_bcast:
             # north_star's variant: rank 0 builds the Bloom filter, NCCL broadcast replicates it, the others adopt it.
             # It serialises the ranks (everyone waits for rank 0's build) -- measured 1.7 ms of a 10 ms step at N=2.
             if rank == 0:
@@ -599,7 +606,8 @@ def measure_job(args, job: Job, lib, dist, rank: int, world: int, local_rank: in
                        "l2": "inputs (reads, pair set, contig table) exceed the 126 MB L2; no flush",
                        "sharding": ((("one read set split into contiguous shards, " if job.scaling == "strong" else "each rank its own read set of the configuration's size, ")
                                      + "contigs replicated, Bloom filter "
-                                     + ("NCCL-broadcast from rank 0, " if bloom_bcast else "built by every rank from the replicated contigs (LINKS_BLOOM=broadcast: NCCL broadcast from rank 0), ")
+                                     + ("built in shares (each rank inserts 1/N of the contig k-mers) and OR-ed over NVLink peer memory, " if bloom_shared else
+                                        "NCCL-broadcast from rank 0, " if bloom_bcast else "built by every rank from the replicated contigs (LINKS_BLOOM=broadcast: NCCL broadcast from rank 0), ")
                                      + ("every surviving pair written by extract_kernel itself into its owner rank's inbox (hash of (h_a,h_b)) over NVLink peer "
                                         "memory and imported there while extraction continues, partial link rows summed on rank 0 on the device"
                                         if p2p else "distinct pairs routed by one NCCL all-to-all keyed on hash(h_a,h_b), rows summed on rank 0"))
@@ -632,7 +640,7 @@ def measure_job(args, job: Job, lib, dist, rank: int, world: int, local_rank: in
     if phases:
         print(f"[rank {rank}] host ms per phase, last step: " + json.dumps({k2: round(v, 2) for k2, v in ph.items()}), file=sys.stderr)
     L.close()
-    del keep_alive
+    del keep_alive, keep_bloom
     return out
 
 

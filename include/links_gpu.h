@@ -198,6 +198,18 @@ uint32_t links_pair_owner(uint64_t h_a, uint64_t h_b, uint32_t n_ranks);
 int links_bf_download_dev(links_ctx* ctx, void* dev_dst);
 int links_bf_load_dev(links_ctx* ctx, const void* dev_bits, uint64_t bytes, uint32_t hash_num);
 
+/* Bloom filter built in shares (large assemblies).  A filter of GBs is DRAM-resident and its build -- hash_num random
+ * read-modify-writes per contig k-mer -- would be repeated in full on every rank.  Instead every rank owns a
+ * peer-addressable buffer of `bytes` (bloom[r] = rank r's, as addressable from THIS process; same bytes / hash_num on all
+ * ranks), inserts only its 1/n_ranks share of the k-mers of the contigs it is given (all ranks push ALL contigs, they stay
+ * resident for stage 3), and links_bf_allreduce makes every copy the bitwise OR of all of them through peer memory:
+ *   every rank: links_bf_alloc_shared -> links_contigs_push* ... -> links_sync;   barrier (caller's: all shares inserted)
+ *   every rank: links_bf_allreduce (returns when this rank's slice is stored in every copy);   barrier;   links_reads_push* ...
+ * The result is bit-identical to links_bf_alloc + the same contigs on one rank.  The exact member set
+ * (links_bf_covers_contigs) is not kept in this mode. */
+int links_bf_alloc_shared(links_ctx* ctx, uint64_t bytes, uint32_t hash_num, uint32_t rank, uint32_t n_ranks, void* const* bloom);
+int links_bf_allreduce(links_ctx* ctx);
+
 /* ---- multi-GPU over peer memory (NVLink P2P / NVSwitch): the exchange above without the stop in the middle.
  * Every rank owns an INBOX, a device buffer of inbox_bytes that all ranks of the node can address (CUDA
  * IPC, VMM export or torch symmetric memory -- the caller's business); inbox[r] is rank r's buffer as

@@ -293,4 +293,34 @@ __global__ void rows_gather_kernel(ExchangeDev* __restrict__ x, InboxLayout L, u
   }
 }
 
+// ------------------------------------------------------------------ Bloom filter built in shares, OR-ed over peer memory
+//
+// A filter for a Gbp-scale assembly is GBs of DRAM-resident bits and its build is bound by random read-modify-writes
+// (hash_num per contig k-mer), the same on every rank if every rank builds its own copy.  With links_bf_alloc_shared each
+// rank inserts 1/N of the k-mers into its own full-size copy; this kernel then makes all copies equal to the OR of all:
+// rank r owns the r-th slice of the words, reads that slice from every peer (NVLink loads), ORs, and stores the result into
+// every copy (NVLink stores) -- a reduce-scatter and an all-gather in one pass, 2 x (N-1)/N x filter bytes over the links.
+// The barriers around it (everybody has inserted / everybody has stored) are the caller's: one per job, host side.
+struct BloomPeers { uint4* p[kMaxP2PRanks]; };
+
+__global__ void __launch_bounds__(kCtaThreads) bloom_or_reduce_kernel(BloomPeers bp, uint32_t n_ranks, uint64_t lo, uint64_t hi, uint64_t tail8,
+                                                                     uint64_t n16)
+{
+  const uint64_t stride = uint64_t(gridDim.x) * blockDim.x;
+  for (uint64_t i = lo + uint64_t(blockIdx.x) * blockDim.x + threadIdx.x; i < hi; i += stride) {
+    uint4 v = make_uint4(0, 0, 0, 0);
+    for (uint32_t r = 0; r < n_ranks; ++r) {
+      const uint4 w = __ldcg(bp.p[r] + i);
+      v.x |= w.x; v.y |= w.y; v.z |= w.z; v.w |= w.w;
+    }
+    for (uint32_t r = 0; r < n_ranks; ++r) __stcg(bp.p[r] + i, v);
+  }
+  if (tail8 && blockIdx.x == 0 && threadIdx.x == 0) {  // a filter of 8 (mod 16) bytes: the last rank takes the odd half word pair
+    unsigned long long v = 0;
+    for (uint32_t r = 0; r < n_ranks; ++r) v |= __ldcg(reinterpret_cast<const unsigned long long*>(bp.p[r] + n16));
+    for (uint32_t r = 0; r < n_ranks; ++r) __stcg(reinterpret_cast<unsigned long long*>(bp.p[r] + n16), v);
+  }
+  __threadfence_system();
+}
+
 }  // namespace links

@@ -434,7 +434,8 @@ __global__ void __launch_bounds__(kCtaThreads) table_seed_kernel(const ulonglong
 // A filter far larger than L2 is built in several passes over the contigs (MODE 0): a pass sets only the bits whose
 // 32-bit word lies in [w_lo, w_hi), so its atomics stay in L2 (3.2 G positions/s with a DRAM-resident 180 MB filter
 // against 21 G/s when the filter fits); the member set is filled by the first pass only.  One pass = {0, ~0, 1}.
-struct BloomPass { uint64_t w_lo, w_hi; int with_set; };
+// share_n > 1 (links_bf_alloc_shared): this rank inserts only the tiles with tile % share_n == share_rank.
+struct BloomPass { uint64_t w_lo, w_hi; int with_set; uint32_t share_rank = 0, share_n = 1; };
 
 template <int MODE>
 __global__ void __launch_bounds__(kCtaThreads) contig_kernel(ContigBatch cb, int k, uint64_t kseed,
@@ -447,6 +448,7 @@ __global__ void __launch_bounds__(kCtaThreads) contig_kernel(ContigBatch cb, int
   __syncthreads();
   unsigned long long n_kmers = 0;
   for (uint32_t tile = blockIdx.x; tile < cb.n_tiles; tile += gridDim.x) {
+    if (MODE == 0 && bp.share_n > 1 && tile % bp.share_n != bp.share_rank) continue;  // another rank's share (block-uniform)
     if (threadIdx.x == 0) s_seg = find_segment(cb.seg_tile_start, cb.n_seq, tile);
     __syncthreads();
     const uint32_t c = s_seg;

@@ -82,6 +82,12 @@ struct links_ctx {
 
   // Bloom filter
   DevBuf d_bloom;
+  // links_bf_alloc_shared: the filter lives in a caller-provided, peer-addressable buffer; this rank inserts only its share
+  // of the contig k-mers and links_bf_allreduce ORs the ranks' copies through peer memory
+  void* bloom_ext = nullptr;
+  void* bloom_peers[kMaxP2PRanks] = {nullptr};
+  uint32_t bf_share_rank = 0, bf_share_n = 1;
+  bool bf_reduced = true;  // false between links_bf_alloc_shared and links_bf_allreduce
   uint64_t bf_bytes = 0;
   uint32_t hash_num = 0;
   bool bf_ready = false, bf_insert = false;
@@ -366,7 +372,7 @@ MemberView member_view(links_ctx* c)
 BloomView bloom_view(links_ctx* c)
 {
   BloomView bf;
-  bf.words = c->d_bloom.as<uint32_t>();
+  bf.words = static_cast<uint32_t*>(c->bloom_ext ? c->bloom_ext : c->d_bloom.p);
   bf.array_bits = c->bf_bytes * 8;
   bf.magic = bf.array_bits ? uint64_t((((unsigned __int128)1) << 64) / bf.array_bits) : 0;
   bf.hash_num = c->hash_num;
@@ -1144,7 +1150,7 @@ int links_create(links_ctx** out, const links_params* p)
       cudaFuncAttributes fa;
       const void* fns[] = {(const void*)pack_kernel, (const void*)rank_build_kernel, (const void*)table_init_kernel,
                            (const void*)contig_kernel<0>, (const void*)contig_kernel<1>, (const void*)contig_kernel<2>,
-                           (const void*)contig_kernel<3>, (const void*)table_seed_kernel,
+                           (const void*)contig_kernel<3>, (const void*)table_seed_kernel, (const void*)bloom_or_reduce_kernel,
                            (const void*)pair_rehash_kernel, (const void*)classify_kernel, (const void*)mirror_expand_kernel,
                            (const void*)gather_rows_kernel, (const void*)pair_bucket_count_kernel, (const void*)pair_bucket_scatter_kernel,
                            (const void*)pair_import_kernel, (const void*)pair_export_kernel, (const void*)route_kernel,
@@ -1234,7 +1240,51 @@ int links_bf_alloc(links_ctx* c, uint64_t bytes, uint32_t hash_num)
   CU(c, cudaSetDevice(c->device));
   CU(c, c->d_bloom.ensure(bytes));
   CU(c, cudaMemsetAsync(c->d_bloom.p, 0, bytes, c->s_compute));
+  c->bloom_ext = nullptr; c->bf_share_n = 1; c->bf_share_rank = 0; c->bf_reduced = true;
   c->bf_bytes = bytes; c->hash_num = hash_num; c->bf_ready = true; c->bf_insert = true;
+  return LINKS_OK;
+}
+
+int links_bf_alloc_shared(links_ctx* c, uint64_t bytes, uint32_t hash_num, uint32_t rank, uint32_t n_ranks, void* const* bloom)
+{
+  if (!c || !bloom) return LINKS_E_INVAL;
+  if (bytes == 0 || (bytes & 7) || hash_num == 0 || hash_num > LINKS_MAX_HASH_NUM)
+    return fail(c, LINKS_E_INVAL, "links_bf_alloc_shared: bytes must be a positive multiple of 8 and hash_num in 1..%u", LINKS_MAX_HASH_NUM);
+  if (n_ranks == 0 || n_ranks > uint32_t(kMaxP2PRanks) || rank >= n_ranks)
+    return fail(c, LINKS_E_LIMIT, "links_bf_alloc_shared: rank %u of %u (at most %d ranks)", rank, n_ranks, kMaxP2PRanks);
+  for (uint32_t r = 0; r < n_ranks; ++r)
+    if (!bloom[r] || (reinterpret_cast<uintptr_t>(bloom[r]) & 15)) return fail(c, LINKS_E_INVAL, "links_bf_alloc_shared: bloom[%u] is null or not 16-byte aligned", r);
+  if (!c->contig_batches.empty()) return fail(c, LINKS_E_INVAL, "links_bf_alloc_shared: call before the job's first links_contigs_push");
+  CU(c, cudaSetDevice(c->device));
+  for (uint32_t r = 0; r < n_ranks; ++r) c->bloom_peers[r] = bloom[r];
+  c->bloom_ext = bloom[rank];
+  c->bf_share_rank = rank; c->bf_share_n = n_ranks; c->bf_reduced = n_ranks == 1;
+  CU(c, cudaMemsetAsync(c->bloom_ext, 0, bytes, c->s_compute));
+  c->bf_bytes = bytes; c->hash_num = hash_num; c->bf_ready = true; c->bf_insert = true;
+  c->member_off = n_ranks > 1;  // the exact member set would hold this rank's share only: every k-mer takes the filter's own bits
+  return LINKS_OK;
+}
+
+int links_bf_allreduce(links_ctx* c)
+{
+  if (!c) return LINKS_E_INVAL;
+  if (!c->bloom_ext) return fail(c, LINKS_E_INVAL, "links_bf_allreduce: the filter was not made by links_bf_alloc_shared");
+  if (c->bf_reduced) return LINKS_OK;
+  NvtxRange nvtx_("links_bf_allreduce");
+  CU(c, cudaSetDevice(c->device));
+  BloomPeers bp;
+  for (uint32_t r = 0; r < c->bf_share_n; ++r) bp.p[r] = static_cast<uint4*>(c->bloom_peers[r]);
+  const uint64_t n16 = c->bf_bytes / 16, tail8 = (c->bf_bytes % 16) / 8;  // bytes is a multiple of 8
+  const uint64_t lo = n16 * c->bf_share_rank / c->bf_share_n, hi = n16 * (c->bf_share_rank + 1) / c->bf_share_n;
+  {
+    Span sp(c, F_BF, c->s_compute);
+    bloom_or_reduce_kernel<<<c->sm_count * 8, kCtaThreads, 0, c->s_compute>>>(bp, c->bf_share_n, lo, hi,
+                                                                             c->bf_share_rank == c->bf_share_n - 1 ? tail8 : 0, n16);
+    c->launches++;
+  }
+  CU(c, cudaGetLastError());
+  CU(c, cudaStreamSynchronize(c->s_compute));  // the caller's barrier that follows must mean "my slice is written everywhere"
+  c->bf_reduced = true;
   return LINKS_OK;
 }
 
@@ -1245,6 +1295,7 @@ int links_bf_load(links_ctx* c, const uint8_t* bits, uint64_t bytes, uint32_t ha
     return fail(c, LINKS_E_INVAL, "links_bf_load: bytes must be a positive multiple of 4 and hash_num in 1..%u", LINKS_MAX_HASH_NUM);
   CU(c, cudaSetDevice(c->device));
   CU(c, c->d_bloom.ensure(bytes));
+  c->bloom_ext = nullptr; c->bf_share_n = 1; c->bf_share_rank = 0; c->bf_reduced = true;
   CU(c, cudaMemcpyAsync(c->d_bloom.p, bits, bytes, cudaMemcpyHostToDevice, c->s_compute));
   CU(c, cudaStreamSynchronize(c->s_compute));
   c->bf_bytes = bytes; c->hash_num = hash_num; c->bf_ready = true; c->bf_insert = false;
@@ -1265,7 +1316,7 @@ int links_bf_download(links_ctx* c, uint8_t* dst)
   if (!c || !dst) return LINKS_E_INVAL;
   if (!c->bf_ready) return fail(c, LINKS_E_INVAL, "links_bf_download: no Bloom filter");
   CU(c, cudaSetDevice(c->device));
-  CU(c, cudaMemcpyAsync(dst, c->d_bloom.p, c->bf_bytes, cudaMemcpyDeviceToHost, c->s_compute));
+  CU(c, cudaMemcpyAsync(dst, bloom_view(c).words, c->bf_bytes, cudaMemcpyDeviceToHost, c->s_compute));
   CU(c, cudaStreamSynchronize(c->s_compute));
   return LINKS_OK;
 }
@@ -1333,7 +1384,7 @@ static int contigs_push_impl(links_ctx* c, const char* seq, const uint8_t* dev_s
       static const uint64_t max_passes = []() { const char* e = getenv("LINKS_BF_MAX_PASSES"); return e ? strtoull(e, nullptr, 10) : 6ull; }();
       if (passes > max_passes) passes = 1;
       for (uint64_t ps = 0; ps < passes; ++ps) {
-        const BloomPass bp{n_words * ps / passes, ps + 1 == passes ? ~0ull : n_words * (ps + 1) / passes, ps == 0};
+        const BloomPass bp{n_words * ps / passes, ps + 1 == passes ? ~0ull : n_words * (ps + 1) / passes, ps == 0, c->bf_share_rank, c->bf_share_n};
         contig_kernel<0><<<grid_for(c, b->n_tiles, 1, 8), kCtaThreads, k * 4 * sizeof(ulonglong2), c->s_compute>>>(
           cb, int(k), c->kseed, c->d_tab.as<ulonglong2>(), bloom_view(c), TableView{nullptr, 0, 0}, member_view(c), c->d_ctr.as<Counters>(), bp);
         c->launches++;
@@ -1442,6 +1493,7 @@ static int reads_push_impl(links_ctx* c, const char* seq, const uint8_t* dev_seq
   if (!c || !off || (!seq && !dev_seq && n && off[n] != off[0])) return LINKS_E_INVAL;
   if (!c->bf_ready) return fail(c, LINKS_E_INVAL, "links_reads_push: no Bloom filter yet");
   if (c->finalized) return fail(c, LINKS_E_INVAL, "links_reads_push: context already finalized (links_reset first)");
+  if (!c->bf_reduced) return fail(c, LINKS_E_INVAL, "links_reads_push: links_bf_allreduce has not been called on the shared Bloom filter");
   if (n == 0) return LINKS_OK;
   // the 64-bit order key (28 bits of read ordinal, 8 of distance index, 28 of k-mer rank) only exists with several distances
   const bool okey_limits = c->prm.n_dist > 1;
@@ -1580,6 +1632,7 @@ int links_reset(links_ctx* c)
   c->tig_len.assign(1, 0);
   c->contig_positions = 0; c->n_tigs_seen = 0;
   c->bf_ready = false; c->bf_insert = false; c->bf_covers_contigs = false;
+  c->bloom_ext = nullptr; c->bf_share_n = 1; c->bf_share_rank = 0; c->bf_reduced = true;
   c->member_buckets = 0; c->member_positions = 0; c->member_off = false;
   c->cand_total = 0; c->known_unique = 0; c->known_cand = 0;
   for (int i = 0; i < links_ctx::kSnaps; ++i) c->snap_live[i] = false;
@@ -2245,7 +2298,7 @@ int links_bf_download_dev(links_ctx* c, void* dev_dst)
   if (!c || !dev_dst) return LINKS_E_INVAL;
   if (!c->bf_ready) return fail(c, LINKS_E_INVAL, "links_bf_download_dev: no Bloom filter");
   CU(c, cudaSetDevice(c->device));
-  CU(c, cudaMemcpyAsync(dev_dst, c->d_bloom.p, c->bf_bytes, cudaMemcpyDeviceToDevice, c->s_compute));
+  CU(c, cudaMemcpyAsync(dev_dst, bloom_view(c).words, c->bf_bytes, cudaMemcpyDeviceToDevice, c->s_compute));
   CU(c, cudaStreamSynchronize(c->s_compute));
   return LINKS_OK;
 }
@@ -2257,6 +2310,7 @@ int links_bf_load_dev(links_ctx* c, const void* dev_bits, uint64_t bytes, uint32
     return fail(c, LINKS_E_INVAL, "links_bf_load_dev: bytes must be a positive multiple of 4 and hash_num in 1..%u", LINKS_MAX_HASH_NUM);
   CU(c, cudaSetDevice(c->device));
   CU(c, c->d_bloom.ensure(bytes));
+  c->bloom_ext = nullptr; c->bf_share_n = 1; c->bf_share_rank = 0; c->bf_reduced = true;
   CU(c, cudaMemcpyAsync(c->d_bloom.p, dev_bits, bytes, cudaMemcpyDeviceToDevice, c->s_compute));
   CU(c, cudaStreamSynchronize(c->s_compute));
   c->bf_bytes = bytes; c->hash_num = hash_num; c->bf_ready = true; c->bf_insert = false;

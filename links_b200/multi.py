@@ -113,6 +113,29 @@ def attach_exchange(L, dist, device, inbox_bytes: int, group=None):
     return buf, hdl
 
 
+def alloc_shared_bloom(dist, device, nbytes: int, group=None):
+    """Peer-addressable Bloom buffers for links_bf_alloc_shared: (keep-alive objects, [pointer of rank r's buffer as seen here]).
+    Allocate once; reuse for every job with the same filter size."""
+    import torch
+    import torch.distributed._symmetric_memory as symm
+    g = group if group is not None else dist.group.WORLD
+    buf = symm.empty((int(nbytes) + 4095) // 4096 * 4096, dtype=torch.uint8, device=device)
+    hdl = symm.rendezvous(buf, g)
+    return (buf, hdl), [int(p) for p in hdl.buffer_ptrs]
+
+
+def build_bloom_shared(L, nbytes: int, hash_num: int, ptrs: list[int], push_contigs, dist, group=None) -> None:
+    """One job's filter built in shares: every rank inserts 1/N of the contig k-mers (push_contigs() pushes ALL contigs, which
+    also stay resident for stage 3), then the copies are OR-ed through peer memory (exchange.cuh bloom_or_reduce_kernel)."""
+    g = group if group is not None else dist.group.WORLD
+    L.bf_alloc_shared(nbytes, hash_num, dist.get_rank(g), dist.get_world_size(g), ptrs)
+    push_contigs()
+    L.sync()
+    dist.barrier(group=g)   # every share is in its rank's copy
+    L.bf_allreduce()
+    dist.barrier(group=g)   # every slice is stored in every copy
+
+
 _BIN_CODE = {-1: 0, 10: 1, 500: 2, 5000: 3, 10000: 4}  # get_distance_bin's range (src/LINKS.hpp:764-770)
 
 

@@ -232,6 +232,15 @@ class Links:
         arr = (C.c_void_p * n_ranks)(*inbox_ptrs)
         self._check(self._lib.links_exchange_attach(self._h, rank, n_ranks, arr, inbox_bytes))
 
+    def bf_alloc_shared(self, nbytes: int, hash_num: int, rank: int, n_ranks: int, bloom_ptrs: list[int]) -> None:
+        """Bloom filter built in shares and OR-ed over peer memory (links_gpu.h links_bf_alloc_shared)."""
+        arr = (C.c_void_p * n_ranks)(*bloom_ptrs)
+        self._check(self._lib.links_bf_alloc_shared(self._h, nbytes, hash_num, rank, n_ranks, arr))
+        self.bf_bytes, self.hash_num = nbytes, hash_num
+
+    def bf_allreduce(self) -> None:
+        self._check(self._lib.links_bf_allreduce(self._h))
+
     def exchange_finish(self) -> None:
         self._check(self._lib.links_exchange_finish(self._h))
 

@@ -400,7 +400,10 @@ def test_pair_exchange_between_contexts_equals_single_context(gpu_lib, name, n_r
                                                          ("adv_offset_k20", 3, 1024, "owner"), ("c1", 2, 1024, "owner"),
                                                          ("c1", 2, 512, "local"),
                                                          # one distance: stage 4 runs beside the imports (classify_increment_owned)
-                                                         ("adv_k40", 2, 1024, "owner"), ("adv_k40", 3, 64, "local")])
+                                                         ("adv_k40", 2, 1024, "owner"), ("adv_k40", 3, 64, "local"),
+                                                         # Bloom filter built in shares + OR over peer memory; table restricted to owned mates
+                                                         ("c1", 2, 1024, "owner+sharedbf+mates"), ("adv_ns_lower", 3, 256, "owner+sharedbf"),
+                                                         ("adv_tandem", 2, 256, "local+mates")])
 def test_peer_memory_exchange_equals_single_context(gpu_lib, name, n_ranks, inbox_mb, dedup):
     """links_exchange_attach/finish as deployed: one PROCESS per rank (tests/_exchange_worker.py), here all
     on GPU 0, inboxes shared through CUDA IPC like peer memory on an NVLink box.  Reads are sharded;
@@ -454,6 +457,8 @@ def test_peer_memory_exchange_equals_single_context(gpu_lib, name, n_ranks, inbo
         iss = b"".join(out[r][job]["issues"] for r in range(n_ranks))
         assert sort_issue_records(iss) == c.expected_issues()
         assert sum(out[r][job]["stats"]["n_candidates"] for r in range(n_ranks)) == stats1["n_candidates"]
+        for r in range(n_ranks):  # a filter built in shares is, after the OR, the reference's filter on every rank
+            assert out[r][job]["bloom_sha"] in (None, c.meta["bloom_sha256"]), f"rank {r} job {job}"
 
 
 @pytest.mark.parametrize("name,host_threads", [("c1", None), ("adv_offset_k20", None), ("adv_ns_lower", None), ("adv_ns_lower", "1"),
