@@ -34,6 +34,9 @@ namespace links {
 #ifndef LINKS_EXTRACT_MIN_CTAS
 #define LINKS_EXTRACT_MIN_CTAS 4
 #endif
+#ifndef LINKS_SEQ_PROBES
+#define LINKS_SEQ_PROBES 0   // 1: one Bloom bit per visit of S2 / S4, survivors re-queued (the reference's early exit: fewest sectors)
+#endif
 #ifndef LINKS_REST_FIRST
 #define LINKS_REST_FIRST 0   // > 0: S2 / S4 test that many of the remaining Bloom bits first and the others only if those are all set
 #endif
@@ -126,6 +129,8 @@ __global__ void __launch_bounds__(kCtaThreads, LINKS_EXTRACT_MIN_CTAS) extract_k
   const bool multi_d = dp.n_dist > 1;
   const uint32_t hn = H ? uint32_t(H) : bf.hash_num;
   const uint32_t h_first = hn < 2u ? hn : 2u;
+  // one Bloom bit per visit of S2 / S4 (queue entries carry the bit index above the 9 bits of the candidate index)
+  constexpr bool kSeq = LINKS_SEQ_PROBES != 0 && H != 0 && kExtractTile <= 512;
   constexpr int kFirst = H >= 2 ? 2 : H;        // compile-time split when H is known
   const uint32_t n_seg = rb.n_seq * dp.n_dist;
   unsigned long long n_cand = 0, n_surv = 0;
@@ -210,6 +215,7 @@ __global__ void __launch_bounds__(kCtaThreads, LINKS_EXTRACT_MIN_CTAS) extract_k
         const uint32_t q = next_q + lane;
         bool pass = false, member = false;
         uint64_t h0 = 0;
+        uint32_t i_next = 0;  // kSeq: the next Bloom bit to test rides in the queue entry's high bits
         if (q < n_tile) {
           uint64_t f, rr;
           LINKS_HASH(pos_a(rank_n(q)), f, rr);
@@ -225,7 +231,16 @@ __global__ void __launch_bounds__(kCtaThreads, LINKS_EXTRACT_MIN_CTAS) extract_k
 #else
           if (has_set) member = member_contains(mv, h0, n_msec);
           if (member) n_probe += hn;  // the filter holds every set key: all hash_num bits are set, no need to look
-          else {
+          else if (kSeq) {
+            // bits are tested one per visit of S2; without a set the first one is tested here
+            if (has_set) pass = true;
+            else {
+              ++n_probe; ++n_load;
+              pass = bloom_bit<SMALL>(bf, h0, kseed, 0) != 0;
+              i_next = 1;
+              if (hn == 1) { member = pass; pass = false; }
+            }
+          } else {
             pass = H ? bloom_probe_fixed<kFirst, SMALL>(bf, h0, kseed, 0, n_probe) : bloom_probe_loop<SMALL>(bf, h0, kseed, 0, h_first, n_probe);
             n_load += h_first;
           }
@@ -234,25 +249,37 @@ __global__ void __launch_bounds__(kCtaThreads, LINKS_EXTRACT_MIN_CTAS) extract_k
         next_q += 32;
         uint32_t slot;
         n1 = warp_push_slot(pass, n1, slot);
-        if (pass) { Q.q1_i[slot] = uint16_t(q); Q.q1_h[slot] = h0; }
-        if (has_set) {  // proven members skip S2
+        if (pass) { Q.q1_i[slot] = uint16_t(q | (i_next << 9)); Q.q1_h[slot] = h0; }
+        if (has_set || kSeq) {  // proven members skip S2
           n2 = warp_push_slot(member, n2, slot);
           if (member) Q.q2_i[slot] = uint16_t(q);
         }
       } else if (stage == 2) {  // ---- S2: remaining probes of A
         const uint32_t take = n1 < 32u ? n1 : 32u;
         n1 -= take;
-        bool pass = false;
+        bool pass = false, again = false;
         uint16_t q = 0;
+        uint64_t h0 = 0;
         if (uint32_t(lane) < take) {
           q = Q.q1_i[n1 + lane];
-          const uint64_t h0 = Q.q1_h[n1 + lane];
-          pass = bloom_probe_rest<H, SMALL>(bf, h0, kseed, h_first, hn, n_probe, n_load);
+          h0 = Q.q1_h[n1 + lane];
+          if (kSeq) {
+            const uint32_t i = q >> 9;
+            ++n_probe; ++n_load;
+            const bool bit = bloom_bit<SMALL>(bf, h0, kseed, i) != 0;
+            pass = bit && i + 1 == hn;
+            again = bit && !pass;
+            q = uint16_t(again ? q + 512u : q & 511u);
+          } else pass = bloom_probe_rest<H, SMALL>(bf, h0, kseed, h_first, hn, n_probe, n_load);
         }
         __syncwarp();
         uint32_t slot;
         n2 = warp_push_slot(pass, n2, slot);
         if (pass) Q.q2_i[slot] = q;
+        if (kSeq) {  // still in the filter after this bit: back into the queue for the next one
+          n1 = warp_push_slot(again, n1, slot);
+          if (again) { Q.q1_i[slot] = q; Q.q1_h[slot] = h0; }
+        }
       } else if (stage == 3) {  // ---- S3: hash B, first probes (ref :554 tests B only if A is in the filter)
         const uint32_t take = n2 < 32u ? n2 : 32u;
         n2 -= take;
@@ -272,7 +299,15 @@ __global__ void __launch_bounds__(kCtaThreads, LINKS_EXTRACT_MIN_CTAS) extract_k
 #else
           if (has_set) member = member_contains(mv, h0, n_msec);
           if (member) n_probe += hn;
-          else {
+          else if (kSeq) {
+            if (has_set) pass = true;
+            else {
+              ++n_probe; ++n_load;
+              pass = bloom_bit<SMALL>(bf, h0, kseed, 0) != 0;
+              q = uint16_t(q + 512u);
+              if (hn == 1) { member = pass; pass = false; q = uint16_t(q & 511u); }
+            }
+          } else {
             pass = H ? bloom_probe_fixed<kFirst, SMALL>(bf, h0, kseed, 0, n_probe) : bloom_probe_loop<SMALL>(bf, h0, kseed, 0, h_first, n_probe);
             n_load += h_first;
           }
@@ -282,25 +317,36 @@ __global__ void __launch_bounds__(kCtaThreads, LINKS_EXTRACT_MIN_CTAS) extract_k
         uint32_t slot;
         n3 = warp_push_slot(pass, n3, slot);
         if (pass) { Q.q3_i[slot] = q; Q.q3_f[slot] = f; Q.q3_r[slot] = rr; }
-        if (has_set) {  // proven members skip S4
+        if (has_set || kSeq) {  // proven members skip S4
           n4 = warp_push_slot(member, n4, slot);
           if (member) { Q.q4_i[slot] = q; Q.q4_f[slot] = f; Q.q4_r[slot] = rr; }
         }
       } else if (stage == 4) {  // ---- S4: remaining probes of B
         const uint32_t take = n3 < 32u ? n3 : 32u;
         n3 -= take;
-        bool pass = false;
+        bool pass = false, again = false;
         uint16_t q = 0;
         uint64_t f = 0, rr = 0;
         if (uint32_t(lane) < take) {
           q = Q.q3_i[n3 + lane]; f = Q.q3_f[n3 + lane]; rr = Q.q3_r[n3 + lane];
           const uint64_t h0 = rr < f ? rr : f;
-          pass = bloom_probe_rest<H, SMALL>(bf, h0, kseed, h_first, hn, n_probe, n_load);
+          if (kSeq) {
+            const uint32_t i = q >> 9;
+            ++n_probe; ++n_load;
+            const bool bit = bloom_bit<SMALL>(bf, h0, kseed, i) != 0;
+            pass = bit && i + 1 == hn;
+            again = bit && !pass;
+            q = uint16_t(again ? q + 512u : q & 511u);
+          } else pass = bloom_probe_rest<H, SMALL>(bf, h0, kseed, h_first, hn, n_probe, n_load);
         }
         __syncwarp();
         uint32_t slot;
         n4 = warp_push_slot(pass, n4, slot);
         if (pass) { Q.q4_i[slot] = q; Q.q4_f[slot] = f; Q.q4_r[slot] = rr; }
+        if (kSeq) {
+          n3 = warp_push_slot(again, n3, slot);
+          if (again) { Q.q3_i[slot] = q; Q.q3_f[slot] = f; Q.q3_r[slot] = rr; }
+        }
       } else if (stage == 5) {  // ---- S5: pair key (ref :546-552) + first-wins insert (ref :370-373)
         const uint32_t take = n4 < 32u ? n4 : 32u;
         n4 -= take;

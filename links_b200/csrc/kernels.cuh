@@ -13,8 +13,8 @@
 //   bloom    u32[bytes/4]          btllib byte array viewed as little-endian words
 //   table    {u64 key,u64 val}[cap+1]   key = ntHash (fwd or rev) of a contig k-mer, EMPTY = ~0
 //                                  val = pos<<32 | tig<<3 | orient<<2 | multiple<<1 | present
-//   pairs    {u64 h_a,u64 h_b}[cap]         16 B slots, two per DRAM sector; 128-bit CAS claims a slot
-//   okeys    u64[cap]                       order key of the slot's pair (only allocated when n_dist > 1)
+//   pairs    {u64 h_a,u64 h_b}[cap]         16 B slots, two per DRAM sector; 128-bit CAS claims a slot.  With several distances
+//            {h_a, h_b, okey, -}[cap]       32 B slots: the order key (first distance wins) sits in the sector its pair is in
 //   rows     u64 key[] + i32 distance[]  (dense packed row key, see pack_row_key)
 #pragma once
 #include "device_prims.cuh"
@@ -36,8 +36,16 @@ struct TableView { TableSlot* slots; uint64_t mask; int shift; /* 64 - log2(cap)
 struct PairView {
   PairSlot* slots; uint64_t mask; int shift;
   ulonglong2* list;            // dense (h_a,h_b) of every distinct pair, in insertion order
-  unsigned long long* okeys;   // per-slot minimum order key; nullptr when there is a single distance
+  uint32_t wide;               // 1: 32-byte slots {h_a, h_b, minimum order key, unused} (several distances); 0: 16-byte slots
 };
+__device__ __forceinline__ PairSlot* pair_slot(const PairView& pv, uint64_t i)
+{
+  return reinterpret_cast<PairSlot*>(reinterpret_cast<char*>(pv.slots) + (i << (4 + pv.wide)));
+}
+__device__ __forceinline__ unsigned long long* pair_okey_ptr(const PairView& pv, uint64_t i)  // wide slots only
+{
+  return reinterpret_cast<unsigned long long*>(pair_slot(pv, i)) + 2;
+}
 
 // counters accumulated on the device (one atomic per warp at kernel end)
 struct Counters {
@@ -510,14 +518,14 @@ __device__ __forceinline__ bool pair_insert(const PairView& pv, uint64_t a, uint
   uint64_t i = slot_hash2(a, b) >> pv.shift;
   bool fresh = false;
   for (;;) {
-    PairSlot* s = pv.slots + i;
+    PairSlot* s = pair_slot(pv, i);
     ulonglong2 cur = __ldcg(reinterpret_cast<const ulonglong2*>(s));
     if (cur.x == kEmpty || cur.y == kEmpty) { // empty (or a torn read of a slot being claimed)
       cur = cas128(s, make_ulonglong2(kEmpty, kEmpty), make_ulonglong2(a, b));
       if (cur.x == kEmpty && cur.y == kEmpty) { fresh = true; cur = make_ulonglong2(a, b); }
     }
     if (cur.x == a && cur.y == b) {
-      if (multi_d) atomicMin(pv.okeys + i, (unsigned long long)okey);
+      if (multi_d) atomicMin(pair_okey_ptr(pv, i), (unsigned long long)okey);  // same sector as the pair: no second DRAM access
       return fresh;
     }
     i = (i + 1) & pv.mask;
@@ -533,9 +541,9 @@ __device__ __forceinline__ uint64_t pair_okey(const PairView& pv, uint64_t a, ui
 {
   uint64_t i = slot_hash2(a, b) >> pv.shift;
   for (;;) {
-    const PairSlot* s = pv.slots + i;
+    const PairSlot* s = pair_slot(pv, i);
     const ulonglong2 cur = __ldcg(reinterpret_cast<const ulonglong2*>(s));
-    if (cur.x == a && cur.y == b) return pv.okeys ? __ldcg(pv.okeys + i) : 0ull;
+    if (cur.x == a && cur.y == b) return pv.wide ? __ldcg(pair_okey_ptr(pv, i)) : 0ull;
     if (cur.x == kEmpty && cur.y == kEmpty) return kEmpty; // not present (cannot happen for listed pairs)
     i = (i + 1) & pv.mask;
   }
@@ -552,14 +560,13 @@ __host__ __device__ __forceinline__ uint32_t okey_d_idx(uint64_t okey)
 }
 
 // re-insert every occupied slot of `src` into `dst` (growth) -- also used by links_pairs_import
-__global__ void pair_rehash_kernel(const PairSlot* __restrict__ src, const unsigned long long* __restrict__ src_okeys, uint64_t n_src,
-                                   PairView dst, Counters* ctr, int count_unique)
+__global__ void pair_rehash_kernel(PairView src, uint64_t n_src, PairView dst, Counters* ctr, int count_unique)
 {
   unsigned long long fresh = 0;
   for (uint64_t i = uint64_t(blockIdx.x) * blockDim.x + threadIdx.x; i < n_src; i += uint64_t(gridDim.x) * blockDim.x) {
-    const PairSlot s = src[i];
+    const PairSlot s = *pair_slot(src, i);
     if (s.a == kEmpty && s.b == kEmpty) continue;
-    if (pair_insert(dst, s.a, s.b, src_okeys ? src_okeys[i] : 0ull, src_okeys != nullptr)) ++fresh;
+    if (pair_insert(dst, s.a, s.b, src.wide ? *pair_okey_ptr(src, i) : 0ull, src.wide != 0)) ++fresh;
   }
   if (count_unique) {
     fresh = warp_sum_ull(fresh);

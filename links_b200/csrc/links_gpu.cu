@@ -124,7 +124,7 @@ struct links_ctx {
   DevBuf contig_ascii;
 
   // pair set
-  DevBuf d_pairs, d_pair_list, d_pair_okeys;  // okeys only when n_dist > 1
+  DevBuf d_pairs, d_pair_list;  // slots of 16 bytes, or 32 with the order key inside when n_dist > 1 (pair_slot_bytes)
   uint64_t pair_cap = 0;
   int extract_ctas_per_sm = 4;
   uint64_t cand_total = 0;   // candidates enqueued so far (upper bound on inserts)
@@ -164,7 +164,7 @@ struct links_ctx {
   InboxLayout x_lay{};
   uint64_t x_epoch = 0;
   DevBuf d_xdev;                                  // ExchangeDev
-  DevBuf d_owned, d_owned_list, d_owned_okeys;    // the pairs this rank owns (imports land here)
+  DevBuf d_owned, d_owned_list;                   // the pairs this rank owns (imports land here)
   uint64_t owned_cap = 0;
   cudaStream_t s_import = nullptr, s_route = nullptr;
   cudaEvent_t ev_routed = nullptr, ev_imported = nullptr, ev_extracted = nullptr;
@@ -350,16 +350,16 @@ TableView table_view(links_ctx* c)
   tv.shift = 64 - log2_ceil(c->table_cap ? c->table_cap : 2);
   return tv;
 }
-PairView pair_view(PairSlot* p, uint64_t cap, ulonglong2* list, unsigned long long* okeys)
+PairView pair_view(PairSlot* p, uint64_t cap, ulonglong2* list, bool wide)
 {
   PairView pv;
-  pv.slots = p; pv.mask = cap ? cap - 1 : 0; pv.shift = 64 - log2_ceil(cap ? cap : 2); pv.list = list; pv.okeys = okeys;
+  pv.slots = p; pv.mask = cap ? cap - 1 : 0; pv.shift = 64 - log2_ceil(cap ? cap : 2); pv.list = list; pv.wide = wide ? 1u : 0u;
   return pv;
 }
+size_t pair_slot_bytes(const links_ctx* c) { return c->prm.n_dist > 1 ? 32 : 16; }
 PairView pair_view(links_ctx* c)
 {
-  return pair_view(c->d_pairs.as<PairSlot>(), c->pair_cap, c->d_pair_list.as<ulonglong2>(),
-                   c->prm.n_dist > 1 ? c->d_pair_okeys.as<unsigned long long>() : nullptr);
+  return pair_view(c->d_pairs.as<PairSlot>(), c->pair_cap, c->d_pair_list.as<ulonglong2>(), c->prm.n_dist > 1);
 }
 uint64_t pair_list_capacity(uint64_t cap) { return cap / 10 * 7 + 1024; }
 MemberView member_view(links_ctx* c)
@@ -596,19 +596,16 @@ int ensure_pair_capacity(links_ctx* c, uint64_t incoming, uint64_t later)
   const double projected = double(c->known_unique) + rate * double(later) + 2.0 * double(incoming);
   const uint64_t want = uint64_t(std::max(projected, double(bound())) / 0.7) + 1024;
   const uint64_t cap = 1ull << log2_ceil(std::max<uint64_t>(want, 1ull << 16));
-  DevBuf nb, nl, nk;
+  DevBuf nb, nl;
   const bool multi_d = c->prm.n_dist > 1;
-  CU(c, nb.ensure(cap * sizeof(PairSlot)));
+  CU(c, nb.ensure(cap * pair_slot_bytes(c)));
   CU(c, nl.ensure(pair_list_capacity(cap) * sizeof(ulonglong2)));
-  if (multi_d) CU(c, nk.ensure(cap * 8));
   {
     Span sp(c, F_GROW, c->s_compute);
-    CU(c, cudaMemsetAsync(nb.p, 0xFF, cap * sizeof(PairSlot), c->s_compute));
-    if (multi_d) CU(c, cudaMemsetAsync(nk.p, 0xFF, cap * 8, c->s_compute));
+    CU(c, cudaMemsetAsync(nb.p, 0xFF, cap * pair_slot_bytes(c), c->s_compute));
     if (c->pair_cap && c->known_unique) {
       pair_rehash_kernel<<<grid_for(c, c->pair_cap, 256, 8), 256, 0, c->s_compute>>>(
-        c->d_pairs.as<PairSlot>(), multi_d ? c->d_pair_okeys.as<unsigned long long>() : nullptr, c->pair_cap,
-        pair_view(nb.as<PairSlot>(), cap, nl.as<ulonglong2>(), multi_d ? nk.as<unsigned long long>() : nullptr), c->d_ctr.as<Counters>(), 0);
+        pair_view(c), c->pair_cap, pair_view(nb.as<PairSlot>(), cap, nl.as<ulonglong2>(), multi_d), c->d_ctr.as<Counters>(), 0);
       c->launches++;
       CU(c, cudaMemcpyAsync(nl.p, c->d_pair_list.p, c->known_unique * sizeof(ulonglong2), cudaMemcpyDeviceToDevice, c->s_compute));
     }
@@ -617,8 +614,8 @@ int ensure_pair_capacity(links_ctx* c, uint64_t incoming, uint64_t later)
   CU(c, cudaStreamSynchronize(c->s_route));  // a routing kernel may still read the old list
   CU(c, cudaStreamSynchronize(c->s_cls));    // and so may an incremental classify; its row buffers were sized for the old table
   c->cls_valid = false;
-  c->d_pairs.release(); c->d_pair_list.release(); c->d_pair_okeys.release();
-  c->d_pairs = nb; c->d_pair_list = nl; c->d_pair_okeys = nk;
+  c->d_pairs.release(); c->d_pair_list.release();
+  c->d_pairs = nb; c->d_pair_list = nl;
   c->pair_cap = cap;
   return LINKS_OK;
 }
@@ -680,8 +677,7 @@ unsigned long long exchange_timeout_ns()
 
 PairView owned_view(links_ctx* c)
 {
-  return pair_view(c->d_owned.as<PairSlot>(), c->owned_cap, c->d_owned_list.as<ulonglong2>(),
-                   c->prm.n_dist > 1 ? c->d_owned_okeys.as<unsigned long long>() : nullptr);
+  return pair_view(c->d_owned.as<PairSlot>(), c->owned_cap, c->d_owned_list.as<ulonglong2>(), c->prm.n_dist > 1);
 }
 
 int ensure_owned(links_ctx* c, uint64_t min_cap)
@@ -699,14 +695,12 @@ int ensure_owned(links_ctx* c, uint64_t min_cap)
   CU(c, cudaStreamSynchronize(c->s_cls));
   CU(c, cudaStreamSynchronize(c->s_import));
   CU(c, cudaStreamSynchronize(c->s_aux));  // links_reset may still be clearing the old table
-  c->d_owned.release(); c->d_owned_list.release(); c->d_owned_okeys.release();
-  CU(c, c->d_owned.ensure(cap * sizeof(PairSlot)));
+  c->d_owned.release(); c->d_owned_list.release();
+  CU(c, c->d_owned.ensure(cap * pair_slot_bytes(c)));
   CU(c, c->d_owned_list.ensure(pair_list_capacity(cap) * sizeof(ulonglong2)));
-  if (multi_d) CU(c, c->d_owned_okeys.ensure(cap * 8));
   c->owned_cap = cap;
   Span sp(c, F_GROW, c->s_import);
-  CU(c, cudaMemsetAsync(c->d_owned.p, 0xFF, cap * sizeof(PairSlot), c->s_import));
-  if (multi_d) CU(c, cudaMemsetAsync(c->d_owned_okeys.p, 0xFF, cap * 8, c->s_import));
+  CU(c, cudaMemsetAsync(c->d_owned.p, 0xFF, cap * pair_slot_bytes(c), c->s_import));
   return LINKS_OK;
 }
 
@@ -806,15 +800,14 @@ int exchange_settle(links_ctx* c)
                           offsetof(ExchangeDev, routed) - offsetof(ExchangeDev, imported), c->s_import));
     CU(c, cudaMemsetAsync(&x->n_owned, 0, 8, c->s_import));
     CU(c, cudaMemsetAsync(&x->owned_overflow, 0, 8, c->s_import));
-    CU(c, cudaMemsetAsync(c->d_owned.p, 0xFF, c->owned_cap * sizeof(PairSlot), c->s_import));
-    if (c->prm.n_dist > 1) CU(c, cudaMemsetAsync(c->d_owned_okeys.p, 0xFF, c->owned_cap * 8, c->s_import));
+    CU(c, cudaMemsetAsync(c->d_owned.p, 0xFF, c->owned_cap * pair_slot_bytes(c), c->s_import));
     Span sp(c, F_EXCHANGE, c->s_import);
     inbox_snapshot_kernel<<<1, kMaxP2PRanks, 0, c->s_import>>>(x, c->x_lay, c->x_epoch, c->owned_cap / 10 * 7);
     inbox_import_kernel<<<c->sm_count * 2, kCtaThreads, 0, c->s_import>>>(x, c->x_lay, c->x_epoch, owned_view(c), c->prm.n_dist > 1 ? 1 : 0);
     c->launches += 2;
     CU(c, cudaGetLastError());
   }
-  std::swap(c->d_pairs, c->d_owned); std::swap(c->d_pair_list, c->d_owned_list); std::swap(c->d_pair_okeys, c->d_owned_okeys);
+  std::swap(c->d_pairs, c->d_owned); std::swap(c->d_pair_list, c->d_owned_list);
   std::swap(c->pair_cap, c->owned_cap);
   c->x_settled = true;
   return LINKS_OK;
@@ -1197,7 +1190,7 @@ void links_destroy(links_ctx* c)
   for (DevBuf* b : {&c->f_keys[0], &c->f_keys[1], &c->f_vals[0], &c->f_vals[1], &c->f_issues, &c->f_tiglen, &c->f_hist,
                     &c->f_scan_tmp, &c->f_flags, &c->f_total, &c->f_okeys, &c->f_olinks, &c->f_ogaps, &c->f_final, &c->f_exch, &c->f_il, &c->f_ig}) b->release();
   c->d_tab.release(); c->d_tab2.release(); c->d_cursor.release(); c->d_dist.release(); c->d_step.release(); c->d_minallowed.release();
-  c->d_bloom.release(); c->d_pairs.release(); c->d_pair_list.release(); c->d_pair_okeys.release(); c->d_ctr.release(); c->d_table.release();
+  c->d_bloom.release(); c->d_pairs.release(); c->d_pair_list.release(); c->d_ctr.release(); c->d_table.release();
   if (c->s_compute && c->own_compute_stream) cudaStreamDestroy(c->s_compute);
   if (c->s_copy) cudaStreamDestroy(c->s_copy);
   if (c->s_aux) cudaStreamDestroy(c->s_aux);
@@ -1211,7 +1204,7 @@ void links_destroy(links_ctx* c)
   if (c->ev_extracted) cudaEventDestroy(c->ev_extracted);
   if (c->ev_routed) cudaEventDestroy(c->ev_routed);
   if (c->ev_imported) cudaEventDestroy(c->ev_imported);
-  c->d_xdev.release(); c->d_owned.release(); c->d_owned_list.release(); c->d_owned_okeys.release(); c->f_rowcnt.release();
+  c->d_xdev.release(); c->d_owned.release(); c->d_owned_list.release(); c->f_rowcnt.release();
   c->d_members.release(); c->d_need_idx.release(); c->d_need_res.release();
   if (c->ev_table) cudaEventDestroy(c->ev_table);
   if (c->ev_fork) cudaEventDestroy(c->ev_fork);
@@ -1451,10 +1444,10 @@ static int push_read_chunk(links_ctx* c, const char* seq, const uint8_t* dev_seq
                    first_read_idx, c->d_cursor.as<unsigned int>()};
       DistParams dp{c->d_dist.as<uint32_t>(), c->d_step.as<uint32_t>(), c->prm.n_dist, c->prm.offset};
       CU(c, cudaMemsetAsync(c->d_cursor.p, 0, sizeof(unsigned int), c->s_compute));
-      MemberMap mm{nullptr, nullptr, nullptr, nullptr, 0, 0};
+      MemberMap mm{nullptr, nullptr, nullptr, nullptr, 0, 0, 0, 0};
       if (mapped) {
         mm = MemberMap{b.mm_bytes.as<uint8_t>(), b.mm_base.as<unsigned long long>(), c->d_need_idx.as<int16_t>(), c->d_need_res.as<uint16_t>(),
-                       c->map_T, c->map_c};
+                       c->map_T, c->map_c, map_magic(c->map_T), map_magic(c->map_c)};
         MapBatch mb{b.packed.as<uint32_t>(), b.off.as<uint64_t>(), b.base0, b.mm_segs.as<uint32_t>(), b.n_seq, map_segs.back(), b.flags.as<uint32_t>()};
         map_fn_for(c->hash_num, bloom_view(c).bits32 != 0)<<<grid_for(c, map_segs.back(), 1, 8), kCtaThreads,
                                                            size_t((c->prm.k + 1) / 2) * 16 * sizeof(ulonglong2), c->s_compute>>>(
@@ -1642,14 +1635,13 @@ int links_reset(links_ctx* c)
   CU(c, cudaMemsetAsync(c->d_cls.p, 0, 64, c->s_compute));
   c->cls_valid = c->cls_on; c->cls_started = false; c->max_read_end = 0;
   if (c->x_attached && c->x_settled) {  // the previous job swapped the owned set in: undo, so each buffer keeps its role (and size)
-    std::swap(c->d_pairs, c->d_owned); std::swap(c->d_pair_list, c->d_owned_list); std::swap(c->d_pair_okeys, c->d_owned_okeys);
+    std::swap(c->d_pairs, c->d_owned); std::swap(c->d_pair_list, c->d_owned_list);
     std::swap(c->pair_cap, c->owned_cap);
   }
   if (c->pair_cap) {
     // off the compute stream: the Bloom build and the first copies do not have to wait for it
     Span sp(c, F_GROW, c->s_aux);
-    CU(c, cudaMemsetAsync(c->d_pairs.p, 0xFF, c->pair_cap * sizeof(PairSlot), c->s_aux));
-    if (c->prm.n_dist > 1) CU(c, cudaMemsetAsync(c->d_pair_okeys.p, 0xFF, c->pair_cap * 8, c->s_aux));
+    CU(c, cudaMemsetAsync(c->d_pairs.p, 0xFF, c->pair_cap * pair_slot_bytes(c), c->s_aux));
   }
   if (c->x_attached) {
     c->x_epoch++;
@@ -1658,8 +1650,7 @@ int links_reset(links_ctx* c)
                           sizeof(ExchangeDev) - offsetof(ExchangeDev, cursor), c->s_compute));
     if (c->owned_cap) {
       Span sp(c, F_GROW, c->s_aux);
-      CU(c, cudaMemsetAsync(c->d_owned.p, 0xFF, c->owned_cap * sizeof(PairSlot), c->s_aux));
-      if (c->prm.n_dist > 1) CU(c, cudaMemsetAsync(c->d_owned_okeys.p, 0xFF, c->owned_cap * 8, c->s_aux));
+      CU(c, cudaMemsetAsync(c->d_owned.p, 0xFF, c->owned_cap * pair_slot_bytes(c), c->s_aux));
     }
   }
   CU(c, cudaEventRecord(c->ev_cleared, c->s_aux));
@@ -2205,8 +2196,7 @@ int links_pairs_clear(links_ctx* c)
   c->known_unique = 0; c->known_cand = c->cand_total;
   Span sp(c, F_EXCHANGE, c->s_compute);
   CU(c, cudaMemsetAsync(reinterpret_cast<char*>(c->d_ctr.p) + offsetof(Counters, n_unique), 0, sizeof(unsigned long long), c->s_compute));
-  if (c->pair_cap) CU(c, cudaMemsetAsync(c->d_pairs.p, 0xFF, c->pair_cap * sizeof(PairSlot), c->s_compute));
-  if (c->pair_cap && c->prm.n_dist > 1) CU(c, cudaMemsetAsync(c->d_pair_okeys.p, 0xFF, c->pair_cap * 8, c->s_compute));
+  if (c->pair_cap) CU(c, cudaMemsetAsync(c->d_pairs.p, 0xFF, c->pair_cap * pair_slot_bytes(c), c->s_compute));
   return LINKS_OK;
 }
 

@@ -31,7 +31,13 @@ struct MemberMap {
   const int16_t* need_idx;         // [T]
   const uint16_t* need_res;        // [c]
   uint32_t T, c;
+  uint64_t magic_T, magic_c;       // ceil(2^64 / T), ceil(2^64 / c): x / T == umul64hi(x, magic_T) exactly for x < 2^32 (T > 1)
 };
+
+// divisions by the period and by the entries per period happen once or twice per candidate: a 64-bit hardware division there
+// (~100 instructions) cost more than the filter walks the map saves
+__host__ __device__ inline uint64_t map_magic(uint32_t d) { return d > 1 ? ~0ull / d + 1 : 0; }
+__device__ __forceinline__ uint32_t map_div(uint32_t x, uint32_t d, uint64_t magic) { return d > 1 ? uint32_t(__umul64hi(uint64_t(x), magic)) : x; }
 
 struct MapBatch {
   const uint32_t* packed; const uint64_t* off; uint64_t base0;
@@ -40,9 +46,10 @@ struct MapBatch {
   const uint32_t* flags;
 };
 
-__device__ __forceinline__ uint64_t map_entry_of(const MemberMap& mm, uint64_t x)
+__device__ __forceinline__ uint64_t map_entry_of(const MemberMap& mm, uint64_t x64)  // x < 2^32 (reads are shorter)
 {
-  return (x / mm.T) * mm.c + uint64_t(__ldg(mm.need_idx + uint32_t(x % mm.T)));
+  const uint32_t x = uint32_t(x64), p = map_div(x, mm.T, mm.magic_T);
+  return uint64_t(p) * mm.c + uint64_t(__ldg(mm.need_idx + (x - p * mm.T)));
 }
 
 // one thread per map entry
@@ -76,7 +83,8 @@ __global__ void __launch_bounds__(kCtaThreads) member_map_kernel(MapBatch mb, Me
     for (int q = threadIdx.x; q < kMapTile; q += kCtaThreads) {
       const uint64_t e = e_begin + q;
       if (e >= n_entries) break;
-      const uint64_t x = (e / mm.c) * mm.T + __ldg(mm.need_res + uint32_t(e % mm.c));
+      const uint32_t p = map_div(uint32_t(e), mm.c, mm.magic_c);  // e < 2^32: a read has fewer entries than bases
+      const uint64_t x = uint64_t(p) * mm.T + __ldg(mm.need_res + (uint32_t(e) - p * mm.c));
       uint8_t v = 0;
       if (x < X) {
         uint64_t f, rr;

@@ -14,6 +14,8 @@ declare -A V=(
   [ctas3]="-DLINKS_EXTRACT_MIN_CTAS=3"
   [tile1024]="-DLINKS_EXTRACT_TILE=1024"
   [tile256]="-DLINKS_EXTRACT_TILE=256"
+  [seq]="-DLINKS_SEQ_PROBES=1"
+  [seq_ctas5]="-DLINKS_SEQ_PROBES=1 -DLINKS_EXTRACT_MIN_CTAS=5"
 )
 [ -n "${VARIANTS:-}" ] && names=$VARIANTS || names="${!V[@]}"
 case "${1:-}" in
