@@ -745,13 +745,19 @@ def check_sharding(args, rank: int, world: int, local_rank: int):
         rec = 24 if len(job.d) > 1 else 16
         est = int(sum(job.closed_form_candidates()) * 0.3) + (1 << 20)
         keep_alive = multi.attach_exchange(L, dist, dev, inbox_bytes=max(64 << 20, est * rec * 2 * 3 // 2)) if p2p else None
-        if rank == 0:
-            L.bf_alloc(bf_bytes, hash_num)
-            L.push_contigs_dev(job.d_contigs.data_ptr(), job.contigs_off, 1)
-        if world > 1:
-            multi.replicate_bloom(L, bf_bytes, hash_num, dist, dev)
-            if rank != 0:
+        bloom_mode = os.environ.get("LINKS_BLOOM", "broadcast")
+        keep_bloom = None
+        if world > 1 and bloom_mode == "shared":  # every rank inserts 1/N of the contig k-mers, OR over peer memory
+            keep_bloom, bloom_ptrs = multi.alloc_shared_bloom(dist, dev, bf_bytes)
+            multi.build_bloom_shared(L, bf_bytes, hash_num, bloom_ptrs, lambda: L.push_contigs_dev(job.d_contigs.data_ptr(), job.contigs_off, 1), dist)
+        else:
+            if rank == 0:
+                L.bf_alloc(bf_bytes, hash_num)
                 L.push_contigs_dev(job.d_contigs.data_ptr(), job.contigs_off, 1)
+            if world > 1:
+                multi.replicate_bloom(L, bf_bytes, hash_num, dist, dev)
+                if rank != 0:
+                    L.push_contigs_dev(job.d_contigs.data_ptr(), job.contigs_off, 1)
         L.push_reads_dev(job.d_reads.data_ptr(), job.reads_off, job.first_read)
         if p2p:
             L.exchange_finish()
@@ -762,7 +768,7 @@ def check_sharding(args, rank: int, world: int, local_rank: int):
         if world > 1 and not p2p:
             rows = multi.gather_rows(rows, dist, dev)
         rows = rows.copy() if rows is not None else None
-        del keep_alive
+        del keep_alive, keep_bloom
     tot = torch.tensor([stats["n_candidates"], stats["n_unique_pairs"], len(issues)], dtype=torch.int64, device=dev)
     if world > 1:
         dist.all_reduce(tot)
@@ -782,7 +788,7 @@ def check_sharding(args, rank: int, world: int, local_rank: int):
         ok = (rows_digest(rows) == rows_digest(rows1) and int(tot[0]) == stats1["n_candidates"]
               and int(tot[1]) == stats1["n_unique_pairs"] and int(tot[2]) == len(issues1))
         emit({"check_sharding": "ok" if ok else "MISMATCH", "n_gpus": world, "workload": args.workload, "scale": args.scale,
-              "contig_table": [args.table or "auto", args.table_single or "auto"],
+              "contig_table": [args.table or "auto", args.table_single or "auto"], "bloom": os.environ.get("LINKS_BLOOM", "broadcast"),
               "rows": len(rows1), "rows_digest_sharded": rows_digest(rows), "rows_digest_single": rows_digest(rows1),
               "candidates": [int(tot[0]), stats1["n_candidates"]], "unique_pairs": [int(tot[1]), stats1["n_unique_pairs"]],
               "issues": [int(tot[2]), len(issues1)], "exchange_rank0": ex})
