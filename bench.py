@@ -86,7 +86,7 @@ def fasta_file_bytes(off: np.ndarray) -> int:
     '>' + 1-based ordinal + newline + sequence + newline -- what tools/make_fullsize_golden.py writes."""
     n = len(off) - 1
     digits = np.floor(np.log10(np.arange(1, n + 1))).astype(np.int64) + 1
-    return int(off[-1]) + int(digits.sum()) + 2 * n
+    return int(off[-1]) + int(digits.sum()) + 3 * n
 
 
 def load_workload(name: str, scale: float, seed_shift: int = 0, coverage: float | None = None):

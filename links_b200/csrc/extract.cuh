@@ -103,8 +103,11 @@ __device__ __forceinline__ uint32_t warp_push_slot(bool pass, uint32_t n, uint32
 // the kernel's last block publishes the new record counts after system-scope fences.  The transfer is part of
 // the extraction, tile by tile; the owner de-duplicates while this rank keeps extracting.
 // SMALL: the filter has fewer than 2^31 bits (bf.bits32 set): 32-bit remainder in bloom_mod
-// MAP: the launch comes with a member map (member_map.cuh); reads without an invalid base take their filter answers from it
-template <int H, bool ROUTED, bool SMALL, bool MAP>
+// MODE 0: S1 tests two Bloom bits, S2 the rest together (fewest round trips: right while the filter and the sets sit in L2)
+// MODE 1 (MAP): the launch comes with a member map (member_map.cuh); reads without an invalid base take their answers from it
+// MODE 2 (SEQ): one Bloom bit per visit of S2 / S4, survivors re-queued -- the reference's early exit, fewest sectors:
+//               right when the filter lives in DRAM, where random sectors are the scarce resource (gather_peak.cu)
+template <int H, bool ROUTED, bool SMALL, int MODE>
 __global__ void __launch_bounds__(kCtaThreads, LINKS_EXTRACT_MIN_CTAS) extract_kernel(ReadBatch rb, DistParams dp, int k, uint64_t kseed,
                                                                  const ulonglong2* __restrict__ g_tab2, BloomView bf,
                                                                  MemberView mv, PairView pv, Counters* __restrict__ ctr,
@@ -130,7 +133,8 @@ __global__ void __launch_bounds__(kCtaThreads, LINKS_EXTRACT_MIN_CTAS) extract_k
   const uint32_t hn = H ? uint32_t(H) : bf.hash_num;
   const uint32_t h_first = hn < 2u ? hn : 2u;
   // one Bloom bit per visit of S2 / S4 (queue entries carry the bit index above the 9 bits of the candidate index)
-  constexpr bool kSeq = LINKS_SEQ_PROBES != 0 && H != 0 && kExtractTile <= 512;
+  constexpr bool MAP = MODE == 1;
+  constexpr bool kSeq = (MODE == 2 || LINKS_SEQ_PROBES != 0) && H != 0 && kExtractTile <= 512;
   constexpr int kFirst = H >= 2 ? 2 : H;        // compile-time split when H is known
   const uint32_t n_seg = rb.n_seq * dp.n_dist;
   unsigned long long n_cand = 0, n_surv = 0;

@@ -177,7 +177,9 @@ struct links_ctx {
   bool cls_on = true, cls_valid = false, cls_started = false;
   cudaStream_t s_cls = nullptr;
   cudaEvent_t ev_cls_in = nullptr, ev_cls_done = nullptr;
-  DevBuf d_cls;               // {classified prefix, list length at the last launch}
+  DevBuf d_cls;               // bounds[r] = length of the pair list after round r-1 (bounds[0] = 0): round r classifies [bounds[r], bounds[r+1])
+  uint32_t cls_round = 0;     // rounds enqueued so far in this job; every round has its own bound, so no stream waits for another
+  static constexpr uint32_t kClsRounds = 8192;
   uint64_t cls_row_cap = 0, cls_pair_cap = 0, cls_issue_cap = 0, max_read_end = 0;
 
   // timing
@@ -399,32 +401,37 @@ MapFn map_fn_sel(uint32_t hash_num)
   }
 }
 MapFn map_fn_for(uint32_t hash_num, bool small_filter) { return small_filter ? map_fn_sel<true>(hash_num) : map_fn_sel<false>(hash_num); }
-template <bool ROUTED, bool SMALL, bool MAP>
+template <bool ROUTED, bool SMALL, int MODE>
 ExtractFn extract_fn_sel(uint32_t hash_num)
 {
   switch (hash_num) {
-  case 6: return extract_kernel<6, ROUTED, SMALL, MAP>;
-  case 7: return extract_kernel<7, ROUTED, SMALL, MAP>;
-  case 8: return extract_kernel<8, ROUTED, SMALL, MAP>;
-  case 9: return extract_kernel<9, ROUTED, SMALL, MAP>;
-  case 10: return extract_kernel<10, ROUTED, SMALL, MAP>;
-  case 13: return extract_kernel<13, ROUTED, SMALL, MAP>;
-  default: return extract_kernel<0, ROUTED, SMALL, MAP>;
+  case 6: return extract_kernel<6, ROUTED, SMALL, MODE>;
+  case 7: return extract_kernel<7, ROUTED, SMALL, MODE>;
+  case 8: return extract_kernel<8, ROUTED, SMALL, MODE>;
+  case 9: return extract_kernel<9, ROUTED, SMALL, MODE>;
+  case 10: return extract_kernel<10, ROUTED, SMALL, MODE>;
+  case 13: return extract_kernel<13, ROUTED, SMALL, MODE>;
+  default: return extract_kernel<0, ROUTED, SMALL, MODE>;
   }
 }
-// small_filter: fewer than 2^31 bits (BloomView::bits32 set), the 32-bit remainder variant; mapped: a member map comes with the launch
-ExtractFn extract_fn_for(uint32_t hash_num, bool routed, bool small_filter, bool mapped)
+// small_filter: fewer than 2^31 bits (BloomView::bits32 set), the 32-bit remainder variant; mode: 0 grouped probes, 1 a member
+// map comes with the launch, 2 one probe per stage visit (extract.cuh)
+ExtractFn extract_fn_for(uint32_t hash_num, bool routed, bool small_filter, int mode)
 {
-  const int v = (routed ? 1 : 0) | (small_filter ? 2 : 0) | (mapped ? 4 : 0);
-  switch (v) {
-  case 0: return extract_fn_sel<false, false, false>(hash_num);
-  case 1: return extract_fn_sel<true, false, false>(hash_num);
-  case 2: return extract_fn_sel<false, true, false>(hash_num);
-  case 3: return extract_fn_sel<true, true, false>(hash_num);
-  case 4: return extract_fn_sel<false, false, true>(hash_num);
-  case 5: return extract_fn_sel<true, false, true>(hash_num);
-  case 6: return extract_fn_sel<false, true, true>(hash_num);
-  default: return extract_fn_sel<true, true, true>(hash_num);
+  const int v = (routed ? 1 : 0) | (small_filter ? 2 : 0);
+  switch (mode * 4 + v) {
+  case 0: return extract_fn_sel<false, false, 0>(hash_num);
+  case 1: return extract_fn_sel<true, false, 0>(hash_num);
+  case 2: return extract_fn_sel<false, true, 0>(hash_num);
+  case 3: return extract_fn_sel<true, true, 0>(hash_num);
+  case 4: return extract_fn_sel<false, false, 1>(hash_num);
+  case 5: return extract_fn_sel<true, false, 1>(hash_num);
+  case 6: return extract_fn_sel<false, true, 1>(hash_num);
+  case 7: return extract_fn_sel<true, true, 1>(hash_num);
+  case 8: return extract_fn_sel<false, false, 2>(hash_num);
+  case 9: return extract_fn_sel<true, false, 2>(hash_num);
+  case 10: return extract_fn_sel<false, true, 2>(hash_num);
+  default: return extract_fn_sel<true, true, 2>(hash_num);
   }
 }
 const uint32_t kExtractVariants[] = {0, 6, 7, 8, 9, 10, 13};
@@ -900,9 +907,8 @@ int classify_increment(links_ctx* c)
     c->cls_started = true;
   }
   if (c->pair_cap != c->cls_pair_cap) { c->cls_valid = false; return LINKS_OK; }
-  unsigned long long* range = c->d_cls.as<unsigned long long>();
-  // the previous round (beside the launch that just ended) must be through before its upper bound moves
-  CU(c, cudaStreamWaitEvent(c->s_compute, c->ev_cls_done, 0));
+  if (c->cls_round + 2 >= links_ctx::kClsRounds) return LINKS_OK;  // out of bounds slots: the rest is classified at finalize
+  unsigned long long* range = c->d_cls.as<unsigned long long>() + c->cls_round++;
   CU(c, cudaMemcpyAsync(range + 1, &c->d_ctr.as<Counters>()->n_unique, 8, cudaMemcpyDeviceToDevice, c->s_compute));
   CU(c, cudaEventRecord(c->ev_cls_in, c->s_compute));
   CU(c, cudaStreamWaitEvent(c->s_cls, c->ev_cls_in, 0));
@@ -914,8 +920,7 @@ int classify_increment(links_ctx* c)
                       c->f_keys[0].as<uint64_t>(), c->f_vals[0].as<int32_t>(), c->cls_row_cap, c->f_issues.as<IssueRec>(), c->cls_issue_cap};
     classify_kernel<<<c->sm_count * 4, kCtaThreads, 0, c->s_cls>>>(pair_view(c), 0, table_view(c), cp, int(c->prm.k),
                                                                    c->d_ctr.as<Counters>(), range);
-    range_advance_kernel<<<1, 1, 0, c->s_cls>>>(range);
-    c->launches += 2;
+    c->launches++;
   }
   CU(c, cudaGetLastError());
   CU(c, cudaEventRecord(c->ev_cls_done, c->s_cls));
@@ -941,9 +946,9 @@ int classify_increment_owned(links_ctx* c)
     c->cls_started = true;
   }
   if (c->owned_cap != c->cls_pair_cap) { c->cls_valid = false; return LINKS_OK; }
-  unsigned long long* range = c->d_cls.as<unsigned long long>();
+  if (c->cls_round + 2 >= links_ctx::kClsRounds) return LINKS_OK;
+  unsigned long long* range = c->d_cls.as<unsigned long long>() + c->cls_round++;
   ExchangeDev* x = c->d_xdev.as<ExchangeDev>();
-  CU(c, cudaStreamWaitEvent(c->s_import, c->ev_cls_done, 0));  // the previous round still reads its upper bound
   CU(c, cudaMemcpyAsync(range + 1, &x->n_owned, 8, cudaMemcpyDeviceToDevice, c->s_import));
   CU(c, cudaEventRecord(c->ev_imported, c->s_import));
   CU(c, cudaStreamWaitEvent(c->s_cls, c->ev_imported, 0));
@@ -955,8 +960,7 @@ int classify_increment_owned(links_ctx* c)
                       c->f_keys[0].as<uint64_t>(), c->f_vals[0].as<int32_t>(), c->cls_row_cap, c->f_issues.as<IssueRec>(), c->cls_issue_cap};
     classify_kernel<<<c->sm_count * 2, kCtaThreads, 0, c->s_cls>>>(owned_view(c), 0, table_view(c), cp, int(c->prm.k),
                                                                    c->d_ctr.as<Counters>(), range);
-    range_advance_kernel<<<1, 1, 0, c->s_cls>>>(range);
-    c->launches += 2;
+    c->launches++;
   }
   CU(c, cudaGetLastError());
   CU(c, cudaEventRecord(c->ev_cls_done, c->s_cls));
@@ -1064,8 +1068,8 @@ int links_create(links_ctx** out, const links_params* p)
   CUC(cudaStreamCreateWithFlags(&c->s_cls, cudaStreamNonBlocking));
   CUC(cudaEventCreateWithFlags(&c->ev_cls_in, cudaEventDisableTiming));
   CUC(cudaEventCreateWithFlags(&c->ev_cls_done, cudaEventDisableTiming));
-  CUC(c->d_cls.ensure(64));
-  CUC(cudaMemset(c->d_cls.p, 0, 64));
+  CUC(c->d_cls.ensure(size_t(links_ctx::kClsRounds) * 8));
+  CUC(cudaMemset(c->d_cls.p, 0, size_t(links_ctx::kClsRounds) * 8));
   { const char* e = getenv("LINKS_INCREMENTAL_CLASSIFY"); c->cls_on = !(e && e[0] == '0'); c->cls_valid = c->cls_on; }
   { const char* e = getenv("LINKS_TABLE_MODE"); c->table_mode = !e ? LINKS_TABLE_AUTO : !strcmp(e, "full") ? LINKS_TABLE_FULL : !strcmp(e, "mates") ? LINKS_TABLE_MATES : LINKS_TABLE_AUTO; }
   CUC(cudaEventCreateWithFlags(&c->ev_extracted, cudaEventDisableTiming));
@@ -1126,8 +1130,8 @@ int links_create(links_ctx** out, const links_params* p)
     host_mark(c, "create: streams, events, hash tables on device");
     int occ = 0;
     for (uint32_t h : kExtractVariants)
-      for (int v = 0; v < 8; ++v) {
-        const ExtractFn fn = extract_fn_for(h, (v & 1) != 0, (v & 2) != 0, (v & 4) != 0);
+      for (int v = 0; v < 12; ++v) {
+        const ExtractFn fn = extract_fn_for(h, (v & 1) != 0, (v & 2) != 0, v >> 2);
         CUC(cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, int(extract_smem_bytes(p->k))));
         CUC(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, fn, kCtaThreads, extract_smem_bytes(p->k)));
         c->extract_ctas_per_sm = std::max(occ, 1);
@@ -1454,7 +1458,10 @@ static int push_read_chunk(links_ctx* c, const char* seq, const uint8_t* dev_seq
           mb, mm, int(c->prm.k), c->prm.offset, c->kseed, c->d_tab2.as<ulonglong2>(), bloom_view(c), member_view(c), c->d_ctr.as<Counters>());
         c->launches++;
       }
-      extract_fn_for(c->hash_num, fused, bloom_view(c).bits32 != 0, mapped)<<<grid_for(c, b.n_tiles, kWarpsPerCta, c->extract_ctas_per_sm), kCtaThreads,
+      // probes one at a time (fewest sectors) once the filter lives in DRAM; grouped (fewest round trips) while it sits in L2
+      static const int seq_env = []() { const char* e = getenv("LINKS_SEQ_PROBES"); return !e ? -1 : e[0] == '0' ? 0 : 1; }();
+      const bool seq = seq_env >= 0 ? seq_env == 1 : c->bf_bytes > (64ull << 20);
+      extract_fn_for(c->hash_num, fused, bloom_view(c).bits32 != 0, mapped ? 1 : seq ? 2 : 0)<<<grid_for(c, b.n_tiles, kWarpsPerCta, c->extract_ctas_per_sm), kCtaThreads,
                                            extract_smem_bytes(c->prm.k), c->s_compute>>>(
         rb, dp, int(c->prm.k), c->kseed, c->d_tab2.as<ulonglong2>(), bloom_view(c), member_view(c),
         pair_view(c), c->d_ctr.as<Counters>(), c->d_xdev.as<ExchangeDev>(), c->x_lay, c->x_epoch, mm);
@@ -1506,7 +1513,11 @@ static int reads_push_impl(links_ctx* c, const char* seq, const uint8_t* dev_seq
     const char* e = getenv("LINKS_CHUNK_BASES");
     return e ? strtoull(e, nullptr, 10) : (64ull << 20);
   }();
-  uint64_t kChunkBases = dev_seq ? kChunkMax : std::min<uint64_t>(kChunkMax, 8ull << 20);
+  // Device-resident pushes go in equal chunks of the maximum size.  LINKS_CHUNK_SHAPE=taper makes them ramp up and taper off
+  // like host pushes (a short first pack, a short last classify); measured on C2: 5.51 ms per job against 5.37 flat -- the
+  // extra launches cost more than the shorter tail saves -- so it is not the default.
+  static const bool kFlat = []() { const char* e = getenv("LINKS_CHUNK_SHAPE"); return !(e && !strcmp(e, "taper")); }();
+  uint64_t kChunkBases = dev_seq ? (kFlat ? kChunkMax : std::min<uint64_t>(kChunkMax, 32ull << 20)) : std::min<uint64_t>(kChunkMax, 8ull << 20);
   const uint64_t kChunkCand = 1ull << 27;
   // upper bound on candidates per (read, distance): exact when the read has no invalid base (reference src/LINKS.hpp:525-543)
   auto seg_count = [&](uint64_t len, uint32_t di) -> uint64_t {
@@ -1535,7 +1546,7 @@ static int reads_push_impl(links_ctx* c, const char* seq, const uint8_t* dev_seq
     uint64_t tiles = 0, cand = 0, map_entries = 0, map_tiles = 0;
     uint32_t i = i0;
     // host pushes also taper off: the last chunk's kernels run after its copy with nothing left to overlap
-    const uint64_t chunk_limit = dev_seq ? kChunkBases : std::min(kChunkBases, std::max<uint64_t>((off[n] - off[i0]) / 2, 8ull << 20));
+    const uint64_t chunk_limit = dev_seq && kFlat ? kChunkBases : std::min(kChunkBases, std::max<uint64_t>((off[n] - off[i0]) / 2, dev_seq ? 16ull << 20 : 8ull << 20));
     for (; i < n; ++i) {
       const uint64_t len = off[i + 1] - off[i];
       if (i > i0 && (off[i + 1] - off[i0] > chunk_limit || cand > kChunkCand || uint64_t(i - i0) * nd > (1ull << 26))) break;
@@ -1632,7 +1643,8 @@ int links_reset(links_ctx* c)
   for (int i = 0; i < links_ctx::kSlots; ++i) c->slot_used[i] = false;
   c->next_slot = 0;  // same chunk -> slot assignment every job: slot buffers stop growing after the first one
   CU(c, cudaMemsetAsync(c->d_ctr.p, 0, sizeof(Counters), c->s_compute));
-  CU(c, cudaMemsetAsync(c->d_cls.p, 0, 64, c->s_compute));
+  CU(c, cudaMemsetAsync(c->d_cls.p, 0, 64, c->s_compute));  // bounds[0] = 0; later bounds are written before they are read
+  c->cls_round = 0;
   c->cls_valid = c->cls_on; c->cls_started = false; c->max_read_end = 0;
   if (c->x_attached && c->x_settled) {  // the previous job swapped the owned set in: undo, so each buffer keeps its role (and size)
     std::swap(c->d_pairs, c->d_owned); std::swap(c->d_pair_list, c->d_owned_list);
@@ -1827,7 +1839,7 @@ int links_finalize(links_ctx* c, links_row** rows_out, uint64_t* n_rows_out, lin
   for (int attempt = 0; attempt < 2; ++attempt) {
     CU(c, d_issues.ensure(issue_cap * sizeof(IssueRec)));
     const bool rest_only = incremental && attempt == 0;  // pairs up to the last extract launch but one are already classified
-    unsigned long long* range = c->d_cls.as<unsigned long long>();
+    unsigned long long* range = c->d_cls.as<unsigned long long>() + c->cls_round;  // [end of the last round, all pairs)
     if (rest_only) {
       CU(c, cudaMemcpyAsync(range + 1, &c->d_ctr.as<Counters>()->n_unique, 8, cudaMemcpyDeviceToDevice, s));
     } else {

@@ -86,6 +86,19 @@ def job_layout(name: str, scale: float):
     rep_len = rng.integers(2000, 5001, size=n_rep).astype(np.uint64)
     rep_src = (rng.random(n_rep) * (G - rep_len.astype(np.float64))).astype(np.uint64)
     rep_dst = (rng.random(n_rep) * (G - rep_len.astype(np.float64))).astype(np.uint64)
+    if n_rep:
+        # destinations must not overlap: two copies landing on the same bytes would race on the device and the genome would
+        # differ from one generation to the next (every rank generates its own copy and they must be identical)
+        order = np.argsort(rep_dst, kind="stable")
+        rep_dst, rep_src, rep_len = rep_dst[order], rep_src[order], rep_len[order]
+        keep = np.ones(n_rep, dtype=bool)
+        end = 0
+        for i in range(n_rep):
+            if int(rep_dst[i]) < end:
+                keep[i] = False
+            else:
+                end = int(rep_dst[i]) + int(rep_len[i])
+        rep_dst, rep_src, rep_len = rep_dst[keep], rep_src[keep], rep_len[keep]
     # contigs: exponential lengths around the mean, 1 % short, a 0-2 kb gap between neighbours
     rng = np.random.default_rng(43)
     mean_len = max(G / nc - 1000, 200)
@@ -150,7 +163,7 @@ def make_config_dev(name: str, scale: float, device, rank: int = 0, world: int =
             _ck(lib.synth_fill_runs(d_contigs.data_ptr(), t_pos.data_ptr(), t_ln.data_ptr(), len(pos), ord("N")), "N runs")
         n = len(c_len)
         digits = np.floor(np.log10(np.arange(1, n + 1))).astype(np.int64) + 1
-        file_bytes = int(c_off[-1]) + int(digits.sum()) + 2 * n  # ">" + ordinal + "\n" + sequence + "\n"
+        file_bytes = int(c_off[-1]) + int(digits.sum()) + 3 * n  # ">" + ordinal + "\n" + sequence + "\n"
         r_start, r_len, r_rc = lay["reads"]
         R = len(r_len)
         lo, hi = read_range if read_range is not None else (R * rank // world, R * (rank + 1) // world)

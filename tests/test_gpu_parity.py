@@ -699,3 +699,29 @@ def test_unmodified_wrapper_chain_over_gpu_binary(gpu_lib, tmp_path, layout):
     meta = json.load(open(os.path.join(GOLDEN_DIR, "c1", "layout", "layout.json")))
     assert hashlib.sha256(open(wd / "installation_test.scaffolds.fa", "rb").read()).hexdigest() == meta["scaffolds_fa_sha256"]
     assert open(wd / "installation_test.scaffolds", "rb").read() == open(os.path.join(GOLDEN_DIR, "c1", "layout", "expected.scaffolds"), "rb").read()
+
+
+def test_device_generator_is_deterministic_and_shards_concatenate(gpu_lib):
+    """links_b200/synth_dev.py (the human-scale workload of BASELINE.json configs[3], generated on the device): the same
+    bytes from every generation, and the ranks' read shards concatenate to exactly the reads one rank generates -- the
+    premise of the strong-scaling runs and of `bench.py --check-sharding` on that workload."""
+    import torch
+
+    from links_b200 import synth_dev
+    dev = torch.device("cuda", 0)
+    a = synth_dev.make_config_dev("c4_human_3gbp", 0.002, dev)
+    b = synth_dev.make_config_dev("c4_human_3gbp", 0.002, dev)
+    assert torch.equal(a.d_contigs, b.d_contigs) and torch.equal(a.d_reads, b.d_reads)
+    assert np.array_equal(a.contigs_off, b.contigs_off) and np.array_equal(a.reads_off, b.reads_off)
+    parts = [synth_dev.make_config_dev("c4_human_3gbp", 0.002, dev, rank=r, world=3) for r in range(3)]
+    assert torch.equal(torch.cat([p.d_reads for p in parts]), a.d_reads)
+    assert [p.first_read for p in parts] == [0, len(parts[0].reads_off) - 1, len(parts[0].reads_off) + len(parts[1].reads_off) - 2]
+    assert sum(len(p.reads_off) - 1 for p in parts) == a.n_reads_total == len(a.reads_off) - 1
+    for p in parts:
+        assert torch.equal(p.d_contigs, a.d_contigs)
+    reads = a.d_reads.cpu().numpy()
+    assert set(np.unique(reads)) <= set(b"ACGTN") and set(np.unique(a.d_contigs.cpu().numpy())) <= set(b"ACGTN")
+    cov = len(reads) / a.genome_bp
+    assert 18.0 < cov < 22.0  # 20x: insertions and deletions cancel on average
+    lens = np.diff(a.reads_off.astype(np.int64))
+    assert 15_000 < lens.mean() < 25_000 and lens.min() >= 150
