@@ -32,7 +32,8 @@ constexpr int kCtaThreads = 256;
 struct TableSlot { uint64_t key, val; };
 struct PairSlot { uint64_t a, b; };
 
-struct TableView { TableSlot* slots; uint64_t mask; int shift; /* 64 - log2(cap) */ };
+// occ (MATES build only): one bit per 32-byte sector of the table (two slots), set when a slot of it has been claimed
+struct TableView { TableSlot* slots; uint64_t mask; int shift; /* 64 - log2(cap) */ uint32_t* occ = nullptr; };
 struct PairView {
   PairSlot* slots; uint64_t mask; int shift;
   ulonglong2* list;            // dense (h_a,h_b) of every distinct pair, in insertion order
@@ -400,8 +401,14 @@ __device__ __forceinline__ void table_seed(const TableView& tv, uint64_t h)
   uint64_t i = slot_hash1(h) >> tv.shift;
   for (;;) {
     ulonglong2 cur = __ldcg(reinterpret_cast<const ulonglong2*>(&tv.slots[i]));
-    if (cur.x == kEmpty) cur = cas128_raw(&tv.slots[i], make_ulonglong2(kEmpty, 0ull), make_ulonglong2(h, 0ull));  // (a stale "empty" is settled by the CAS)
-    if (cur.x == kEmpty || cur.x == h) return;
+    if (cur.x == kEmpty) {
+      cur = cas128_raw(&tv.slots[i], make_ulonglong2(kEmpty, 0ull), make_ulonglong2(h, 0ull));  // (a stale "empty" is settled by the CAS)
+      if (cur.x == kEmpty) {  // claimed: mark the sector occupied (read by the NEXT kernel only)
+        if (tv.occ) atomicOr(tv.occ + (i >> 6), 1u << ((i >> 1) & 31));
+        return;
+      }
+    }
+    if (cur.x == h) return;
     i = (i + 1) & tv.mask;
   }
 }
@@ -410,6 +417,11 @@ __device__ __forceinline__ void table_update(const TableView& tv, uint64_t h, ui
 {
   if (h == kEmpty) { table_insert(tv, h, payload); return; }
   uint64_t i = slot_hash1(h) >> tv.shift;
+  // Most contig k-mers are not mates of THIS rank's pairs (with the pairs split over N ranks: ~1 - 1/N of them), and each
+  // such miss would cost a random DRAM sector.  The occupancy bitmap (1 bit per sector, 1/256 of the table: L2-resident)
+  // answers the common case first: nothing was ever claimed in the home sector => the home slot is empty => the key,
+  // which linear probing would have put there or after an unbroken run of occupied slots, is absent.
+  if (tv.occ && !((__ldg(tv.occ + (i >> 6)) >> ((i >> 1) & 31)) & 1u)) return;
   for (;;) {
     // keys are final (seeded by the previous kernel); values move 0 -> payload|1 -> |2 only
     ulonglong2 s = __ldcg(reinterpret_cast<const ulonglong2*>(&tv.slots[i]));

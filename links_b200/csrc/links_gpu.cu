@@ -141,7 +141,8 @@ struct links_ctx {
   DevBuf d_ctr;
 
   // contig table (built on s_aux while the reads stream in; finalize waits on ev_table)
-  DevBuf d_table;
+  DevBuf d_table, d_table_occ;  // occ: the MATES build's sector-occupancy bitmap (kernels.cuh TableView::occ)
+  bool table_has_occ = false;
   uint64_t table_cap = 0;
   cudaEvent_t ev_table = nullptr, ev_fork = nullptr;
   size_t table_batches_built = 0;
@@ -350,6 +351,7 @@ TableView table_view(links_ctx* c)
   tv.slots = c->d_table.as<TableSlot>();
   tv.mask = c->table_cap ? c->table_cap - 1 : 0;
   tv.shift = 64 - log2_ceil(c->table_cap ? c->table_cap : 2);
+  tv.occ = c->table_has_occ ? c->d_table_occ.as<uint32_t>() : nullptr;
   return tv;
 }
 PairView pair_view(PairSlot* p, uint64_t cap, ulonglong2* list, bool wide)
@@ -1194,7 +1196,7 @@ void links_destroy(links_ctx* c)
   for (DevBuf* b : {&c->f_keys[0], &c->f_keys[1], &c->f_vals[0], &c->f_vals[1], &c->f_issues, &c->f_tiglen, &c->f_hist,
                     &c->f_scan_tmp, &c->f_flags, &c->f_total, &c->f_okeys, &c->f_olinks, &c->f_ogaps, &c->f_final, &c->f_exch, &c->f_il, &c->f_ig}) b->release();
   c->d_tab.release(); c->d_tab2.release(); c->d_cursor.release(); c->d_dist.release(); c->d_step.release(); c->d_minallowed.release();
-  c->d_bloom.release(); c->d_pairs.release(); c->d_pair_list.release(); c->d_ctr.release(); c->d_table.release();
+  c->d_table_occ.release(); c->d_bloom.release(); c->d_pairs.release(); c->d_pair_list.release(); c->d_ctr.release(); c->d_table.release();
   if (c->s_compute && c->own_compute_stream) cudaStreamDestroy(c->s_compute);
   if (c->s_copy) cudaStreamDestroy(c->s_copy);
   if (c->s_aux) cudaStreamDestroy(c->s_aux);
@@ -1700,6 +1702,7 @@ static int build_table(links_ctx* c, cudaStream_t st)
   const uint64_t cap = full_table_cap(c);
   CU(c, c->d_table.ensure((cap + 1) * sizeof(TableSlot)));
   c->table_cap = cap;
+  c->table_has_occ = false;
   Span sp(c, F_TABLE, st);
   CU(c, cudaMemsetAsync(reinterpret_cast<char*>(c->d_ctr.p) + offsetof(Counters, n_contig_kmers), 0, sizeof(unsigned long long), st));
   // keys = EMPTY (all ones), vals = 0
@@ -1728,10 +1731,16 @@ static int build_table(links_ctx* c, cudaStream_t st)
 static int build_table_mates(links_ctx* c, cudaStream_t st, uint64_t n_pairs)
 {
   const uint32_t k = c->prm.k;
-  const uint64_t cap = 1ull << log2_ceil(std::max<uint64_t>(n_pairs * 2 * 10 / 6, 1ull << 10));  // <= 2 hashes per pair, load <= 0.6
+  // <= 2 hashes per pair; load <= 0.4 (a miss that gets past the occupancy bitmap should end in its first sector), but never
+  // more than a quarter of the device for the table
+  uint64_t cap = 1ull << log2_ceil(std::max<uint64_t>(n_pairs * 2 * 10 / 4, 1ull << 10));
+  while (cap > (1ull << 10) && (cap + 1) * sizeof(TableSlot) > c->dev_total_mem / 4 && (cap >> 1) * 6 / 10 >= n_pairs * 2) cap >>= 1;
   CU(c, c->d_table.ensure((cap + 1) * sizeof(TableSlot)));
+  CU(c, c->d_table_occ.ensure(cap / 16 + 64));
   c->table_cap = cap;
+  c->table_has_occ = true;
   Span sp(c, F_TABLE, st);
+  CU(c, cudaMemsetAsync(c->d_table_occ.p, 0, cap / 16 + 64, st));
   CU(c, cudaMemsetAsync(reinterpret_cast<char*>(c->d_ctr.p) + offsetof(Counters, n_contig_kmers), 0, sizeof(unsigned long long), st));
   table_init_kernel<<<grid_for(c, cap + 1, 256 * 4, 16), 256, 0, st>>>(c->d_table.as<TableSlot>(), cap + 1);
   c->launches++;
