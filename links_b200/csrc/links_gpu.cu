@@ -1548,7 +1548,14 @@ static int reads_push_impl(links_ctx* c, const char* seq, const uint8_t* dev_seq
     uint64_t tiles = 0, cand = 0, map_entries = 0, map_tiles = 0;
     uint32_t i = i0;
     // host pushes also taper off: the last chunk's kernels run after its copy with nothing left to overlap
-    const uint64_t chunk_limit = dev_seq && kFlat ? kChunkBases : std::min(kChunkBases, std::max<uint64_t>((off[n] - off[i0]) / 2, dev_seq ? 16ull << 20 : 8ull << 20));
+    uint64_t chunk_limit = dev_seq && kFlat ? kChunkBases : std::min(kChunkBases, std::max<uint64_t>((off[n] - off[i0]) / 2, dev_seq ? 16ull << 20 : 8ull << 20));
+    // with an exchange attached the records of the LAST launch are imported, and their pairs classified, after every rank has
+    // finished: a short last chunk is a short tail for all ranks (LINKS_EXCHANGE_LAST_CHUNK bases; 0 = off)
+    static const uint64_t kLastChunk = []() { const char* e = getenv("LINKS_EXCHANGE_LAST_CHUNK"); return e ? strtoull(e, nullptr, 10) : 0ull; }();
+    if (c->x_attached && kLastChunk) {
+      const uint64_t remaining = off[n] - off[i0];
+      if (remaining > kLastChunk + (kLastChunk >> 1) && remaining <= chunk_limit) chunk_limit = remaining - kLastChunk;
+    }
     for (; i < n; ++i) {
       const uint64_t len = off[i + 1] - off[i];
       if (i > i0 && (off[i + 1] - off[i0] > chunk_limit || cand > kChunkCand || uint64_t(i - i0) * nd > (1ull << 26))) break;
