@@ -506,6 +506,117 @@ __global__ void __launch_bounds__(kCtaThreads) contig_kernel(ContigBatch cb, int
   }
 }
 
+// ------------------------------------------------------------------ Bloom build for filters beyond L2: partition, then apply
+//
+// hash_num random read-modify-writes per contig k-mer into a DRAM-resident filter cost two DRAM operations each (sector
+// in, sector back) and DRAM delivers ~43 G random sectors/s (tools/gather_peak.cu): 3.2 G k-mers/s, the longest stage of a
+// Gbp-scale job.  Restricting a pass to an L2-sized block of the filter (BloomPass) keeps the atomics in L2 but hashes
+// every k-mer once per block.  Here every k-mer is hashed ONCE: its hash_num updates are appended, as 4-byte entries
+// (word within the block << 5 | bit), to one bucket per L2-sized block of the filter -- sequential streams, which DRAM
+// takes at copy speed: 2 x 4 B x hash_num streamed per k-mer instead of 2 x hash_num random sectors -- and a second
+// kernel replays bucket after bucket with the atomics landing in an L2-resident block.
+struct BloomBuckets {
+  uint32_t* entries;             // bucket b occupies [b * cap, (b + 1) * cap)
+  unsigned long long* cursor;    // [n_buckets] entries appended (may exceed cap: the excess is dropped and flagged)
+  uint64_t cap;
+  uint32_t n_buckets, block_shift;  // filter word w belongs to bucket w >> block_shift
+  unsigned int* overflow;
+};
+constexpr int kMaxBloomBuckets = 256;
+
+template <bool WITH_SET>
+__global__ void __launch_bounds__(kCtaThreads) bloom_partition_kernel(ContigBatch cb, uint32_t tile_lo, uint32_t tile_hi, int k, uint64_t kseed,
+                                                                     const ulonglong2* __restrict__ g_tab, BloomView bf, MemberView mv,
+                                                                     BloomBuckets bk, uint32_t share_rank, uint32_t share_n)
+{
+  constexpr int kWarps = kCtaThreads / 32;
+  extern __shared__ ulonglong2 s_tab[];
+  // per-warp counters: a warp counts its own entries per bucket (lanes with the same bucket are found with match.any, one
+  // plain add per distinct bucket), so no shared-memory atomics and no contention however few buckets there are
+  __shared__ uint32_t s_cnt[kWarps][kMaxBloomBuckets];
+  __shared__ unsigned long long s_base[kMaxBloomBuckets];
+  __shared__ uint32_t s_seg;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const uint32_t lt = (1u << lane) - 1u;
+  for (int i = threadIdx.x; i < k * 4; i += blockDim.x) s_tab[i] = g_tab[i];
+  for (uint32_t i = threadIdx.x; i < uint32_t(kWarps) * kMaxBloomBuckets; i += blockDim.x) (&s_cnt[0][0])[i] = 0;
+  __syncthreads();
+  const uint32_t block_mask = (1u << bk.block_shift) - 1u;
+  for (uint32_t tile = tile_lo + blockIdx.x; tile < tile_hi; tile += gridDim.x) {
+    if (share_n > 1 && tile % share_n != share_rank) continue;  // another rank's share (block-uniform)
+    if (threadIdx.x == 0) s_seg = find_segment(cb.seg_tile_start, cb.n_seq, tile);
+    __syncthreads();
+    const uint32_t c = s_seg;
+    const uint64_t g0 = cb.off[c] - cb.base0, len = cb.off[c + 1] - cb.off[c];
+    const uint64_t npos = len - k + 1;
+    const uint64_t p_begin = uint64_t(tile - cb.seg_tile_start[c]) * kTile;
+    for (int q0 = 0; q0 < kTile; q0 += kCtaThreads) {  // one round: every thread one position, hash_num entries
+      const uint64_t p = p_begin + q0 + threadIdx.x;
+      const bool live = p < npos && window_valid(cb.inv, g0 + p, k);
+      uint64_t h0 = 0;
+      if (live) {
+        uint64_t f, r;
+        hash_kmer(cb.packed, g0 + p, k, s_tab, f, r);
+        h0 = r < f ? r : f;
+        if (WITH_SET && mv.buckets) member_insert(mv, h0);
+      }
+      __syncwarp();
+      for (uint32_t i = 0; i < bf.hash_num; ++i) {  // pass 1: count per bucket
+        uint32_t b = 0xFFFFFFFFu;
+        if (live) b = uint32_t(bloom_mod(multihash_i(h0, kseed, i), bf) >> 5) >> bk.block_shift;
+        const uint32_t peers = __match_any_sync(0xffffffffu, b);
+        if (live && lane == __ffs(peers) - 1) s_cnt[warp][b] += __popc(peers);
+        __syncwarp();
+      }
+      __syncthreads();
+      for (uint32_t b = threadIdx.x; b < bk.n_buckets; b += blockDim.x) {  // one reservation per bucket and round
+        uint32_t total = 0;
+#pragma unroll
+        for (int w = 0; w < kWarps; ++w) { const uint32_t n = s_cnt[w][b]; s_cnt[w][b] = total; total += n; }  // -> each warp's offset
+        s_base[b] = total ? atomicAdd(bk.cursor + b, (unsigned long long)total) : 0ull;
+      }
+      __syncthreads();
+      for (uint32_t i = 0; i < bf.hash_num; ++i) {  // pass 2: write (the multi-hash is a multiply and a shift: cheaper to redo than to keep)
+        uint32_t b = 0xFFFFFFFFu, w = 0, bit = 0;
+        if (live) {
+          const uint64_t n = bloom_mod(multihash_i(h0, kseed, i), bf);
+          w = uint32_t(n >> 5); bit = uint32_t(n & 31); b = w >> bk.block_shift;
+        }
+        const uint32_t peers = __match_any_sync(0xffffffffu, b);
+        const int leader = __ffs(peers) - 1;
+        uint32_t first = 0;
+        if (live && lane == leader) { first = s_cnt[warp][b]; s_cnt[warp][b] = first + __popc(peers); }
+        first = __shfl_sync(0xffffffffu, first, leader);
+        if (live) {
+          const unsigned long long at = s_base[b] + first + __popc(peers & lt);
+          if (at < bk.cap) bk.entries[uint64_t(b) * bk.cap + at] = ((w & block_mask) << 5) | bit;
+          else *bk.overflow = 1u;
+        }
+        __syncwarp();
+      }
+      __syncthreads();
+      for (uint32_t i = threadIdx.x; i < uint32_t(kWarps) * bk.n_buckets; i += blockDim.x) s_cnt[i / bk.n_buckets][i % bk.n_buckets] = 0;
+      __syncthreads();
+    }
+  }
+}
+
+// replay: bucket after bucket, all CTAs on the same bucket, so that the atomics of a bucket stay in one L2-sized block
+__global__ void __launch_bounds__(kCtaThreads) bloom_apply_kernel(BloomView bf, BloomBuckets bk)
+{
+  const uint64_t stride = uint64_t(gridDim.x) * blockDim.x;
+  for (uint32_t b = 0; b < bk.n_buckets; ++b) {
+    const unsigned long long have = bk.cursor[b];
+    const uint64_t n = have < bk.cap ? have : bk.cap;
+    const uint32_t* e = bk.entries + uint64_t(b) * bk.cap;
+    uint32_t* words = bf.words + (uint64_t(b) << bk.block_shift);
+    for (uint64_t i = uint64_t(blockIdx.x) * blockDim.x + threadIdx.x; i < n; i += stride) {
+      const uint32_t v = __ldcs(e + i);  // streamed once
+      atomicOr(words + (v >> 5), 1u << (v & 31));
+    }
+  }
+}
+
 // ------------------------------------------------------------------ reads: extract + probe + pair-set insert
 
 __device__ __forceinline__ ulonglong2 cas128(PairSlot* slot, ulonglong2 cmp, ulonglong2 val)

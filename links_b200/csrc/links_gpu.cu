@@ -141,6 +141,7 @@ struct links_ctx {
   DevBuf d_ctr;
 
   // contig table (built on s_aux while the reads stream in; finalize waits on ev_table)
+  DevBuf d_bf_stage, d_bf_cursor;  // Bloom build by partition + apply (kernels.cuh BloomBuckets): update entries, cursors + overflow flag
   DevBuf d_table, d_table_occ;  // occ: the MATES build's sector-occupancy bitmap (kernels.cuh TableView::occ)
   bool table_has_occ = false;
   uint64_t table_cap = 0;
@@ -1149,7 +1150,7 @@ int links_create(links_ctx** out, const links_params* p)
       cudaFuncAttributes fa;
       const void* fns[] = {(const void*)pack_kernel, (const void*)rank_build_kernel, (const void*)table_init_kernel,
                            (const void*)contig_kernel<0>, (const void*)contig_kernel<1>, (const void*)contig_kernel<2>,
-                           (const void*)contig_kernel<3>, (const void*)table_seed_kernel, (const void*)bloom_or_reduce_kernel,
+                           (const void*)contig_kernel<3>, (const void*)table_seed_kernel, (const void*)bloom_or_reduce_kernel, (const void*)bloom_partition_kernel<true>, (const void*)bloom_partition_kernel<false>, (const void*)bloom_apply_kernel,
                            (const void*)pair_rehash_kernel, (const void*)classify_kernel, (const void*)mirror_expand_kernel,
                            (const void*)gather_rows_kernel, (const void*)pair_bucket_count_kernel, (const void*)pair_bucket_scatter_kernel,
                            (const void*)pair_import_kernel, (const void*)pair_export_kernel, (const void*)route_kernel,
@@ -1196,7 +1197,7 @@ void links_destroy(links_ctx* c)
   for (DevBuf* b : {&c->f_keys[0], &c->f_keys[1], &c->f_vals[0], &c->f_vals[1], &c->f_issues, &c->f_tiglen, &c->f_hist,
                     &c->f_scan_tmp, &c->f_flags, &c->f_total, &c->f_okeys, &c->f_olinks, &c->f_ogaps, &c->f_final, &c->f_exch, &c->f_il, &c->f_ig}) b->release();
   c->d_tab.release(); c->d_tab2.release(); c->d_cursor.release(); c->d_dist.release(); c->d_step.release(); c->d_minallowed.release();
-  c->d_table_occ.release(); c->d_bloom.release(); c->d_pairs.release(); c->d_pair_list.release(); c->d_ctr.release(); c->d_table.release();
+  c->d_table_occ.release(); c->d_bf_stage.release(); c->d_bf_cursor.release(); c->d_bloom.release(); c->d_pairs.release(); c->d_pair_list.release(); c->d_ctr.release(); c->d_table.release();
   if (c->s_compute && c->own_compute_stream) cudaStreamDestroy(c->s_compute);
   if (c->s_copy) cudaStreamDestroy(c->s_copy);
   if (c->s_aux) cudaStreamDestroy(c->s_aux);
@@ -1377,12 +1378,64 @@ static int contigs_push_impl(links_ctx* c, const char* seq, const uint8_t* dev_s
         return uint64_t((e ? strtod(e, nullptr) : 64.0) * double(1 << 20));  // fractions allowed (tests: 0.25)
       }();
       const uint64_t n_words = (c->bf_bytes + 3) / 4;
+      // LINKS_BF_PARTITION=0 keeps the older block passes / single DRAM pass below; default: filters beyond L2 are built by
+      // partition + apply (every k-mer hashed once, its updates streamed into one bucket per L2-sized block, then replayed)
+      static const int part_env = []() { const char* e = getenv("LINKS_BF_PARTITION"); return !e ? -1 : e[0] == '0' ? 0 : 1; }();
+      static const uint64_t stage_bytes = []() { const char* e = getenv("LINKS_BF_STAGE_MB"); return uint64_t(e ? strtod(e, nullptr) : 4096.0) << 20; }();
+      bool partitioned = false;
+      // (up to four blocks the block passes are as fast or faster: C3 / C5, 177 MB, 14.9 ms in three passes against 16.5 ms;
+      //  beyond, every further block is another full hashing pass: C4 at a tenth, 560 MB, 136 ms in one DRAM pass against 75 ms)
+      if (block_bytes && (part_env == 1 || (part_env < 0 && c->bf_bytes > 4 * block_bytes + block_bytes / 2))) {
+        uint32_t block_shift = uint32_t(log2_ceil(std::max<uint64_t>(block_bytes / 4, 64)));
+        while (((n_words >> block_shift) + 1 > uint64_t(kMaxBloomBuckets)) && block_shift < 27) ++block_shift;
+        const uint32_t n_buckets = uint32_t((n_words + (1ull << block_shift) - 1) >> block_shift);
+        if (n_buckets <= uint32_t(kMaxBloomBuckets)) {
+          partitioned = true;
+          const uint32_t share_n = c->bf_share_n;
+          // tiles per batch so that the entries of one batch fit the staging budget
+          const uint64_t budget_entries = std::max<uint64_t>(stage_bytes / 4, 1ull << 20);
+          uint64_t tiles_per_batch = std::max<uint64_t>(budget_entries * 10 / 11 / (uint64_t(kTile) * c->hash_num), 1) * share_n;
+          tiles_per_batch = std::min<uint64_t>(tiles_per_batch, b->n_tiles);
+          const double own_positions = double(tiles_per_batch) * kTile / share_n;
+          const double per_bucket = own_positions * c->hash_num / (double(n_words) / double(1ull << block_shift));
+          const uint64_t cap = uint64_t(per_bucket * 1.1) + (1ull << 16);
+          CU(c, c->d_bf_stage.ensure(uint64_t(n_buckets) * cap * 4));
+          CU(c, c->d_bf_cursor.ensure(size_t(kMaxBloomBuckets) * 8 + 64));
+          unsigned int* d_over = reinterpret_cast<unsigned int*>(c->d_bf_cursor.as<unsigned long long>() + kMaxBloomBuckets);
+          CU(c, cudaMemsetAsync(d_over, 0, 4, c->s_compute));
+          BloomBuckets bk{c->d_bf_stage.as<uint32_t>(), c->d_bf_cursor.as<unsigned long long>(), cap, n_buckets, block_shift, d_over};
+          const bool with_set = c->member_buckets != 0;
+          for (uint64_t t0 = 0; t0 < b->n_tiles; t0 += tiles_per_batch) {
+            const uint32_t t1 = uint32_t(std::min<uint64_t>(t0 + tiles_per_batch, b->n_tiles));
+            CU(c, cudaMemsetAsync(c->d_bf_cursor.p, 0, size_t(kMaxBloomBuckets) * 8, c->s_compute));
+            const int grid = grid_for(c, (t1 - t0 + share_n - 1) / share_n, 1, 8);
+            if (with_set)
+              bloom_partition_kernel<true><<<grid, kCtaThreads, k * 4 * sizeof(ulonglong2), c->s_compute>>>(
+                cb, uint32_t(t0), t1, int(k), c->kseed, c->d_tab.as<ulonglong2>(), bloom_view(c), member_view(c), bk, c->bf_share_rank, share_n);
+            else
+              bloom_partition_kernel<false><<<grid, kCtaThreads, k * 4 * sizeof(ulonglong2), c->s_compute>>>(
+                cb, uint32_t(t0), t1, int(k), c->kseed, c->d_tab.as<ulonglong2>(), bloom_view(c), member_view(c), bk, c->bf_share_rank, share_n);
+            bloom_apply_kernel<<<c->sm_count * 8, kCtaThreads, 0, c->s_compute>>>(bloom_view(c), bk);
+            c->launches += 2;
+          }
+          CU(c, cudaGetLastError());
+          unsigned int h_over = 0;  // a bucket that overflowed dropped updates: redo the batch with direct atomics (idempotent)
+          CU(c, cudaMemcpyAsync(&h_over, d_over, 4, cudaMemcpyDeviceToHost, c->s_compute));
+          CU(c, cudaStreamSynchronize(c->s_compute));
+          if (h_over) {
+            contig_kernel<0><<<grid_for(c, b->n_tiles, 1, 8), kCtaThreads, k * 4 * sizeof(ulonglong2), c->s_compute>>>(
+              cb, int(k), c->kseed, c->d_tab.as<ulonglong2>(), bloom_view(c), TableView{nullptr, 0, 0}, member_view(c), c->d_ctr.as<Counters>(),
+              BloomPass{0, ~0ull, 0, c->bf_share_rank, c->bf_share_n});
+            c->launches++;
+          }
+        }
+      }
       uint64_t passes = block_bytes && c->bf_bytes > block_bytes + block_bytes / 2 ? (c->bf_bytes + block_bytes - 1) / block_bytes : 1;
       // every pass hashes all k-mers again (~20 G positions/s with the atomics in L2) against ~3.2 G positions/s for one
       // pass with DRAM-resident atomics: beyond six blocks the single pass is the cheaper one
-      static const uint64_t max_passes = []() { const char* e = getenv("LINKS_BF_MAX_PASSES"); return e ? strtoull(e, nullptr, 10) : 6ull; }();
+      static const uint64_t max_passes = []() { const char* e = getenv("LINKS_BF_MAX_PASSES"); return e ? strtoull(e, nullptr, 10) : 6ull; }();  // (only reached with LINKS_BF_PARTITION=0 beyond four blocks)
       if (passes > max_passes) passes = 1;
-      for (uint64_t ps = 0; ps < passes; ++ps) {
+      for (uint64_t ps = 0; ps < passes && !partitioned; ++ps) {
         const BloomPass bp{n_words * ps / passes, ps + 1 == passes ? ~0ull : n_words * (ps + 1) / passes, ps == 0, c->bf_share_rank, c->bf_share_n};
         contig_kernel<0><<<grid_for(c, b->n_tiles, 1, 8), kCtaThreads, k * 4 * sizeof(ulonglong2), c->s_compute>>>(
           cb, int(k), c->kseed, c->d_tab.as<ulonglong2>(), bloom_view(c), TableView{nullptr, 0, 0}, member_view(c), c->d_ctr.as<Counters>(), bp);

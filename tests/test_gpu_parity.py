@@ -465,7 +465,8 @@ def test_peer_memory_exchange_equals_single_context(gpu_lib, name, n_ranks, inbo
 
 
 @pytest.mark.parametrize("name,host_threads", [("c1", None), ("adv_offset_k20", None), ("adv_ns_lower", None), ("adv_ns_lower", "1"),
-                                               ("adv_tandem", "5"), ("c1", "bf-blocks"), ("adv_k40", "layout-in-process"), ("c1", "stage-grows"), ("c1", "stage-grows-serial")])
+                                               ("adv_tandem", "5"), ("c1", "bf-blocks"), ("c1", "bf-blocks-batches"), ("c1", "bf-passes"), ("adv_k40", "layout-in-process"),
+                                               ("c1", "stage-grows"), ("c1", "stage-grows-serial")])
 def test_links_cpp_binary_writes_reference_files(gpu_lib, tmp_path, name, host_threads):
     """The C++ host LINKS_CPP, run as the reference binary is run (bin/LINKS-make:121-122): same
     options in, byte-identical .bloom, and .tigpair_checkpoint.tsv / .pairing_issues equal to the
@@ -490,8 +491,13 @@ def test_links_cpp_binary_writes_reference_files(gpu_lib, tmp_path, name, host_t
         env["LINKS_CPP_LAYOUT"] = "1"
         cmd += ["-l", str(lay_meta["opts"]["l"]), "-a", str(lay_meta["opts"]["a"]), "-z", str(lay_meta["opts"]["z"])]
         host_threads = None
-    if host_threads == "bf-blocks":  # the Bloom filter built in 6 passes of 0.25 MB blocks (contig_kernel's BloomPass), as for filters beyond L2
+    if host_threads in ("bf-blocks", "bf-blocks-batches", "bf-passes"):  # the Bloom filter built as for filters beyond L2, with 0.25 MB "L2-sized" blocks:
         env["LINKS_BF_BLOCK_MB"] = "0.25"
+        if host_threads == "bf-blocks-batches":  # ... partition + apply (bloom_partition_kernel), the updates staged in many small batches
+            env["LINKS_BF_STAGE_MB"] = "0.5"
+        if host_threads == "bf-passes":          # ... the older way, one pass over the contigs per block (contig_kernel's BloomPass)
+            env["LINKS_BF_PARTITION"] = "0"
+            env["LINKS_BF_MAX_PASSES"] = "64"
         host_threads = None
     if host_threads:  # "1": the serial reader (seq_stream.hpp); default: the multi-threaded FASTA ingest (fasta_ingest.hpp)
         env["LINKS_HOST_THREADS"] = host_threads
