@@ -467,8 +467,13 @@ __global__ void __launch_bounds__(kCtaThreads) contig_kernel(ContigBatch cb, int
   __shared__ uint32_t s_seg;
   __syncthreads();
   unsigned long long n_kmers = 0;
-  for (uint32_t tile = blockIdx.x; tile < cb.n_tiles; tile += gridDim.x) {
-    if (MODE == 0 && bp.share_n > 1 && tile % bp.share_n != bp.share_rank) continue;  // another rank's share (block-uniform)
+  // MODE 0 with shares: this rank's tiles are share_rank, share_rank + share_n, ...; they are enumerated directly (striding
+  // by the grid and skipping foreign tiles would leave only the CTAs with blockIdx % share_n == share_rank any work whenever
+  // the grid size is a multiple of share_n -- and 148 x 8 is)
+  const uint32_t t_step = MODE == 0 && bp.share_n > 1 ? bp.share_n : 1u;
+  const uint32_t t_first = MODE == 0 && bp.share_n > 1 ? bp.share_rank : 0u;
+  for (uint64_t tile64 = t_first + uint64_t(blockIdx.x) * t_step; tile64 < cb.n_tiles; tile64 += uint64_t(gridDim.x) * t_step) {
+    const uint32_t tile = uint32_t(tile64);
     if (threadIdx.x == 0) s_seg = find_segment(cb.seg_tile_start, cb.n_seq, tile);
     __syncthreads();
     const uint32_t c = s_seg;
@@ -542,8 +547,11 @@ __global__ void __launch_bounds__(kCtaThreads) bloom_partition_kernel(ContigBatc
   for (uint32_t i = threadIdx.x; i < uint32_t(kWarps) * kMaxBloomBuckets; i += blockDim.x) (&s_cnt[0][0])[i] = 0;
   __syncthreads();
   const uint32_t block_mask = (1u << bk.block_shift) - 1u;
-  for (uint32_t tile = tile_lo + blockIdx.x; tile < tile_hi; tile += gridDim.x) {
-    if (share_n > 1 && tile % share_n != share_rank) continue;  // another rank's share (block-uniform)
+  // this rank's tiles of [tile_lo, tile_hi): the first one congruent to share_rank, then every share_n-th (enumerated
+  // directly: a grid-stride walk that skips foreign tiles idles all CTAs but every share_n-th when share_n divides the grid)
+  const uint32_t t_first = tile_lo + (share_rank + share_n - tile_lo % share_n) % share_n;
+  for (uint64_t tile64 = t_first + uint64_t(blockIdx.x) * share_n; tile64 < tile_hi; tile64 += uint64_t(gridDim.x) * share_n) {
+    const uint32_t tile = uint32_t(tile64);
     if (threadIdx.x == 0) s_seg = find_segment(cb.seg_tile_start, cb.n_seq, tile);
     __syncthreads();
     const uint32_t c = s_seg;
