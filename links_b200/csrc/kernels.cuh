@@ -480,12 +480,16 @@ __global__ void __launch_bounds__(kCtaThreads) contig_kernel(ContigBatch cb, int
     const uint64_t g0 = cb.off[c] - cb.base0, len = cb.off[c + 1] - cb.off[c];
     const uint64_t npos = len - k + 1; // segments with len < k own zero tiles
     const uint64_t p_begin = uint64_t(tile - cb.seg_tile_start[c]) * kTile;
-    for (int q = threadIdx.x; q < kTile; q += kCtaThreads) {
-      const uint64_t p = p_begin + q;
+    // a thread walks kTile / kCtaThreads consecutive positions: the first k-mer is hashed from scratch (k lookups), the
+    // others rolled from it (2 lookups each)
+    constexpr int kRun = kTile / kCtaThreads;
+    uint64_t f = 0, r = 0;
+    for (int j = 0; j < kRun; ++j) {
+      const uint64_t p = p_begin + uint64_t(threadIdx.x) * kRun + j;
       if (p >= npos) break;
+      if (j == 0) hash_kmer(cb.packed, g0 + p, k, s_tab, f, r);
+      else roll_kmer(cb.packed, g0 + p - 1, k, s_tab, f, r);
       if (!window_valid(cb.inv, g0 + p, k)) continue;
-      uint64_t f, r;
-      hash_kmer(cb.packed, g0 + p, k, s_tab, f, r);
       if (MODE == 0) {
         bloom_insert_range(bf, f, r, kseed, bp.w_lo, bp.w_hi);
         if (bp.with_set && mv.buckets) member_insert(mv, r < f ? r : f);
@@ -558,13 +562,17 @@ __global__ void __launch_bounds__(kCtaThreads) bloom_partition_kernel(ContigBatc
     const uint64_t g0 = cb.off[c] - cb.base0, len = cb.off[c + 1] - cb.off[c];
     const uint64_t npos = len - k + 1;
     const uint64_t p_begin = uint64_t(tile - cb.seg_tile_start[c]) * kTile;
-    for (int q0 = 0; q0 < kTile; q0 += kCtaThreads) {  // one round: every thread one position, hash_num entries
-      const uint64_t p = p_begin + q0 + threadIdx.x;
+    constexpr int kRun = kTile / kCtaThreads;  // a thread walks kRun consecutive positions, one per round: hashed once, then rolled
+    uint64_t f = 0, r = 0;
+    for (int j = 0; j < kRun; ++j) {  // one round: every thread one position, hash_num entries
+      const uint64_t p = p_begin + uint64_t(threadIdx.x) * kRun + j;
+      if (p < npos) {
+        if (j == 0) hash_kmer(cb.packed, g0 + p, k, s_tab, f, r);
+        else roll_kmer(cb.packed, g0 + p - 1, k, s_tab, f, r);
+      }
       const bool live = p < npos && window_valid(cb.inv, g0 + p, k);
       uint64_t h0 = 0;
       if (live) {
-        uint64_t f, r;
-        hash_kmer(cb.packed, g0 + p, k, s_tab, f, r);
         h0 = r < f ? r : f;
         if (WITH_SET && mv.buckets) member_insert(mv, h0);
       }

@@ -78,6 +78,35 @@ __device__ __forceinline__ void hash_kmer(const uint32_t* __restrict__ packed, u
   rev = r;
 }
 
+// ---- rolling by one base (contig-side kernels: a thread walks a few consecutive positions).  The hash is XOR-linear in
+// per-position contributions, so  fwd' = srol(fwd ^ c_out(0)) ^ c_in(k-1)  and  rev' = sror(rev ^ c_out(0)) ^ c_in(k-1)
+// with c(i) the table entries of build_nthash_table (btllib rolls the same way, nthash.hpp:576-603).  A base that is not
+// ACGT enters and leaves with the same (arbitrary) 2-bit code, so a window that has moved past it hashes exactly as from
+// scratch; windows that still hold it are skipped by the caller (window_valid).
+__host__ __device__ __forceinline__ uint64_t srol1(uint64_t v)
+{
+  const uint64_t hi = v >> 33, lo = v & 0x1FFFFFFFFULL;
+  return ((((hi << 1) | (hi >> 30)) & 0x7FFFFFFFULL) << 33) | (((lo << 1) | (lo >> 32)) & 0x1FFFFFFFFULL);
+}
+__host__ __device__ __forceinline__ uint64_t sror1(uint64_t v)
+{
+  const uint64_t hi = v >> 33, lo = v & 0x1FFFFFFFFULL;
+  return ((((hi >> 1) | (hi << 30)) & 0x7FFFFFFFULL) << 33) | (((lo >> 1) | (lo << 32)) & 0x1FFFFFFFFULL);
+}
+__device__ __forceinline__ uint32_t packed_code(const uint32_t* __restrict__ packed, uint64_t g)
+{
+  return (__ldg(packed + (g >> 4)) >> (int(g & 15) * 2)) & 3u;
+}
+// (fwd, rev) of the k-mer at g  ->  of the k-mer at g + 1
+__device__ __forceinline__ void roll_kmer(const uint32_t* __restrict__ packed, uint64_t g, int k, const ulonglong2* __restrict__ tab,
+                                          uint64_t& fwd, uint64_t& rev)
+{
+  const ulonglong2 out = tab[packed_code(packed, g)];                        // offset 0 of the old window
+  const ulonglong2 in = tab[(k - 1) * 4 + packed_code(packed, g + k)];       // offset k-1 of the new window
+  fwd = srol1(fwd ^ out.x) ^ in.x;
+  rev = sror1(rev ^ out.y) ^ in.y;
+}
+
 // ---- two bases per lookup.  Because the hash is XOR-linear, the contributions of k-mer offsets
 // 2p and 2p+1 can be pre-XORed: tab2[p*16 + c4] with c4 = code(2p) | code(2p+1)<<2 (the 4 bits
 // the packed stream already holds).  Halves the shared-memory loads and the XORs per k-mer.
