@@ -864,8 +864,6 @@ __global__ void mirror_expand_kernel(const uint64_t* __restrict__ keys, uint32_t
   out_idx[2 * i + 1] = int32_t(i);
 }
 
-__global__ void range_advance_kernel(unsigned long long* range) { range[0] = range[1]; }
-
 // same layout as links_row (include/links_gpu.h): the rows leave the device ready for the caller
 struct FinalRow { int32_t bin; uint32_t tig_a, tig_b; uint8_t rev_a, rev_b, pad_[2]; unsigned long long links; long long gaps; };
 __global__ void gather_rows_kernel(const uint64_t* __restrict__ keys, const int32_t* __restrict__ idx, uint32_t n, int tb,

@@ -273,27 +273,9 @@ __device__ __forceinline__ uint32_t bloom_bit(const BloomView& bf, uint64_t h0, 
   return (__ldg(bf.words + (n >> 5)) >> (n & 31)) & 1u;
 }
 
-// Probes [i0, i1) of one k-mer issued together (independent loads in flight), instead of the
-// reference's one-at-a-time early-exit loop (bloom_filter.hpp:648-659).  Same answer; `probes`
+// N probes starting at i0, N known at compile time, issued together (independent loads in flight, no predicated-off
+// bodies) instead of the reference's one-at-a-time early-exit loop (bloom_filter.hpp:648-659).  Same answer; `probes`
 // is advanced by the number of probes the sequential loop would have made (roofline accounting).
-__device__ __forceinline__ bool bloom_probe_range(const BloomView& bf, uint64_t h0, uint64_t kseed, uint32_t i0, uint32_t i1,
-                                                  uint32_t& probes)
-{
-  while (i0 < i1) {
-    const uint32_t n = min(i1 - i0, 8u);
-    uint32_t miss = 0;
-#pragma unroll
-    for (uint32_t j = 0; j < 8; ++j)
-      if (j < n) miss |= (bloom_bit(bf, h0, kseed, i0 + j) ^ 1u) << j;
-    if (miss) { probes += __ffs(miss); return false; }
-    probes += n;
-    i0 += n;
-  }
-  return true;
-}
-
-// N probes starting at i0, N known at compile time: all loads in flight together, no predicated-off
-// bodies.  Accounting as in bloom_probe_range.
 template <int N, bool SMALL = false>
 __device__ __forceinline__ bool bloom_probe_fixed(const BloomView& bf, uint64_t h0, uint64_t kseed, uint32_t i0, uint32_t& probes)
 {
