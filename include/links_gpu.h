@@ -229,6 +229,15 @@ int links_exchange_finish(links_ctx* ctx);
 /* fwd/rev ntHash2 of every k-mer start of one sequence (btllib NtHash, nthash.hpp:1265-1338);
  * valid[i] = 1 iff the k-mer at i has only ACGTU/acgtu.  Arrays hold max(len-k+1,0) entries. */
 int links_kmer_hashes(links_ctx* ctx, const char* seq, uint64_t len, uint64_t* fwd, uint64_t* rev, uint8_t* valid);
+/* links_kmer_hashes for callers that may not allocate device memory (CUDA graph capture, tight serving loops,
+ * harnesses that forbid cudaMalloc).  NO COUNTERPART IN THE REFERENCE.
+ * Same arguments, same results, same kernels; every intermediate (staged sequence, 2-bit packing, invalid-base mask,
+ * result staging) lives in one static __device__ array of ~2.4 MB that each GPU loading the library holds until the
+ * process exits, so the call makes no cudaMalloc / cudaFree.  len > LINKS_STATIC_MAX_BASES fails with LINKS_E_LIMIT.
+ * All calls share that array: calls in one process are serialised by the library, but calls from different PROCESSES
+ * on one GPU have their own copy each, and nothing else may be assumed about its contents between calls. */
+#define LINKS_STATIC_MAX_BASES (1u << 17)
+int links_kmer_hashes_static(links_ctx* ctx, const char* seq, uint64_t len, uint64_t* fwd, uint64_t* rev, uint8_t* valid);
 /* KmerBloomFilter membership of given (fwd,rev) hash pairs against the context's filter. */
 int links_bf_contains(links_ctx* ctx, const uint64_t* fwd, const uint64_t* rev, uint64_t n, uint8_t* out);
 /* Distinct pairs currently held: h_a[i], h_b[i], d_idx[i]; call with NULL arrays to get the count. */

@@ -103,6 +103,7 @@ SIGNATURES = {
     "links_bf_alloc_shared": (C.c_int, [C.c_void_p, C.c_uint64, C.c_uint32, C.c_uint32, C.c_uint32, C.POINTER(C.c_void_p)]),
     "links_bf_allreduce": (C.c_int, [C.c_void_p]),
     "links_kmer_hashes": (C.c_int, [C.c_void_p, C.c_void_p, C.c_uint64, C.c_void_p, C.c_void_p, C.c_void_p]),
+    "links_kmer_hashes_static": (C.c_int, [C.c_void_p, C.c_void_p, C.c_uint64, C.c_void_p, C.c_void_p, C.c_void_p]),
     "links_bf_contains": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint64, C.c_void_p]),
     "links_pairs_download": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint64, C.POINTER(C.c_uint64)]),
     "links_get_timing": (C.c_int, [C.c_void_p, C.POINTER(LinksTiming), C.c_int]),

@@ -702,7 +702,6 @@ int ensure_owned(links_ctx* c, uint64_t min_cap)
   c->x_job_started = true;
   if (c->owned_cap >= want || (c->owned_cap && !may_replace)) return LINKS_OK;
   const uint64_t cap = 1ull << log2_ceil(want);
-  const bool multi_d = c->prm.n_dist > 1;
   CU(c, cudaStreamSynchronize(c->s_route));
   CU(c, cudaStreamSynchronize(c->s_cls));
   CU(c, cudaStreamSynchronize(c->s_import));
@@ -969,6 +968,52 @@ int classify_increment_owned(links_ctx* c)
   }
   CU(c, cudaGetLastError());
   CU(c, cudaEventRecord(c->ev_cls_done, c->s_cls));
+  return LINKS_OK;
+}
+
+} // namespace
+
+// ====================================================================== fixed scratch for links_kmer_hashes_static
+//
+// No counterpart in the reference: added for callers that may not allocate device
+// memory (code under CUDA graph capture, tight serving loops, harnesses that forbid cudaMalloc).  links_kmer_hashes
+// stages the sequence, its 2-bit packing, the invalid-base mask, the record offsets / flags pack_kernel wants and the
+// three result arrays in device buffers it allocates and frees on every call; the variant below runs the same two
+// kernels over ONE array in the module's data segment.  Every GPU that loads liblinks_gpu.so holds these
+// kStaticScratchBytes (~2.4 MB) until the process exits.  In host code `g_static_scratch` is only the symbol's host-side
+// stand-in: the device address comes from cudaGetSymbolAddress, asked once per device with that device current.
+constexpr uint64_t kStaticMaxBases = LINKS_STATIC_MAX_BASES;
+constexpr size_t static_al(size_t x) { return (x + 255) & ~size_t(255); }
+constexpr size_t kSsAscii = 0;                                                          // len bytes (+ slack for pack_kernel's 16-byte loads)
+constexpr size_t kSsPacked = kSsAscii + static_al(kStaticMaxBases + 128);               // 2 bits per base + 8 padding words
+constexpr size_t kSsInv = kSsPacked + static_al((kStaticMaxBases / 16 + 8) * 4);        // 1 bit per base + 8 padding words
+constexpr size_t kSsOff = kSsInv + static_al((kStaticMaxBases / 32 + 8) * 4);           // record offsets {0, len}
+constexpr size_t kSsFlags = kSsOff + 256;                                               // per-record "has an invalid base" (must start at zero)
+constexpr size_t kSsFwd = kSsFlags + 256;
+constexpr size_t kSsRev = kSsFwd + static_al(kStaticMaxBases * 8);
+constexpr size_t kSsValid = kSsRev + static_al(kStaticMaxBases * 8);
+constexpr size_t kStaticScratchBytes = kSsValid + static_al(kStaticMaxBases);
+static_assert(kStaticScratchBytes <= (4u << 20), "the static scratch is meant to stay small: every GPU holds it until exit");
+
+static __device__ __align__(256) unsigned char g_static_scratch[kStaticScratchBytes];
+
+namespace {
+
+constexpr int kStaticMaxDevices = 64;
+std::mutex g_static_mu;                              // one call at a time in this process: every call shares the array
+unsigned char* g_static_ptr[kStaticMaxDevices] = {};  // device address of g_static_scratch on device i (null: not asked yet)
+
+// caller holds g_static_mu and has made c->device current
+int static_scratch_base(links_ctx* c, unsigned char** out)
+{
+  if (c->device < 0 || c->device >= kStaticMaxDevices) return fail(c, LINKS_E_LIMIT, "static scratch: device ordinal %d >= %d", c->device, kStaticMaxDevices);
+  if (!g_static_ptr[c->device]) {
+    void* p = nullptr;
+    CU(c, cudaGetSymbolAddress(&p, g_static_scratch));
+    if (!p) return fail(c, LINKS_E_CUDA, "static scratch: cudaGetSymbolAddress returned a null address");
+    g_static_ptr[c->device] = static_cast<unsigned char*>(p);
+  }
+  *out = g_static_ptr[c->device];
   return LINKS_OK;
 }
 
@@ -2118,6 +2163,55 @@ int links_kmer_hashes(links_ctx* c, const char* seq, uint64_t len, uint64_t* fwd
   CU(c, cudaMemcpyAsync(rev, d_r.p, npos * 8, cudaMemcpyDeviceToHost, c->s_compute));
   CU(c, cudaMemcpyAsync(valid, d_v.p, npos, cudaMemcpyDeviceToHost, c->s_compute));
   CU(c, cudaStreamSynchronize(c->s_compute));
+  return LINKS_OK;
+}
+
+// links_kmer_hashes without a single device allocation (see g_static_scratch above): same pack_kernel + kmer_hashes_kernel,
+// same launch shapes, on the fixed array.  The array keeps the previous call's contents, so what the kernels expect to find
+// zeroed / preset is set here on every call (the record flags pack_kernel ORs into, the padding words behind the packed
+// bases and behind the mask).  Calls through this entry point are serialised per process; work that another process or
+// another entry point queues on the same GPU does not touch the array.
+int links_kmer_hashes_static(links_ctx* c, const char* seq, uint64_t len, uint64_t* fwd, uint64_t* rev, uint8_t* valid)
+{
+  if (!c || !seq || !fwd || !rev || !valid) return LINKS_E_INVAL;
+  if (len > kStaticMaxBases)
+    return fail(c, LINKS_E_LIMIT, "links_kmer_hashes_static: %llu bases, the static scratch holds at most %llu (LINKS_STATIC_MAX_BASES); use links_kmer_hashes",
+                (unsigned long long)len, (unsigned long long)kStaticMaxBases);
+  const uint32_t k = c->prm.k;
+  if (len < k) return LINKS_OK;
+  CU(c, cudaSetDevice(c->device));
+  std::lock_guard<std::mutex> lk(g_static_mu);
+  unsigned char* base = nullptr;
+  int rc = static_scratch_base(c, &base);
+  if (rc) return rc;
+  uint8_t* d_ascii = base + kSsAscii;
+  uint32_t* d_packed = reinterpret_cast<uint32_t*>(base + kSsPacked);
+  uint32_t* d_inv = reinterpret_cast<uint32_t*>(base + kSsInv);
+  uint64_t* d_off = reinterpret_cast<uint64_t*>(base + kSsOff);
+  uint32_t* d_flags = reinterpret_cast<uint32_t*>(base + kSsFlags);
+  uint64_t* d_f = reinterpret_cast<uint64_t*>(base + kSsFwd);
+  uint64_t* d_r = reinterpret_cast<uint64_t*>(base + kSsRev);
+  uint8_t* d_v = base + kSsValid;
+  const uint64_t npos = len - k + 1;
+  const uint64_t off[2] = {0, len};
+  cudaStream_t s = c->s_compute;
+  CU(c, cudaStreamSynchronize(s));
+  CU(c, cudaMemcpyAsync(d_ascii, seq, len, cudaMemcpyHostToDevice, s));
+  CU(c, cudaMemcpyAsync(d_off, off, sizeof off, cudaMemcpyHostToDevice, s));
+  CU(c, cudaMemsetAsync(d_flags, 0, 2 * 4, s));
+  CU(c, cudaMemsetAsync(d_packed + (len + 15) / 16, 0, 8 * 4, s));
+  CU(c, cudaMemsetAsync(d_inv + (len + 31) / 32, 0xFF, 8 * 4, s));
+  const uint64_t threads = (len + 31) / 32;
+  pack_kernel<<<unsigned((threads + kCtaThreads - 1) / kCtaThreads), kCtaThreads, 0, s>>>(d_ascii, len, d_packed, d_inv, d_off, 1, 0, d_flags);
+  c->launches++;
+  kmer_hashes_kernel<<<grid_for(c, npos, 256, 16), 256, k * 4 * sizeof(ulonglong2), s>>>(d_packed, d_inv, npos, int(k), c->d_tab.as<ulonglong2>(),
+                                                                                        d_f, d_r, d_v);
+  c->launches++;
+  CU(c, cudaGetLastError());
+  CU(c, cudaMemcpyAsync(fwd, d_f, npos * 8, cudaMemcpyDeviceToHost, s));
+  CU(c, cudaMemcpyAsync(rev, d_r, npos * 8, cudaMemcpyDeviceToHost, s));
+  CU(c, cudaMemcpyAsync(valid, d_v, npos, cudaMemcpyDeviceToHost, s));
+  CU(c, cudaStreamSynchronize(s));
   return LINKS_OK;
 }
 

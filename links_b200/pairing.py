@@ -311,6 +311,17 @@ class Links:
                                                     valid.ctypes.data))
         return fwd, rev, valid
 
+    def kmer_hashes_static(self, seq: bytes) -> tuple[np.ndarray, np.ndarray, np.ndarray]:
+        """kmer_hashes through links_kmer_hashes_static: no device allocation, at most LINKS_STATIC_MAX_BASES (2^17) bases."""
+        n = max(len(seq) - self.opts.k + 1, 0)
+        fwd = np.zeros(n, np.uint64)
+        rev = np.zeros(n, np.uint64)
+        valid = np.zeros(n, np.uint8)
+        buf = np.frombuffer(seq, dtype=np.uint8)
+        self._check(self._lib.links_kmer_hashes_static(self._h, buf.ctypes.data, len(seq), fwd.ctypes.data, rev.ctypes.data,
+                                                       valid.ctypes.data))
+        return fwd, rev, valid
+
     def bf_contains(self, fwd: np.ndarray, rev: np.ndarray) -> np.ndarray:
         fwd = np.ascontiguousarray(fwd, np.uint64)
         rev = np.ascontiguousarray(rev, np.uint64)
