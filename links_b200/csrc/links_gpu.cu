@@ -68,8 +68,6 @@ struct links_ctx {
   int device = 0;
   int sm_count = 148;
   size_t dev_total_mem = 0;
-  size_t l2_persist_max = 0, l2_window_max = 0;  // cudaDeviceProp::persistingL2CacheMaxSize / accessPolicyMaxWindowSize
-  bool l2_pinned = false;                        // persisting lines to hand back once the mates scan has drained
   links_params prm{};
   std::vector<uint32_t> dist;
   std::vector<uint32_t> step;
@@ -1109,8 +1107,6 @@ int links_create(links_ctx** out, const links_params* p)
   CUC(cudaGetDeviceProperties(&prop, c->device));
   c->sm_count = prop.multiProcessorCount;
   c->dev_total_mem = prop.totalGlobalMem;
-  c->l2_persist_max = size_t(std::max(prop.persistingL2CacheMaxSize, 0));
-  c->l2_window_max = size_t(std::max(prop.accessPolicyMaxWindowSize, 0));
   CUC(cudaStreamCreateWithFlags(&c->s_compute, cudaStreamNonBlocking));
   CUC(cudaStreamCreateWithFlags(&c->s_copy, cudaStreamNonBlocking));
   CUC(cudaStreamCreateWithFlags(&c->s_aux, cudaStreamNonBlocking));
@@ -1857,24 +1853,8 @@ static int build_table_mates(links_ctx* c, cudaStream_t st, uint64_t n_pairs)
     table_seed_kernel<<<grid_for(c, n_pairs, kCtaThreads, 8), kCtaThreads, 0, st>>>(c->d_pair_list.as<ulonglong2>(), n_pairs, table_view(c));
     c->launches++;
   }
-  // The scan below asks the occupancy bitmap about every contig k-mer (two random sectors per position) while it streams
-  // the packed contigs through the same L2.  LINKS_TABLE_L2_PERSIST=1 pins the bitmap's lines for the duration of the scan
-  // (an access-policy window on this stream: hits persist, everything else streams); off unless asked for.
-  static const bool want_persist = [] { const char* e = getenv("LINKS_TABLE_L2_PERSIST"); return e && atoi(e) != 0; }();
-  const size_t occ_bytes = size_t(cap / 16 + 64);
-  const bool persist = want_persist && c->l2_persist_max && c->l2_window_max && !c->contig_batches.empty();
-  if (persist) {
-    const size_t carve = std::min(c->l2_persist_max, occ_bytes);
-    CU(c, cudaDeviceSetLimit(cudaLimitPersistingL2CacheSize, carve));
-    cudaStreamAttrValue av;
-    memset(&av, 0, sizeof av);
-    av.accessPolicyWindow.base_ptr = c->d_table_occ.p;
-    av.accessPolicyWindow.num_bytes = std::min(occ_bytes, c->l2_window_max);
-    av.accessPolicyWindow.hitRatio = float(std::min(1.0, double(carve) / double(av.accessPolicyWindow.num_bytes)));
-    av.accessPolicyWindow.hitProp = cudaAccessPropertyPersisting;
-    av.accessPolicyWindow.missProp = cudaAccessPropertyStreaming;
-    CU(c, cudaStreamSetAttribute(st, cudaStreamAttributeAccessPolicyWindow, &av));
-  }
+  // (Pinning the occupancy bitmap in L2 with an access-policy window for the duration of the scan was tried and is slower:
+  // the carve-out is taken from the L2 every other kernel uses, profiles/r02w_table_l2_persist_ab.txt.)
   for (auto* b : c->contig_batches) {
     if (!b->n_tiles) continue;
     ContigBatch cb{b->packed.as<uint32_t>(), b->inv.as<uint32_t>(), b->off.as<uint64_t>(), b->base0,
@@ -1883,13 +1863,6 @@ static int build_table_mates(links_ctx* c, cudaStream_t st, uint64_t n_pairs)
       cb, int(k), c->kseed, c->d_tab.as<ulonglong2>(), bloom_view(c), table_view(c), MemberView{nullptr, 0}, c->d_ctr.as<Counters>(),
       BloomPass{0, ~0ull, 1});
     c->launches++;
-  }
-  if (persist) {  // later launches on this stream go back to the default policy; links_finalize hands the pinned lines
-                  // back after its next synchronisation (a reset now would hit the scan that was just queued)
-    cudaStreamAttrValue av;
-    memset(&av, 0, sizeof av);
-    CU(c, cudaStreamSetAttribute(st, cudaStreamAttributeAccessPolicyWindow, &av));
-    c->l2_pinned = true;
   }
   CU(c, cudaGetLastError());
   return LINKS_OK;
@@ -2001,7 +1974,6 @@ int links_finalize(links_ctx* c, links_row** rows_out, uint64_t* n_rows_out, lin
       CU(c, cudaGetLastError());
     }
     CU(c, cudaStreamSynchronize(s));
-    if (c->l2_pinned) { c->l2_pinned = false; CU(c, cudaCtxResetPersistingL2Cache()); }
     CU(c, cudaMemcpy(&h, c->d_ctr.p, sizeof h, cudaMemcpyDeviceToHost));
     if (h.n_issues <= issue_cap) break;
     issue_cap = h.n_issues; // rerun with an exact-size buffer
