@@ -104,10 +104,11 @@ GATHER_PEAK_BIN = os.path.join(ROOT, "tools", "gather_peak")
 
 
 def build_tools(force: bool = False) -> None:
-    """Measurement probes under tools/ (random-sector gather ceiling)."""
-    src = os.path.join(ROOT, "tools", "gather_peak.cu")
-    if os.path.exists(src) and (force or not _newer(GATHER_PEAK_BIN, [src])):
-        subprocess.run([_nvcc(), *NVCC_FLAGS, "-o", GATHER_PEAK_BIN, src], check=True)
+    """Measurement probes under tools/ (random-sector gather ceiling, random-word atomic ceiling)."""
+    for name in ("gather_peak", "atomic_peak"):
+        src, dst = os.path.join(ROOT, "tools", name + ".cu"), os.path.join(ROOT, "tools", name)
+        if os.path.exists(src) and (force or not _newer(dst, [src])):
+            subprocess.run([_nvcc(), *NVCC_FLAGS, "-o", dst, src], check=True)
 
 
 def build_all(force: bool = False, verbose: bool = False) -> None:

@@ -523,7 +523,7 @@ __global__ void __launch_bounds__(kCtaThreads) contig_kernel(ContigBatch cb, int
 // every k-mer once per block.  Here every k-mer is hashed ONCE: its hash_num updates are appended, as 4-byte entries
 // (word within the block << 5 | bit), to one bucket per L2-sized block of the filter -- sequential streams, which DRAM
 // takes at copy speed: 2 x 4 B x hash_num streamed per k-mer instead of 2 x hash_num random sectors -- and a second
-// kernel replays bucket after bucket with the atomics landing in an L2-resident block.
+// kernel, launched once per bucket, replays it with the atomics landing in an L2-resident block.
 struct BloomBuckets {
   uint32_t* entries;             // bucket b occupies [b * cap, (b + 1) * cap)
   unsigned long long* cursor;    // [n_buckets] entries appended (may exceed cap: the excess is dropped and flagged)
@@ -617,19 +617,21 @@ __global__ void __launch_bounds__(kCtaThreads) bloom_partition_kernel(ContigBatc
   }
 }
 
-// replay: bucket after bucket, all CTAs on the same bucket, so that the atomics of a bucket stay in one L2-sized block
-__global__ void __launch_bounds__(kCtaThreads) bloom_apply_kernel(BloomView bf, BloomBuckets bk)
+// replay of bucket b: its atomics stay in one L2-sized block of the filter.  ONE LAUNCH PER BUCKET: a single kernel that
+// walked bucket after bucket let the CTAs drift apart (nothing holds a fast CTA back: a RED does not wait for its result),
+// so that several blocks were live at once and pushed each other out of L2 -- 47 G updates/s with 64 MB blocks, 83 G/s with
+// 16 MB blocks, against the 181-202 G/s the same access pattern reaches on one block (tools/atomic_peak.cu,
+// profiles/r02z_atomic_peak.jsonl).  The kernel boundary is the grid-wide barrier.
+__global__ void __launch_bounds__(kCtaThreads) bloom_apply_kernel(BloomView bf, BloomBuckets bk, uint32_t b)
 {
   const uint64_t stride = uint64_t(gridDim.x) * blockDim.x;
-  for (uint32_t b = 0; b < bk.n_buckets; ++b) {
-    const unsigned long long have = bk.cursor[b];
-    const uint64_t n = have < bk.cap ? have : bk.cap;
-    const uint32_t* e = bk.entries + uint64_t(b) * bk.cap;
-    uint32_t* words = bf.words + (uint64_t(b) << bk.block_shift);
-    for (uint64_t i = uint64_t(blockIdx.x) * blockDim.x + threadIdx.x; i < n; i += stride) {
-      const uint32_t v = __ldcs(e + i);  // streamed once
-      atomicOr(words + (v >> 5), 1u << (v & 31));
-    }
+  const unsigned long long have = bk.cursor[b];
+  const uint64_t n = have < bk.cap ? have : bk.cap;
+  const uint32_t* e = bk.entries + uint64_t(b) * bk.cap;
+  uint32_t* words = bf.words + (uint64_t(b) << bk.block_shift);
+  for (uint64_t i = uint64_t(blockIdx.x) * blockDim.x + threadIdx.x; i < n; i += stride) {
+    const uint32_t v = __ldcs(e + i);  // streamed once
+    atomicOr(words + (v >> 5), 1u << (v & 31));
   }
 }
 

@@ -1460,8 +1460,8 @@ static int contigs_push_impl(links_ctx* c, const char* seq, const uint8_t* dev_s
             else
               bloom_partition_kernel<false><<<grid, kCtaThreads, k * 4 * sizeof(ulonglong2), c->s_compute>>>(
                 cb, uint32_t(t0), t1, int(k), c->kseed, c->d_tab.as<ulonglong2>(), bloom_view(c), member_view(c), bk, c->bf_share_rank, share_n);
-            bloom_apply_kernel<<<c->sm_count * 8, kCtaThreads, 0, c->s_compute>>>(bloom_view(c), bk);
-            c->launches += 2;
+            for (uint32_t bb = 0; bb < n_buckets; ++bb) bloom_apply_kernel<<<c->sm_count * 8, kCtaThreads, 0, c->s_compute>>>(bloom_view(c), bk, bb);
+            c->launches += 1 + n_buckets;
           }
           CU(c, cudaGetLastError());
           unsigned int h_over = 0;  // a bucket that overflowed dropped updates: redo the batch with direct atomics (idempotent)

@@ -2,7 +2,7 @@
 // random reads of one 32-byte sector each (a Bloom-filter probe reads 4 bytes of a random sector, a member-set or
 // pair-set lookup reads the whole 32-byte bucket).  MEASUREMENT PROBE, not product code.
 //
-//   tools/gather_peak [--mb 64,1024,8192] [--iters 3]
+//   tools/gather_peak [--mb 64,1024,8192] [--iters 3] [--fetch 32|64|128]
 //
 // For every footprint (a table of that many MB of 32-byte sectors), load width (4 or 32 bytes per sector) and number
 // of independent loads in flight per thread (1..16) it prints one JSON line: sectors/s, GB/s counted as 32 bytes per
@@ -76,16 +76,21 @@ int main(int argc, char** argv)
   std::vector<uint64_t> mbs = {64, 1024, 8192};
   int iters = 3;
   double copy_gbs = 0;
+  int fetch = 0;  // cudaLimitMaxL2FetchGranularity to ask for (32 / 64 / 128); 0 = leave the default
   for (int i = 1; i < argc; ++i) {
     if (!strcmp(argv[i], "--mb") && i + 1 < argc) {
       mbs.clear();
       for (char* tok = strtok(argv[++i], ","); tok; tok = strtok(nullptr, ",")) mbs.push_back(strtoull(tok, nullptr, 10));
     } else if (!strcmp(argv[i], "--iters") && i + 1 < argc) iters = atoi(argv[++i]);
     else if (!strcmp(argv[i], "--copy-gbs") && i + 1 < argc) copy_gbs = atof(argv[++i]);
+    else if (!strcmp(argv[i], "--fetch") && i + 1 < argc) fetch = atoi(argv[++i]);
   }
   cudaDeviceProp prop;
   if (cudaGetDeviceProperties(&prop, 0) != cudaSuccess) { fprintf(stderr, "no CUDA device\n"); return 1; }
   const int grid = prop.multiProcessorCount * 8;
+  if (fetch) cudaDeviceSetLimit(cudaLimitMaxL2FetchGranularity, size_t(fetch));
+  size_t fetch_now = 0;
+  cudaDeviceGetLimit(&fetch_now, cudaLimitMaxL2FetchGranularity);
   uint64_t* sink;
   cudaMalloc(&sink, 8);
   for (uint64_t mb : mbs) {
@@ -102,8 +107,8 @@ int main(int argc, char** argv)
     const double sectors = double(threads) * rounds * U;                                                                       \
     const double gbs = sectors * 32.0 / (ms * 1e-3) / 1e9;                                                                     \
     printf("{\"probe\": \"random_sector_gather\", \"gpu\": \"%s\", \"footprint_mb\": %llu, \"load_bytes\": %d, \"in_flight_per_thread\": %d, "   \
-           "\"threads\": %llu, \"sectors\": %.0f, \"ms\": %.4f, \"gsectors_per_s\": %.3f, \"gb_per_s_32B_sectors\": %.1f, \"frac_of_copy_peak\": %s}\n", \
-           prop.name, (unsigned long long)mb, W, U, (unsigned long long)threads, sectors, ms, sectors / (ms * 1e-3) / 1e9, gbs,   \
+           "\"l2_fetch_granularity\": %d, \"threads\": %llu, \"sectors\": %.0f, \"ms\": %.4f, \"gsectors_per_s\": %.3f, \"gb_per_s_32B_sectors\": %.1f, \"frac_of_copy_peak\": %s}\n", \
+           prop.name, (unsigned long long)mb, W, U, int(fetch_now), (unsigned long long)threads, sectors, ms, sectors / (ms * 1e-3) / 1e9, gbs,   \
            copy_gbs > 0 ? std::to_string(gbs / copy_gbs).c_str() : "null");                                                    \
     fflush(stdout);                                                                                                            \
   }
