@@ -104,8 +104,8 @@ GATHER_PEAK_BIN = os.path.join(ROOT, "tools", "gather_peak")
 
 
 def build_tools(force: bool = False) -> None:
-    """Measurement probes under tools/ (random-sector gather ceiling, random-word atomic ceiling)."""
-    for name in ("gather_peak", "atomic_peak"):
+    """Measurement probes under tools/ (random-sector gather ceiling, random-word atomic ceiling, DRAM bytes per load flavour)."""
+    for name in ("gather_peak", "atomic_peak", "load_variants"):
         src, dst = os.path.join(ROOT, "tools", name + ".cu"), os.path.join(ROOT, "tools", name)
         if os.path.exists(src) and (force or not _newer(dst, [src])):
             subprocess.run([_nvcc(), *NVCC_FLAGS, "-o", dst, src], check=True)

@@ -1428,9 +1428,10 @@ static int contigs_push_impl(links_ctx* c, const char* seq, const uint8_t* dev_s
       static const int part_env = []() { const char* e = getenv("LINKS_BF_PARTITION"); return !e ? -1 : e[0] == '0' ? 0 : 1; }();
       static const uint64_t stage_bytes = []() { const char* e = getenv("LINKS_BF_STAGE_MB"); return uint64_t(e ? strtod(e, nullptr) : 4096.0) << 20; }();
       bool partitioned = false;
-      // (up to four blocks the block passes are as fast or faster: C3 / C5, 177 MB, 14.9 ms in three passes against 16.5 ms;
-      //  beyond, every further block is another full hashing pass: C4 at a tenth, 560 MB, 136 ms in one DRAM pass against 75 ms)
-      if (block_bytes && (part_env == 1 || (part_env < 0 && c->bf_bytes > 4 * block_bytes + block_bytes / 2))) {
+      // (every block of the older form is another full hashing pass over the contigs.  With the replay launched once per
+      //  bucket: C3 / C5, 177 MB, 12.6 ms against 14.5-14.8 ms in three passes; C4 at a tenth, 560 MB, 42 ms against 136 ms
+      //  in one DRAM pass.  Two passes are left as they are: not measured against the partition.)
+      if (block_bytes && (part_env == 1 || (part_env < 0 && c->bf_bytes > 2 * block_bytes + block_bytes / 2))) {
         uint32_t block_shift = uint32_t(log2_ceil(std::max<uint64_t>(block_bytes / 4, 64)));
         while (((n_words >> block_shift) + 1 > uint64_t(kMaxBloomBuckets)) && block_shift < 27) ++block_shift;
         const uint32_t n_buckets = uint32_t((n_words + (1ull << block_shift) - 1) >> block_shift);
