@@ -330,54 +330,6 @@ __global__ void table_init_kernel(TableSlot* __restrict__ slots, uint64_t n)
 #ifndef LINKS_TABLE_CAS128
 #define LINKS_TABLE_CAS128 1
 #endif
-// ---- L2 eviction hints for the MATES build (table_seed / table_update).  The table's slots are touched once or twice, at
-// random, in gigabytes; the occupancy bitmap in front of them is small and asked about every contig k-mer.  Each slot
-// access fills a whole 128-byte line (profiles/r03b_load_variants_ncu.txt), and that stream pushed the bitmap out of L2
-// (ncu: L2 hit 15-22 % in both kernels).  Slot loads are therefore marked evict_first (ptxas takes no cache hint on the 16-byte CAS that may follow: it hits
-// the line the load brought) and the bitmap evict_last, per instruction (a persisting carve-out for the bitmap slowed every other kernel down, profiles/r02w_table_l2_persist_ab.txt).
-#ifndef LINKS_TABLE_L2_HINTS
-#define LINKS_TABLE_L2_HINTS 0
-#endif
-__device__ __forceinline__ uint64_t l2_policy_evict_first()
-{
-  uint64_t pol;
-  asm("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(pol));
-  return pol;
-}
-__device__ __forceinline__ uint64_t l2_policy_evict_last()
-{
-  uint64_t pol;
-  asm("createpolicy.fractional.L2::evict_last.b64 %0, 1.0;" : "=l"(pol));
-  return pol;
-}
-__device__ __forceinline__ ulonglong2 slot_ldcg(const void* p)
-{
-#if LINKS_TABLE_L2_HINTS
-  ulonglong2 v;
-  asm volatile("ld.global.cg.L2::cache_hint.v2.u64 {%0,%1}, [%2], %3;" : "=l"(v.x), "=l"(v.y) : "l"(p), "l"(l2_policy_evict_first()) : "memory");
-  return v;
-#else
-  return __ldcg(reinterpret_cast<const ulonglong2*>(p));
-#endif
-}
-__device__ __forceinline__ uint32_t occ_ld(const uint32_t* p)
-{
-#if LINKS_TABLE_L2_HINTS
-  uint32_t v;
-  asm volatile("ld.global.nc.L2::cache_hint.u32 %0, [%1], %2;" : "=r"(v) : "l"(p), "l"(l2_policy_evict_last()));
-  return v;
-#else
-  return __ldg(p);
-#endif
-}
-__device__ __forceinline__ void occ_set(uint32_t* p, uint32_t bit)
-{
-#if LINKS_TABLE_L2_HINTS
-  asm volatile("red.global.or.L2::cache_hint.b32 [%0], %1, %2;" : : "l"(p), "r"(bit), "l"(l2_policy_evict_last()) : "memory");
-#else
-  atomicOr(p, bit);
-#endif
-}
 __device__ __forceinline__ ulonglong2 cas128_raw(void* slot, ulonglong2 cmp, ulonglong2 val)
 {
   ulonglong2 old;
@@ -448,11 +400,11 @@ __device__ __forceinline__ void table_seed(const TableView& tv, uint64_t h)
   if (h == kEmpty) return;  // owns the extra slot [cap], which always exists
   uint64_t i = slot_hash1(h) >> tv.shift;
   for (;;) {
-    ulonglong2 cur = slot_ldcg(&tv.slots[i]);
+    ulonglong2 cur = __ldcg(reinterpret_cast<const ulonglong2*>(&tv.slots[i]));
     if (cur.x == kEmpty) {
       cur = cas128_raw(&tv.slots[i], make_ulonglong2(kEmpty, 0ull), make_ulonglong2(h, 0ull));  // (a stale "empty" is settled by the CAS)
       if (cur.x == kEmpty) {  // claimed: mark the sector occupied (read by the NEXT kernel only)
-        if (tv.occ) occ_set(tv.occ + (i >> 6), 1u << ((i >> 1) & 31));
+        if (tv.occ) atomicOr(tv.occ + (i >> 6), 1u << ((i >> 1) & 31));
         return;
       }
     }
@@ -469,10 +421,10 @@ __device__ __forceinline__ void table_update(const TableView& tv, uint64_t h, ui
   // such miss would cost a random DRAM sector.  The occupancy bitmap (1 bit per sector, 1/256 of the table: L2-resident)
   // answers the common case first: nothing was ever claimed in the home sector => the home slot is empty => the key,
   // which linear probing would have put there or after an unbroken run of occupied slots, is absent.
-  if (tv.occ && !((occ_ld(tv.occ + (i >> 6)) >> ((i >> 1) & 31)) & 1u)) return;
+  if (tv.occ && !((__ldg(tv.occ + (i >> 6)) >> ((i >> 1) & 31)) & 1u)) return;
   for (;;) {
     // keys are final (seeded by the previous kernel); values move 0 -> payload|1 -> |2 only
-    ulonglong2 s = slot_ldcg(&tv.slots[i]);
+    ulonglong2 s = __ldcg(reinterpret_cast<const ulonglong2*>(&tv.slots[i]));
     if (s.x == h) {
       if (s.y == 0ull) {
         s = cas128_raw(&tv.slots[i], make_ulonglong2(h, 0ull), make_ulonglong2(h, payload | 1ull));
