@@ -84,3 +84,23 @@ def test_row_and_issue_formatting(gpu_lib):
                            b"kmer start: 17092 kmer end: 17107 orientation: 0\n"
                            b"kmer start: 9207 kmer end: 9222 orientation: 0\n"
                            b"Calculated distance apart on contig: 7885 - Distance on read: 20000\n")
+
+
+def test_static_entry_point_allocates_nothing_and_states_its_limit():
+    """links_kmer_hashes_static (no counterpart in the reference): its body calls no allocating routine, its scratch is a
+    file-scope static __device__ array whose address comes from cudaGetSymbolAddress, and header, source and test agree on
+    the size limit.  Source-level checks; the behaviour is tested on the GPU in tests/test_zz_no_alloc.py."""
+    src = open(os.path.join(ROOT, "links_b200", "csrc", "links_gpu.cu")).read()
+    hdr = open(os.path.join(ROOT, "include", "links_gpu.h")).read()
+    start = src.index("int links_kmer_hashes_static(")
+    body = src[start:src.index("\n}\n", start)]
+    for banned in ("cudaMalloc", "cudaFree", "cudaHostAlloc", "cudaMallocHost", ".ensure(", "DevBuf", "SeqBatchDev", "std::vector", "new ", "malloc("):
+        assert banned not in body, f"links_kmer_hashes_static uses {banned}"
+    assert "static_scratch_base(" in body and "kStaticMaxBases" in body and "LINKS_E_LIMIT" in body
+    assert re.search(r"static\s+__device__\s+__align__\(256\)\s+unsigned char\s+g_static_scratch\[", src)
+    helper = src[src.index("int static_scratch_base("):src.index("} // namespace", src.index("int static_scratch_base("))]
+    assert "cudaGetSymbolAddress(&p, g_static_scratch)" in helper and "CU(c," in helper
+    m = re.search(r"#define\s+LINKS_STATIC_MAX_BASES\s+\(1u\s*<<\s*(\d+)\)", hdr)
+    assert m, "LINKS_STATIC_MAX_BASES not found in include/links_gpu.h"
+    from . import test_zz_no_alloc
+    assert test_zz_no_alloc.MAX_BASES == 1 << int(m.group(1))
