@@ -163,3 +163,18 @@ def test_unmodified_wrapper_chain_finds_our_layout_program(tmp_path):
     assert r.returncode == 0, r.stdout[-1500:] + r.stderr[-1500:]
     meta = json.load(open(os.path.join(gold, "layout", "layout.json")))
     assert hashlib.sha256(open(tmp_path / "installation_test.scaffolds.fa", "rb").read()).hexdigest() == meta["scaffolds_fa_sha256"]
+
+
+def test_layout_differential_fuzz_against_reference_perl():
+    """tools/layout_fuzz.py: random contigs, random true layouts with spurious and competing links, random -l / -a / -z; the
+    C++ layout must write the files the unmodified Perl writes.  Needs oracle/_ref/perl/LINKS.pl (the reference's file,
+    installed by oracle/Makefile in the build container), so it is skipped where that is absent.  340 cases of the same
+    generator were run when this was added: none differed."""
+    import sys
+    from .conftest import ROOT
+    perl = os.path.join(ROOT, "oracle", "_ref", "perl", "LINKS.pl")
+    if not os.path.exists(perl) or shutil.which("perl") is None:
+        pytest.skip("the reference's LINKS.pl is not installed here (oracle/_ref/perl)")
+    r = subprocess.run([sys.executable, os.path.join(ROOT, "tools", "layout_fuzz.py"), "--cases", "12", "--seed", "5"], capture_output=True, text=True)
+    assert r.returncode == 0, r.stdout + r.stderr
+    assert "12 cases: 0 differ" in r.stdout
