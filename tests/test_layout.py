@@ -168,7 +168,7 @@ def test_unmodified_wrapper_chain_finds_our_layout_program(tmp_path):
 def test_layout_differential_fuzz_against_reference_perl():
     """tools/layout_fuzz.py: random contigs, random true layouts with spurious and competing links, random -l / -a / -z; the
     C++ layout must write the files the unmodified Perl writes.  Needs oracle/_ref/perl/LINKS.pl (the reference's file,
-    installed by oracle/Makefile in the build container), so it is skipped where that is absent.  340 cases of the same
+    installed by oracle/Makefile in the build container), so it is skipped where that is absent.  1840 cases of the same
     generator were run when this was added: none differed."""
     import sys
     from .conftest import ROOT

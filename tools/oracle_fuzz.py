@@ -44,7 +44,7 @@ def dirty(rng: np.random.Generator, seqset):
     return SeqSet(seq, seqset.off, seqset.names)
 
 
-def make_case(seed: int):
+def make_case(seed: int, wide: bool = False):
     from links_b200 import synth
     rng = np.random.default_rng(seed)
     G = int(rng.integers(15_000, 120_000))
@@ -60,6 +60,8 @@ def make_case(seed: int):
     contigs.names = [str(i + 1) for i in range(contigs.n)]
     reads.names = [f"r{i}" for i in range(reads.n)]
     k = int(rng.choice([8, 11, 15, 16, 17, 20, 26, 31, 32, 33, 40]))
+    if wide:  # (a separate switch: the seeded cases of the test suites keep the jobs they were validated with)
+        k = int(rng.choice([1, 2, 3, 5, 48, 63, 64, 65, 100, 127, 200]))
     nd = int(rng.integers(1, 5))
     d = sorted(int(x) for x in rng.choice(np.arange(100, 6000, 50), size=nd, replace=False))
     if rng.random() < 0.3:
@@ -75,6 +77,7 @@ def main() -> int:
     ap.add_argument("--cases", type=int, default=100)
     ap.add_argument("--seed", type=int, default=1)
     ap.add_argument("--keep", action="store_true")
+    ap.add_argument("--wide", action="store_true", help="k from {1, 2, 3, 5, 48, 63, 64, 65, 100, 127, 200} instead of 8..40")
     a = ap.parse_args()
     from make_golden import REF_BIN, fasta_bytes, run_ref, sort_issue_records
     from oracle import oracle_py as oracle
@@ -85,7 +88,7 @@ def main() -> int:
     n_bad = 0
     n_rows = n_issues = 0
     for i in range(a.cases):
-        contigs, reads, o = make_case(a.seed * 100_003 + i)
+        contigs, reads, o = make_case(a.seed * 100_003 + i, a.wide)
         wd = tempfile.mkdtemp(prefix="oracle_fuzz_")
         cfa = fasta_bytes(contigs)
         open(os.path.join(wd, "contigs.fa"), "wb").write(cfa)
