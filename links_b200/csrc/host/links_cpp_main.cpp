@@ -48,10 +48,15 @@ struct Options {
 
 template <class T> std::vector<T> split_numbers(const std::string& text)
 {
+  // the reference's own loop shape (src/InputParser.hpp:28-52): `while (ss.good())`, so an empty text and a trailing
+  // comma both reach std::stoul("") and end the program with std::invalid_argument there -- and therefore here
   std::vector<T> out;
   std::stringstream ss(text);
-  std::string item;
-  while (std::getline(ss, item, ',')) out.push_back(static_cast<T>(std::stoul(item)));
+  while (ss.good()) {
+    std::string item;
+    std::getline(ss, item, ',');
+    out.push_back(static_cast<T>(std::stoul(item)));
+  }
   return out;
 }
 

@@ -227,3 +227,19 @@ def test_readers_differential_fuzz_against_btllib():
     r = subprocess.run([sys.executable, os.path.join(ROOT, "tools", "reader_fuzz.py"), "--cases", "10", "--seed", "8"], capture_output=True, text=True)
     assert r.returncode == 0, r.stdout + r.stderr
     assert "10 files: 0 differ" in r.stdout
+
+
+def test_command_line_differential_fuzz_against_reference_binary():
+    """tools/cli_fuzz.py: random option lines (valid and broken -d / -t lists, lost option values, unknown options, omitted
+    -b, junk in numeric options) through the unmodified reference binary and through links_b200/bin/LINKS_CPP: the same
+    options block, and where the reference stops in its argument handling the same exit code and message.  Needs
+    oracle/_ref/LINKS_CPP; skipped where that is absent.  300 lines of the same generator: none differed (a trailing comma
+    in a list used to: the reference ends in std::stoul(""), this binary had skipped the empty item)."""
+    import subprocess
+    import sys
+    from .conftest import ROOT
+    if not os.path.exists(os.path.join(ROOT, "oracle", "_ref", "LINKS_CPP")):
+        pytest.skip("oracle/_ref/LINKS_CPP not built (needs /root/reference)")
+    r = subprocess.run([sys.executable, os.path.join(ROOT, "tools", "cli_fuzz.py"), "--cases", "40", "--seed", "6"], capture_output=True, text=True)
+    assert r.returncode == 0, r.stdout + r.stderr
+    assert "40 command lines: 0 differ" in r.stdout
