@@ -234,8 +234,9 @@ int links_kmer_hashes(links_ctx* ctx, const char* seq, uint64_t len, uint64_t* f
  * Same arguments, same results, same kernels; every intermediate (staged sequence, 2-bit packing, invalid-base mask,
  * result staging) lives in one static __device__ array of ~2.4 MB that each GPU loading the library holds until the
  * process exits, so the call makes no cudaMalloc / cudaFree.  len > LINKS_STATIC_MAX_BASES fails with LINKS_E_LIMIT.
- * All calls share that array: calls in one process are serialised by the library, but calls from different PROCESSES
- * on one GPU have their own copy each, and nothing else may be assumed about its contents between calls. */
+ * All calls share that array, and it keeps the last call's contents (the call re-zeroes what its kernels expect zeroed).
+ * Two calls that overlapped on the GPU would RACE on it: the library therefore serialises the calls of one process (a
+ * mutex held until the call's stream has drained); different processes on one GPU each have their own copy. */
 #define LINKS_STATIC_MAX_BASES (1u << 17)
 int links_kmer_hashes_static(links_ctx* ctx, const char* seq, uint64_t len, uint64_t* fwd, uint64_t* rev, uint8_t* valid);
 /* KmerBloomFilter membership of given (fwd,rev) hash pairs against the context's filter. */
